@@ -1,0 +1,409 @@
+#!/usr/bin/env python
+"""Benchmark of the locomotion environment step (BASELINE.json metric: Humanoid env-steps/s at
+16k envs/GPU; obs+reward HBM GB/s).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--envs-per-gpu E]
+
+A "step" is one VecEnvRLGames.step of every environment: clamp actions, device-side reset of
+flagged envs (K3), controlFrequencyInv=2 articulation substeps (K2), fused obs/reward/termination
+(K1).  One process per GPU; environments are partitioned by index, no per-step collective; NCCL
+all-reduces the episode statistics every 16 steps on a side stream.
+
+Printed JSON (rank 0, one line): the driver contract keys plus
+  roofline      K1 at 1,048,576 envs (772 MB per launch > 126 MB L2), algorithmic bytes / CUDA-event time
+  cpu_baseline  the oracle (torch CPU obs/reward + float64 OpenMP dynamics) on a bounded sample, rank 0, N=1
+  e2e           the same step through `step_host` (pinned HOST buffers, H2D + D2H inside the timed region)
+  step_breakdown per-kernel device time of one step (hook-by-hook path), for the kernel-share check
+`--impl reference` times the CPU oracle port alone (PhysX / Isaac Sim are not installable: see DESIGN.md).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+ENVS_PER_GPU = 16384
+ROBOT = "Humanoid"
+K1_BYTES = {"Humanoid": 772, "Ant": 556}      # SURVEY.md section 8(d) algorithmic bytes per env-step (K1)
+STEP_BYTES = {"Humanoid": 944}                # informational: fused full step
+ROOFLINE_ENVS = 1 << 20
+
+
+def read_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        try:
+            with open(path) as f:
+                return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.samples, self._stop, self._t = index, [], threading.Event(), None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
+                                      str(self.index)], capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.samples.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.1)
+
+    def __enter__(self):
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        self._t.join(timeout=6)
+
+    def summary(self):
+        sm = [float(s[0]) for s in self.samples if s and s[0].replace(".", "").isdigit()]
+        mx = [float(s[1]) for s in self.samples if len(s) > 1 and s[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(s) > 2 + i and s[2 + i].lower().startswith("active")
+                                                         for s in self.samples)]
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU reference arm / cpu_baseline: the oracle port on the host cores
+# ------------------------------------------------------------------------------------------------
+def cpu_env_step_rate(n_envs: int, steps: int, warmup: int, threads: int):
+    """Full env step on the CPU: float64 OpenMP dynamics (2 substeps) + torch obs/reward/termination +
+    reset of flagged envs.  Returns (env-steps/s, ms per step)."""
+    import numpy as np
+    import torch
+
+    from omniisaacgymenvs_b200.robots.model import build_model
+    from oracle import dynamics as dyn
+    from oracle import locomotion_oracle as lo
+
+    torch.set_num_threads(threads)
+    spec = lo.SPECS[ROBOT]
+    model = build_model(ROBOT)
+    desc = dyn.make_desc(model)
+    D = model.num_dof
+    rng = np.random.default_rng(0)
+    lim = model.dof_limits().astype(np.float64)
+    pos = np.zeros((n_envs, 3)); pos[:, 2] = model.spawn_height
+    quat = np.tile([[1.0, 0, 0, 0]], (n_envs, 1))
+    vel = np.zeros((n_envs, 6))
+    q = np.clip(rng.uniform(-0.2, 0.2, (n_envs, D)), lim[:, 0], lim[:, 1])
+    qd = rng.uniform(-0.1, 0.1, (n_envs, D))
+    sens = np.zeros((n_envs, model.num_sensors, 6))
+    init = dict(pos=pos.copy(), quat=quat.copy(), q=q.copy())
+    gears = torch.tensor(spec.joint_gears)
+    s = {"potentials": torch.full((n_envs,), -1000.0 * 60.0), "progress_buf": torch.zeros(n_envs, dtype=torch.int64),
+         "reset_buf": torch.zeros(n_envs, dtype=torch.int64),
+         "targets": torch.tensor([1000.0, 0, 0]).repeat(n_envs, 1), "inv_start_rot": torch.tensor([1.0, 0, 0, 0]).repeat(n_envs, 1),
+         "basis_vec0": torch.tensor([1.0, 0, 0]).repeat(n_envs, 1), "basis_vec1": torch.tensor([0.0, 0, 1]).repeat(n_envs, 1),
+         "dof_lo": torch.from_numpy(lim[:, 0]).float(), "dof_hi": torch.from_numpy(lim[:, 1]).float()}
+
+    def one_step():
+        actions = torch.rand(n_envs, D) * 2 - 1
+        ids = np.nonzero(s["reset_buf"].numpy())[0]
+        if len(ids):
+            pos[ids] = init["pos"][ids]; quat[ids] = init["quat"][ids]; vel[ids] = 0
+            q[ids] = np.clip(init["q"][ids] + rng.uniform(-0.2, 0.2, (len(ids), D)), lim[:, 0], lim[:, 1])
+            qd[ids] = rng.uniform(-0.1, 0.1, (len(ids), D))
+            s["reset_buf"][ids] = 0; s["progress_buf"][ids] = 0
+        eff = (actions * gears * spec.power_scale).double().numpy()
+        dyn.step(desc, pos, quat, vel, q, qd, np.ascontiguousarray(eff), sens, 2, 0.0083, threads)
+        s.update(pos=torch.from_numpy(pos).float(), quat=torch.from_numpy(quat).float(), vel=torch.from_numpy(vel).float(),
+                 dof_pos=torch.from_numpy(q).float(), dof_vel=torch.from_numpy(qd).float(),
+                 sensors=torch.from_numpy(sens).float(), actions=actions)
+        out = lo.post_physics_step(spec, s)
+        s["potentials"], s["progress_buf"], s["reset_buf"] = out["potentials"], out["progress_buf"], out["reset_buf"]
+        return out
+
+    for _ in range(warmup):
+        one_step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        one_step()
+    dt = time.perf_counter() - t0
+    return n_envs * steps / dt, 1e3 * dt / steps
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    threads = os.cpu_count() or 1
+    sample_envs = args.cpu_sample_envs
+    rate, ms = cpu_env_step_rate(sample_envs, args.steps, max(args.warmup, 1), threads)
+    line = {
+        "impl": "reference", "metric": "humanoid_env_steps_per_sec", "value": rate, "unit": "env-steps/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"Humanoid full env step, {ENVS_PER_GPU} envs/GPU (BASELINE.json configs[2])",
+                   "sample_envs_per_step": sample_envs},
+        "cpu_baseline": {"value": rate, "unit": "env-steps/s", "cores": threads, "kind": "port",
+                         "sample": f"{sample_envs} envs x {args.steps} full env steps (2 dynamics substeps + obs/reward/reset); "
+                                   "PhysX/Isaac Sim not installable, float64 OpenMP oracle + torch CPU oracle stand in"},
+        "e2e": {"value": rate, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------
+# our arm
+# ------------------------------------------------------------------------------------------------
+def k1_roofline(torch, device, n_envs, iters=20, warmup=5):
+    """Achieved bandwidth of K1 at n_envs (state + outputs > L2) via CUDA events on the launch stream."""
+    import ctypes as C
+
+    from omniisaacgymenvs_b200 import _lib
+    from omniisaacgymenvs_b200.utils.task_util import make_env
+
+    env, task = make_env(ROBOT, num_envs=n_envs, device_id=device.index or 0)
+    v = task.get_robot()
+    g = torch.Generator(device=device).manual_seed(0)
+    # synthetic state of SURVEY.md 8(d): everything random, heights straddling the termination height
+    v.root_pos.normal_(generator=g); v.root_pos[:, 2].mul_(0.3).add_(1.0)
+    v.root_quat.normal_(generator=g); v.root_quat.div_(v.root_quat.norm(dim=-1, keepdim=True))
+    v.root_vel.normal_(generator=g); v.dof_vel.normal_(generator=g); v.sensor_forces.normal_(generator=g).mul_(10)
+    v.dof_pos.uniform_(-1.0, 1.0, generator=g); task.actions.uniform_(-1.0, 1.0, generator=g)
+    task.progress_buf.random_(0, 900, generator=g); task.reset_buf.zero_()
+    lib = _lib.load()
+    stream = _lib.current_stream_ptr(device)
+
+    def launch():
+        rc = lib.oige_obs_reward_reset_f32(C.byref(task._params), C.byref(v.state_struct), C.byref(task._buffers),
+                                           n_envs, stream)
+        _lib.check(rc, "K1")
+
+    for _ in range(warmup):
+        launch()
+    torch.cuda.synchronize(device)
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(iters)]
+    for a, b in evs:
+        a.record(); launch(); b.record()
+    torch.cuda.synchronize(device)
+    ms = [a.elapsed_time(b) for a, b in evs]
+    del env, task, v
+    torch.cuda.empty_cache()
+    return statistics.mean(ms), min(ms)
+
+
+def step_breakdown(torch, env, task, actions, iters=10):
+    """Device time of each kernel of one step (hook-by-hook calls, CUDA events)."""
+    import ctypes as C
+
+    from omniisaacgymenvs_b200 import _lib
+
+    lib = _lib.load()
+    v = task.get_robot()
+    dev = torch.device(task.device)
+    stream = _lib.current_stream_ptr(dev)
+    n = task.num_envs
+    acc = {"reset_ms": 0.0, "articulation_ms": 0.0, "obs_reward_ms": 0.0}
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+    for _ in range(iters):
+        torch.cuda.synchronize(dev)
+        ev[0].record()
+        _lib.check(lib.oige_reset_masked_f32(C.byref(task._params), C.byref(v.state_struct), C.byref(task._buffers),
+                                             C.byref(task._reset_init), None, None, 1, 1, 0, n, stream), "K3")
+        ev[1].record()
+        _lib.check(lib.oige_articulation_step_f32(v.model_handle, C.byref(task._params), C.byref(v.state_struct),
+                                                  actions.data_ptr(), n, 2, env._world.get_physics_dt(), stream), "K2")
+        ev[2].record()
+        _lib.check(lib.oige_obs_reward_reset_f32(C.byref(task._params), C.byref(v.state_struct), C.byref(task._buffers),
+                                                 n, stream), "K1")
+        ev[3].record()
+        torch.cuda.synchronize(dev)
+        acc["reset_ms"] += ev[0].elapsed_time(ev[1]) / iters
+        acc["articulation_ms"] += ev[1].elapsed_time(ev[2]) / iters
+        acc["obs_reward_ms"] += ev[2].elapsed_time(ev[3]) / iters
+    return acc
+
+
+def run_ours(args):
+    import torch
+
+    from omniisaacgymenvs_b200 import _lib
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py (our arm) needs a CUDA device: there is no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+
+        dist = dist_mod
+        dist.init_process_group("nccl", device_id=device)
+
+    from omniisaacgymenvs_b200.utils.task_util import make_env
+
+    n = args.envs_per_gpu
+    env, task = make_env(ROBOT, num_envs=n, device_id=local_rank, seed=42, env_id_offset=rank * n,
+                         global_num_envs=world * n)
+    env.reset()
+    K, W = args.steps, max(args.warmup, 3)
+    D = task.num_actions
+    gen = torch.Generator(device=device).manual_seed(1234 + rank)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)  # > 126 MB L2
+    side = torch.cuda.Stream(device=device)
+    stats_total = torch.zeros(4, dtype=torch.float64, device=device)
+
+    def reduce_stats():
+        s = task.read_episode_stats()
+        if dist is not None:
+            side.wait_stream(torch.cuda.current_stream(device))
+            with torch.cuda.stream(side):
+                dist.all_reduce(s)
+                stats_total.add_(s)
+        else:
+            stats_total.add_(s)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize(device)
+
+    # ---- warm-up ----
+    for _ in range(W):
+        env.step(torch.rand(n, D, device=device, generator=gen) * 2 - 1)
+    barrier()
+
+    # ---- timed region: device-resident inputs, per-step event pairs, L2 flushed between steps ----
+    launches0 = _lib.launch_count()
+    acts = [torch.rand(n, D, device=device, generator=gen) * 2 - 1 for _ in range(min(K, 64))]
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    with ClockSampler(local_rank) as clocks:
+        barrier()
+        t_wall0 = time.perf_counter()
+        for i in range(K):
+            flush.zero_()
+            a, b = evs[i]
+            a.record()
+            env.step(acts[i % len(acts)])
+            b.record()
+            if (i + 1) % 16 == 0:
+                reduce_stats()
+        barrier()
+        t_wall = time.perf_counter() - t_wall0
+    launches = _lib.launch_count() - launches0
+    dev_ms = sum(a.elapsed_time(b) for a, b in evs)
+    t = torch.tensor([dev_ms], dtype=torch.float64, device=device)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms = float(t.item())
+    ms_per_step = dev_ms / K
+    value = world * n * K / (dev_ms / 1e3)
+    reduce_stats()
+    torch.cuda.current_stream(device).wait_stream(side)
+
+    # ---- end-to-end: HOST buffers through the C-ABI host entry point, copies inside the timed region ----
+    a_host = [(torch.rand(n, D) * 2 - 1).pin_memory() for _ in range(4)]
+    obs_h = torch.empty(n, task.num_observations).pin_memory()
+    rew_h = torch.empty(n).pin_memory()
+    rst_h = torch.empty(n, dtype=torch.int64).pin_memory()
+    for i in range(3):
+        env.step_host(a_host[i % 4], obs_h, rew_h, rst_h)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(K):
+        env.step_host(a_host[i % 4], obs_h, rew_h, rst_h)
+        torch.cuda.synchronize(device)  # the caller reads obs/rew/reset every step
+    if dist is not None:
+        dist.barrier()
+    e2e_s = time.perf_counter() - t0
+    te = torch.tensor([e2e_s], dtype=torch.float64, device=device)
+    if dist is not None:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_value = world * n * K / float(te.item())
+    h2d = n * D * 4
+    d2h = n * task.num_observations * 4 + n * 4 + n * 8
+
+    line = None
+    if rank == 0:
+        breakdown = step_breakdown(torch, env, task, acts[0])
+        stats = stats_total.tolist()
+        del env, task
+        torch.cuda.empty_cache()
+        peak, peak_src = read_peaks()
+        roof = None
+        cpu = None
+        if world == 1 or True:
+            k1_ms, k1_best = k1_roofline(torch, device, ROOFLINE_ENVS)
+            achieved = K1_BYTES[ROBOT] * ROOFLINE_ENVS / (k1_ms * 1e-3) / 1e9
+            roof = {"bound": "hbm", "kernel": "obs_reward_reset_kernel<21,2,64>", "achieved": achieved, "peak": peak,
+                    "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                    "envs": ROOFLINE_ENVS, "bytes_per_env": K1_BYTES[ROBOT], "avg_ms": k1_ms, "best_ms": k1_best,
+                    "note": "K1 timed alone at 1,048,576 envs (772 MB/launch > L2); the full step is dominated by "
+                            "K2 which is issue/latency-bound (no HBM or tensor roofline applies), see step_breakdown"}
+        if world == 1 and not args.no_cpu_baseline:
+            threads = os.cpu_count() or 1
+            rate, cms = cpu_env_step_rate(args.cpu_sample_envs, 30, 2, threads)
+            cpu = {"value": rate, "unit": "env-steps/s", "cores": threads, "kind": "port",
+                   "sample": f"{args.cpu_sample_envs} envs x 30 full env steps on the host cores "
+                             "(float64 OpenMP dynamics oracle, 2 substeps, + torch CPU obs/reward/reset oracle)"}
+        line = {
+            "metric": "humanoid_env_steps_per_sec", "value": value, "unit": "env-steps/s", "n_gpus": world,
+            "steps": K, "warmup": W, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"Humanoid full env step (K3 reset + 2x K2 articulation substeps + K1 obs/reward/reset), "
+                                   f"{n} envs/GPU (BASELINE.json configs[2])",
+                       "envs_per_gpu": n, "global_envs": world * n, "parallelism": f"env-index sharding x{world}",
+                       "l2": "flushed between steps (256 MiB memset outside the per-step CUDA-event pairs)",
+                       "actions": "uniform random policy, device-resident"},
+            "clocks": clocks.summary(),
+            "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+            "gpu_launches": int(launches),
+            "roofline": roof, "cpu_baseline": cpu, "step_breakdown": breakdown,
+            "wall_s_timed_region": t_wall,
+            "episode_stats": {"sum_reward": stats[0], "episodes_finished": stats[1],
+                              "mean_episode_length": (stats[2] / stats[1]) if stats[1] else None,
+                              "env_steps": stats[3]},
+        }
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    if line is not None:
+        print(json.dumps(line), flush=True)
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--envs-per-gpu", type=int, default=ENVS_PER_GPU)
+    ap.add_argument("--cpu-sample-envs", type=int, default=ENVS_PER_GPU)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,228 @@
+/*
+ * oige_b200.h -- C ABI of the B200-native locomotion environment step.
+ *
+ * The reference (tzmhuang/OmniIsaacGymEnvs, OIGE v1.1.0) is pure Python: it has no FFI of its
+ * own.  Each entry point below therefore cites the reference *Python* interface it replaces
+ * (paths relative to /root/reference/omniisaacgymenvs).  The Python host side
+ * (omniisaacgymenvs_b200/) binds these with ctypes -- see INTEGRATION.md for the stub a
+ * maintainer of the reference would add.
+ *
+ * Conventions
+ *   - every pointer in OigeState / OigeTaskBuffers / OigeResetInit is a DEVICE pointer owned by
+ *     the caller (PyTorch allocates everything); contiguous row-major; fp32 unless noted;
+ *     16-byte aligned base addresses (torch allocations are).
+ *   - quaternions are (w, x, y, z); root_vel is (lin xyz, ang xyz); joints in breadth-first order
+ *     (docs/transfering_policies_from_isaac_gym.md:26-54).
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*); the library never
+ *     synchronises the device and never allocates per step.
+ *   - return value: 0 = ok, <0 = argument error (OIGE_E_*), >0 = cudaError_t of a failed launch.
+ *     oige_last_error() returns a thread-local message for the last non-zero return.
+ *   - there is NO CPU fallback: without a CUDA device every compute entry point fails.
+ */
+#ifndef OIGE_B200_H
+#define OIGE_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OIGE_ABI_VERSION 1
+#define OIGE_MAX_DOF 32      /* one lane per link in the articulation kernel */
+#define OIGE_MAX_LINKS 32
+#define OIGE_MAX_SPHERES 48  /* collision spheres per robot */
+#define OIGE_MAX_SENSORS 4
+#define OIGE_STATS_SLOTS 32  /* episode_stats is striped over slots to keep atomics uncontended */
+
+#define OIGE_OK 0
+#define OIGE_E_NULL (-1)        /* null pointer argument */
+#define OIGE_E_SHAPE (-2)       /* unsupported (num_dof, num_sensors, num_obs) combination */
+#define OIGE_E_ALIGN (-3)       /* device pointer not 16-byte aligned */
+#define OIGE_E_RANGE (-4)       /* n_envs / substeps / k out of range */
+#define OIGE_E_MODEL (-5)       /* malformed articulation model */
+#define OIGE_E_NODEVICE (-6)    /* no CUDA device / wrong architecture */
+
+enum { OIGE_LIMIT_COST_HUMANOID = 0, OIGE_LIMIT_COST_ANT = 1 };
+
+/* Scalar constants of one locomotion task.
+ * Replaces: LocomotionTask.__init__ scalars (tasks/shared/locomotion.py:53-67), the per-env
+ * replicated constants of post_reset (locomotion.py:152-163: targets, inv_start_rot, basis
+ * vectors, dt = 1/60), joint_gears / motor_effort_ratio / dof limits (tasks/humanoid.py:82-112,
+ * tasks/ant.py:80-84), clip_obs (tasks/base/rl_task.py:69). */
+typedef struct OigeTaskParams {
+    int32_t num_dof;          /* D: 21 Humanoid, 8 Ant */
+    int32_t num_sensors;      /* S: 2 Humanoid, 4 Ant */
+    int32_t num_obs;          /* 12 + 3D + 6S */
+    int32_t limit_cost_kind;  /* OIGE_LIMIT_COST_* (humanoid.py:120-127 vs ant.py:92-95) */
+    int32_t walk_target_uses_z; /* 1 = upstream compute_rot quirk atan2(dz, dx) (default), 0 = atan2(dy, dx) */
+    int32_t progress_increment; /* 1: fuse `progress_buf += 1` (rl_task.py:242) into the pass; 0: leave it */
+    int32_t reserved_i[2];
+    float dt;                 /* task dt, 1/60 (locomotion.py:163) */
+    float dof_vel_scale;
+    float angular_velocity_scale;
+    float contact_force_scale;
+    float heading_weight;
+    float up_weight;
+    float actions_cost_scale;
+    float energy_cost_scale;
+    float joints_at_limit_cost_scale;
+    float death_cost;
+    float termination_height;
+    float alive_reward_scale;
+    float max_episode_length; /* float, as in the jit signature (locomotion.py:265) */
+    float clip_obs;           /* +inf = no clamp (envs/vec_env_rlgames.py:42) */
+    float power_scale;
+    float reserved_f;
+    float targets[4];         /* xyz (+pad) */
+    float inv_start_rot[4];   /* wxyz */
+    float basis_vec0[4];      /* heading basis xyz (+pad) */
+    float basis_vec1[4];      /* up basis xyz (+pad) */
+    float dof_limits_lower[OIGE_MAX_DOF];
+    float dof_limits_upper[OIGE_MAX_DOF];
+    float motor_effort_ratio[OIGE_MAX_DOF];
+    float joint_gears[OIGE_MAX_DOF];
+} OigeTaskParams;
+
+/* ArticulationView-style state tensors.
+ * Replaces the buffers behind get_world_poses / get_velocities / get_joint_positions /
+ * get_joint_velocities / _physics_view.get_force_sensor_forces (locomotion.py:81-89). */
+typedef struct OigeState {
+    float* root_pos;   /* [N,3] world frame */
+    float* root_quat;  /* [N,4] wxyz */
+    float* root_vel;   /* [N,6] lin, ang (world frame) */
+    float* dof_pos;    /* [N,D] */
+    float* dof_vel;    /* [N,D] */
+    float* sensors;    /* [N,S,6] force, torque at each foot sensor (sensor frame) */
+} OigeState;
+
+/* RL buffers of the task.  Replaces RLTask.cleanup buffers (tasks/base/rl_task.py:98-107) and
+ * the LocomotionTask extras of post_reset (locomotion.py:152-168). */
+typedef struct OigeTaskBuffers {
+    float* obs;              /* [N,OBS] */
+    float* rew;              /* [N] */
+    int64_t* reset_buf;      /* [N] in/out */
+    int64_t* progress_buf;   /* [N] in/out */
+    float* potentials;       /* [N] in/out */
+    float* prev_potentials;  /* [N] out */
+    float* up_vec;           /* [N,3] out */
+    float* heading_vec;      /* [N,3] out */
+    float* actions;          /* [N,D] the task's stored (clamped) actions */
+    double* episode_stats;   /* [OIGE_STATS_SLOTS,4] accumulators or NULL: sum(rew), #done, sum(len at done), #env-steps */
+} OigeTaskBuffers;
+
+/* Per-env initial state captured at post_reset (locomotion.py:148-150). */
+typedef struct OigeResetInit {
+    const float* initial_root_pos;  /* [N,3] */
+    const float* initial_root_rot;  /* [N,4] */
+    const float* initial_dof_pos;   /* [N,D] */
+} OigeResetInit;
+
+/* Host-side description of one robot for the articulation kernel (one link per DoF plus the
+ * floating root; multi-DoF joints are chains of massless links).  No reference equivalent: the
+ * reference loads USD assets from a Nucleus server (robots/articulations/humanoid.py:57, ant.py:57)
+ * into PhysX.  Link 0 is the root. Links are in an order where parent[i] < i. */
+typedef struct OigeModelDesc {
+    int32_t num_links;                       /* 1 + D */
+    int32_t num_spheres;
+    int32_t num_sensors;
+    int32_t reserved;
+    int32_t parent[OIGE_MAX_LINKS];          /* parent[0] = -1 */
+    int32_t dof_index[OIGE_MAX_LINKS];       /* link -> column of dof_pos (BFS dof order); -1 for root */
+    float joint_pos[OIGE_MAX_LINKS][3];      /* joint anchor in the parent link frame */
+    float joint_quat[OIGE_MAX_LINKS][4];     /* fixed rotation parent link frame -> this link frame at q=0 (wxyz) */
+    float joint_axis[OIGE_MAX_LINKS][3];     /* unit hinge axis in this link's frame */
+    float mass[OIGE_MAX_LINKS];
+    float com[OIGE_MAX_LINKS][3];            /* link frame */
+    float inertia[OIGE_MAX_LINKS][6];        /* about COM, link frame: xx yy zz xy xz yz */
+    float armature[OIGE_MAX_LINKS];
+    float damping[OIGE_MAX_LINKS];
+    float stiffness[OIGE_MAX_LINKS];         /* passive spring towards spring_ref */
+    float spring_ref[OIGE_MAX_LINKS];
+    float limit_lower[OIGE_MAX_LINKS];
+    float limit_upper[OIGE_MAX_LINKS];
+    int32_t sphere_link[OIGE_MAX_SPHERES];
+    float sphere_pos[OIGE_MAX_SPHERES][3];   /* link frame */
+    float sphere_radius[OIGE_MAX_SPHERES];
+    int32_t sensor_link[OIGE_MAX_SENSORS];   /* link whose net ground-contact wrench is reported */
+    float gravity[3];
+    float contact_stiffness;                 /* N/m */
+    float contact_damping;                   /* N s/m, only while approaching */
+    float friction_mu;                       /* cfg/task/Humanoid.yaml:46-48 */
+    float friction_viscous;                  /* N s/m regularisation slope of the Coulomb cone */
+    float limit_stiffness;                   /* N m/rad beyond a joint limit */
+    float limit_damping;
+    float max_joint_velocity;                /* rad/s clamp (docs/transfering_policies_from_isaac_gym.md:71-77) */
+    float angular_damping;                   /* 1/s on the root angular velocity */
+} OigeModelDesc;
+
+typedef struct OigeModel OigeModel; /* opaque; holds the immutable device-side model table */
+
+/* ---- library ---- */
+int oige_abi_version(void);
+const char* oige_last_error(void);
+/* number of kernels this library has launched since load (monotonic; for bench.py's gpu_launches) */
+uint64_t oige_kernel_launch_count(void);
+
+/* ---- K1: fused observation / reward / termination pass ----
+ * Replaces, in one launch: RLTask.post_physics_step's `progress_buf += 1` (rl_task.py:242),
+ * LocomotionTask.get_observations + jit get_observations (locomotion.py:80-101, 194-254),
+ * get_dof_at_limit_cost (humanoid.py:116-127 / ant.py:88-95), calculate_metrics + jit
+ * (locomotion.py:173-178, 271-321), is_done + jit (locomotion.py:180-183, 257-268) and the obs
+ * clamp of VecEnvRLGames._process_data (envs/vec_env_rlgames.py:42). */
+int oige_obs_reward_reset_f32(const OigeTaskParams* params, const OigeState* state,
+                              const OigeTaskBuffers* buf, int64_t n_envs, void* stream);
+/* same pass with an explicit tile size (envs per CTA: 32, 64 or 128; 0 = automatic) -- tuning hook */
+int oige_obs_reward_reset_tile_f32(const OigeTaskParams* params, const OigeState* state,
+                                   const OigeTaskBuffers* buf, int64_t n_envs, int32_t tile, void* stream);
+
+/* ---- K3: reset ----
+ * Replaces LocomotionTask.reset_idx (locomotion.py:116-145) and the nonzero()/len() host sync of
+ * pre_physics_step (locomotion.py:104-106).
+ * masked: resets every env whose reset_buf != 0 (device-side mask, no host sync).
+ * idx:    resets the k envs listed in env_ids (device int64), the reference's calling form.
+ * rand_pos / rand_vel: raw U[0,1) draws ([N,D] for masked, [k,D] for idx) -- the values
+ * torch.rand would have produced (parity mode).  If NULL the kernel draws Philox4x32-10
+ * uniforms keyed by (seed, env_id_offset + env, counter) so results do not depend on sharding. */
+int oige_reset_masked_f32(const OigeTaskParams* params, const OigeState* state, const OigeTaskBuffers* buf,
+                          const OigeResetInit* init, const float* rand_pos, const float* rand_vel,
+                          uint64_t seed, uint64_t counter, int64_t env_id_offset,
+                          int64_t n_envs, void* stream);
+int oige_reset_idx_f32(const OigeTaskParams* params, const OigeState* state, const OigeTaskBuffers* buf,
+                       const OigeResetInit* init, const int64_t* env_ids, int64_t k,
+                       const float* rand_pos, const float* rand_vel,
+                       uint64_t seed, uint64_t counter, int64_t env_id_offset, void* stream);
+
+/* ---- K2: batched reduced-coordinate articulation step ----
+ * Replaces set_joint_efforts (locomotion.py:108-114) + control_frequency_inv x World.step
+ * (envs/vec_env_rlgames.py:64-66; PhysX, unavailable) with a warp-per-env articulated-body
+ * forward-dynamics step.  efforts = actions * joint_gears * power_scale. */
+OigeModel* oige_model_create(const OigeModelDesc* desc);
+void oige_model_destroy(OigeModel* model);
+int oige_articulation_step_f32(const OigeModel* model, const OigeTaskParams* params, const OigeState* state,
+                               const float* actions, int64_t n_envs, int32_t substeps, float dt, void* stream);
+
+/* ---- whole VecEnvRLGames.step on device buffers (K3 -> K2 -> K1) ----
+ * Replaces VecEnvRLGames.step (envs/vec_env_rlgames.py:56-78) minus the rl_device copies:
+ * clamps `actions_in` to +-clip_actions into buf->actions, then masked reset, articulation
+ * step, fused obs/reward/reset. */
+int oige_env_step_f32(const OigeModel* model, const OigeTaskParams* params, const OigeState* state,
+                      const OigeTaskBuffers* buf, const OigeResetInit* init, const float* actions_in,
+                      float clip_actions, uint64_t seed, uint64_t counter, int64_t env_id_offset,
+                      int64_t n_envs, int32_t substeps, float dt, void* stream);
+
+/* ---- the same step with HOST buffers (the call rl_games would make with CPU tensors) ----
+ * actions_host [N,D] -> H2D into actions_dev_staging; after the step obs/rew/reset_buf are copied
+ * D2H into the host buffers.  All copies are cudaMemcpyAsync on `stream` (pinned host memory
+ * gives true asynchrony); the caller synchronises the stream before reading the outputs. */
+int oige_env_step_host_f32(const OigeModel* model, const OigeTaskParams* params, const OigeState* state,
+                           const OigeTaskBuffers* buf, const OigeResetInit* init,
+                           const float* actions_host, float* actions_dev_staging,
+                           float* obs_host, float* rew_host, int64_t* reset_host,
+                           float clip_actions, uint64_t seed, uint64_t counter, int64_t env_id_offset,
+                           int64_t n_envs, int32_t substeps, float dt, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OIGE_B200_H */

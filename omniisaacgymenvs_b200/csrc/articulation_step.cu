@@ -1,0 +1,664 @@
+// K2 -- batched reduced-coordinate articulation step, one warp per environment (sm_100a).
+//
+// Stands in for `set_joint_efforts` + `control_frequency_inv x World.step` of the reference
+// (tasks/shared/locomotion.py:108-114, envs/vec_env_rlgames.py:64-66), i.e. for the PhysX 5 GPU
+// articulation pipeline that cannot be installed here.  See DESIGN.md "K2" for the model.
+//
+//   lane i            = link i of the kinematic tree (lane 0 = floating root, one link per DoF)
+//   spatial vectors   = (angular xyz, linear xyz) in WORLD-aligned axes about the point O that
+//                       coincides with the root origin at the start of the substep, so that
+//                       parent->child propagation needs no frame transforms: the tree recursion
+//                       is pure shuffle + add.
+//   forward dynamics  = articulated-body algorithm: top-down kinematics, bottom-up articulated
+//                       inertia (symmetric 6x6, 21 registers/lane), 6x6 Cholesky at the root,
+//                       top-down accelerations.  Parent/child exchange = warp shuffles.
+//   time stepping     = linearly-implicit Euler: joint springs/dampers/limit penalties and the
+//                       ground-contact spring-damper-friction forces are evaluated at the
+//                       end-of-step velocity, which adds a PSD term to the joint-space inertia
+//                       (diagonal for joints; P^T C P on the link's 6x6 inertia for contacts)
+//                       and keeps the 120 Hz step unconditionally stable for stiff contacts.
+//   tree constants    = SoA table staged in shared memory once per CTA.
+//
+// Tensor cores are not used: the per-env matrices are 6x6 and the work is a latency-bound tree
+// recursion, not a dense contraction.
+#include <math.h>
+
+#include "oige_common.cuh"
+
+struct OigeModel {
+    void* dev_table;      // DevModel in device memory
+    int num_links;
+    int num_dof;
+    int num_sensors;
+};
+
+namespace oige {
+namespace {
+
+constexpr int kWarpsPerBlock = 4;
+constexpr int kMaxLevels = 16;
+constexpr int kMaxChildren = 4;
+
+struct DevModel {
+    int num_links, num_spheres, num_sensors, max_depth;
+    int max_sph_per_link, pad0, pad1, pad2;
+    int parent[32];
+    int dof[32];
+    int level[32];
+    int child[kMaxChildren][32];
+    int maxch_at_level[kMaxLevels];  // max #children over parents at this level
+    int sph_start[32];
+    int sph_count[32];
+    int sensor_of_link[32];
+    float jpos[3][32];
+    float jquat[4][32];
+    float axis[3][32];
+    float mass[32];
+    float com[3][32];
+    float inertia[6][32];  // xx yy zz xy xz yz
+    float armature[32], damping[32], stiffness[32], sref[32], lo[32], hi[32];
+    float sph_pos[3][OIGE_MAX_SPHERES];
+    float sph_r[OIGE_MAX_SPHERES];
+    float gravity[4];
+    float k_c, d_c, mu, c_visc, k_lim, d_lim, max_qd, ang_damp;
+};
+static_assert(sizeof(DevModel) % 16 == 0, "DevModel must be int4-copyable");
+
+// ---- small vector helpers ---------------------------------------------------------------
+struct V3 { float x, y, z; };
+__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+__device__ __forceinline__ V3 operator-(V3 a, V3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+__device__ __forceinline__ V3 operator*(float s, V3 a) { return {s * a.x, s * a.y, s * a.z}; }
+__device__ __forceinline__ V3 cross(V3 a, V3 b) {
+    return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x};
+}
+__device__ __forceinline__ float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+
+struct Q4 { float w, x, y, z; };
+__device__ __forceinline__ Q4 qmul(Q4 a, Q4 b) {
+    return {a.w * b.w - a.x * b.x - a.y * b.y - a.z * b.z, a.w * b.x + a.x * b.w + a.y * b.z - a.z * b.y,
+            a.w * b.y - a.x * b.z + a.y * b.w + a.z * b.x, a.w * b.z + a.x * b.y - a.y * b.x + a.z * b.w};
+}
+struct M3 { float m[9]; };  // row-major
+__device__ __forceinline__ M3 qmat(Q4 q) {
+    const float xx = q.x * q.x, yy = q.y * q.y, zz = q.z * q.z;
+    const float xy = q.x * q.y, xz = q.x * q.z, yz = q.y * q.z;
+    const float wx = q.w * q.x, wy = q.w * q.y, wz = q.w * q.z;
+    M3 R;
+    R.m[0] = 1.f - 2.f * (yy + zz); R.m[1] = 2.f * (xy - wz);       R.m[2] = 2.f * (xz + wy);
+    R.m[3] = 2.f * (xy + wz);       R.m[4] = 1.f - 2.f * (xx + zz); R.m[5] = 2.f * (yz - wx);
+    R.m[6] = 2.f * (xz - wy);       R.m[7] = 2.f * (yz + wx);       R.m[8] = 1.f - 2.f * (xx + yy);
+    return R;
+}
+__device__ __forceinline__ V3 mulv(const M3& R, V3 v) {
+    return {R.m[0] * v.x + R.m[1] * v.y + R.m[2] * v.z, R.m[3] * v.x + R.m[4] * v.y + R.m[5] * v.z,
+            R.m[6] * v.x + R.m[7] * v.y + R.m[8] * v.z};
+}
+__device__ __forceinline__ V3 mulTv(const M3& R, V3 v) {
+    return {R.m[0] * v.x + R.m[3] * v.y + R.m[6] * v.z, R.m[1] * v.x + R.m[4] * v.y + R.m[7] * v.z,
+            R.m[2] * v.x + R.m[5] * v.y + R.m[8] * v.z};
+}
+
+// symmetric 6x6 in 21 registers; index of (i,j), i<=j
+__host__ __device__ constexpr int sidx(int i, int j) {
+    return i <= j ? (i * 6 - (i * (i - 1)) / 2 + (j - i)) : (j * 6 - (j * (j - 1)) / 2 + (i - j));
+}
+struct S6 { float a[21]; };
+struct V6 { float a[6]; };  // (ang xyz, lin xyz)
+
+__device__ __forceinline__ V6 s6mul(const S6& I, const V6& x) {
+    V6 y;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+        float acc = 0.f;
+#pragma unroll
+        for (int j = 0; j < 6; ++j) acc = fmaf(I.a[sidx(i, j)], x.a[j], acc);
+        y.a[i] = acc;
+    }
+    return y;
+}
+__device__ __forceinline__ float dot6(const V6& a, const V6& b) {
+    float acc = 0.f;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) acc = fmaf(a.a[i], b.a[i], acc);
+    return acc;
+}
+__device__ __forceinline__ V3 ang(const V6& v) { return {v.a[0], v.a[1], v.a[2]}; }
+__device__ __forceinline__ V3 lin(const V6& v) { return {v.a[3], v.a[4], v.a[5]}; }
+__device__ __forceinline__ V6 mk6(V3 a, V3 l) { return {{a.x, a.y, a.z, l.x, l.y, l.z}}; }
+
+__device__ __forceinline__ float shfl(float v, int src) { return __shfl_sync(0xffffffffu, v, src); }
+
+// Ground contact of one sphere attached to a link (see DESIGN.md "contact model").
+// Inputs in the substep's O-frame; root_z = absolute height of O.  Returns false if inactive.
+struct Contact {
+    V3 r;    // application point (bottom of the sphere), rel. O
+    V3 F0;   // force at the current state incl. the velocity-product correction C*(P b)
+    V3 C;    // dt * G (diagonal: tangential, tangential, normal)
+};
+__device__ __forceinline__ bool contact_eval(const DevModel& M, int s, const M3& R, V3 p, const V6& v, const V6& b,
+                                             float root_z, float dt, Contact& c) {
+    const V3 local = {M.sph_pos[0][s], M.sph_pos[1][s], M.sph_pos[2][s]};
+    const float rad = M.sph_r[s];
+    const V3 x = p + mulv(R, local);
+    const float pen = rad - (root_z + x.z);
+    if (!(pen > 0.f)) return false;
+    c.r = {x.x, x.y, x.z - rad};
+    const V3 vp = lin(v) + cross(ang(v), c.r);
+    const float vn = vp.z;
+    const float Gn = dt * M.k_c + (vn < 0.f ? M.d_c : 0.f);
+    const float fn0 = M.k_c * pen - Gn * vn;
+    if (!(fn0 > 0.f)) return false;
+    const float vt = sqrtf(vp.x * vp.x + vp.y * vp.y);
+    const float ct = fminf(M.c_visc, M.mu * fn0 / (vt + 1e-6f));
+    c.C = {dt * ct, dt * ct, dt * Gn};
+    const V3 ab = lin(b) + cross(ang(b), c.r);
+    c.F0 = {-ct * vp.x + c.C.x * ab.x, -ct * vp.y + c.C.y * ab.y, fn0 + c.C.z * ab.z};
+    return true;
+}
+
+struct K2Args {
+    float* pos; float* quat; float* vel; float* q; float* qd; float* sens;
+    const float* actions;
+    long long n;
+    int substeps;
+    float dt;
+};
+
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_constant__ OigeTaskParams P,
+                         const __grid_constant__ K2Args A) {
+    __shared__ __align__(16) DevModel M;
+    {
+        const int4* src = reinterpret_cast<const int4*>(gmodel);
+        int4* dst = reinterpret_cast<int4*>(&M);
+        for (int i = threadIdx.x; i < (int)(sizeof(DevModel) / 16); i += blockDim.x) dst[i] = src[i];
+    }
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31;
+    const long long env = (long long)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
+    if (env >= A.n) return;  // warp-uniform
+
+    const int L = M.num_links;
+    const bool active = lane < L;
+    const int li = active ? lane : 0;  // clamp so table reads stay in range
+    const int level = active ? M.level[li] : -1;
+    const int parent = active && lane > 0 ? M.parent[li] : lane;
+    const int dofi = active ? M.dof[li] : -1;
+    const bool is_joint = active && lane > 0;
+    const float dt = A.dt;
+    const int D = P.num_dof;
+
+    // ---- load state -------------------------------------------------------------------------
+    float q = 0.f, qd = 0.f, effort = 0.f;
+    if (is_joint) {
+        q = A.q[env * D + dofi];
+        qd = A.qd[env * D + dofi];
+        effort = A.actions[env * D + dofi] * P.joint_gears[dofi] * P.power_scale;  // locomotion.py:109
+    }
+    V3 rpos = {0.f, 0.f, 0.f};
+    Q4 rquat = {1.f, 0.f, 0.f, 0.f};
+    V6 rvel = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};  // (ang, lin)
+    if (lane == 0) {
+        rpos = {A.pos[env * 3], A.pos[env * 3 + 1], A.pos[env * 3 + 2]};
+        const float4 t = *reinterpret_cast<const float4*>(A.quat + env * 4);
+        rquat = {t.x, t.y, t.z, t.w};
+        const float* vv = A.vel + env * 6;
+        rvel = {{vv[3], vv[4], vv[5], vv[0], vv[1], vv[2]}};
+    }
+
+    // per-lane constants
+    const V3 jpos = {M.jpos[0][li], M.jpos[1][li], M.jpos[2][li]};
+    const Q4 jquat = {M.jquat[0][li], M.jquat[1][li], M.jquat[2][li], M.jquat[3][li]};
+    const V3 axis = {M.axis[0][li], M.axis[1][li], M.axis[2][li]};
+    const V3 grav = {M.gravity[0], M.gravity[1], M.gravity[2]};
+    const int max_depth = M.max_depth;
+
+    for (int step = 0; step < A.substeps; ++step) {
+        const bool last = (step == A.substeps - 1);
+        const float root_z = shfl(rpos.z, 0);
+
+        // ---- pass 1: kinematics, top-down -----------------------------------------------------
+        Q4 quat = rquat;
+        V3 p = {0.f, 0.f, 0.f};
+        V6 v = rvel;
+        V6 b = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
+        V6 s = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
+        V6 c = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
+        if (lane == 0) {
+            const V3 wxv = cross(ang(rvel), lin(rvel));
+            b = {{0.f, 0.f, 0.f, -wxv.x, -wxv.y, -wxv.z}};
+        }
+        Q4 ql = {1.f, 0.f, 0.f, 0.f};
+        if (is_joint) {
+            float sh, ch;
+            sincosf(0.5f * q, &sh, &ch);
+            ql = qmul(jquat, Q4{ch, sh * axis.x, sh * axis.y, sh * axis.z});
+        }
+        for (int l = 1; l <= max_depth; ++l) {
+            const bool mine = (level == l);
+            const int src = mine ? parent : lane;
+            const Q4 pq = {shfl(quat.w, src), shfl(quat.x, src), shfl(quat.y, src), shfl(quat.z, src)};
+            const V3 pp = {shfl(p.x, src), shfl(p.y, src), shfl(p.z, src)};
+            V6 pv, pb;
+#pragma unroll
+            for (int k = 0; k < 6; ++k) {
+                pv.a[k] = shfl(v.a[k], src);
+                pb.a[k] = shfl(b.a[k], src);
+            }
+            if (mine) {
+                const M3 Rp = qmat(pq);
+                p = pp + mulv(Rp, jpos);
+                quat = qmul(pq, ql);
+                const M3 Ri = qmat(quat);
+                const V3 aw = mulv(Ri, axis);
+                s = mk6(aw, cross(p, aw));
+#pragma unroll
+                for (int k = 0; k < 6; ++k) v.a[k] = fmaf(s.a[k], qd, pv.a[k]);
+                const V3 w = ang(v), vl = lin(v);
+                const V3 ca = cross(w, aw);
+                const V3 cl = cross(w, lin(s)) + cross(vl, aw);
+                c = mk6(qd * ca, qd * cl);
+#pragma unroll
+                for (int k = 0; k < 6; ++k) b.a[k] = pb.a[k] + c.a[k];
+            }
+        }
+
+        // ---- per-link spatial inertia, bias force, contacts (all lanes in parallel) -------------
+        const M3 R = qmat(quat);
+        S6 IA;
+        V6 pA;
+        {
+            const float m = active ? M.mass[li] : 0.f;
+            const V3 cl = {M.com[0][li], M.com[1][li], M.com[2][li]};
+            const V3 cw = p + mulv(R, cl);
+            // Ic_world = R diag/sym(I) R^T
+            const float ixx = M.inertia[0][li], iyy = M.inertia[1][li], izz = M.inertia[2][li];
+            const float ixy = M.inertia[3][li], ixz = M.inertia[4][li], iyz = M.inertia[5][li];
+            float T[9];  // T = R * Iloc
+#pragma unroll
+            for (int r = 0; r < 3; ++r) {
+                const float r0 = R.m[3 * r], r1 = R.m[3 * r + 1], r2 = R.m[3 * r + 2];
+                T[3 * r + 0] = r0 * ixx + r1 * ixy + r2 * ixz;
+                T[3 * r + 1] = r0 * ixy + r1 * iyy + r2 * iyz;
+                T[3 * r + 2] = r0 * ixz + r1 * iyz + r2 * izz;
+            }
+            const float cc = dot(cw, cw);
+            const float cv[3] = {cw.x, cw.y, cw.z};
+#pragma unroll
+            for (int i = 0; i < 3; ++i)
+#pragma unroll
+                for (int j = i; j < 3; ++j) {
+                    float icw = T[3 * i] * R.m[3 * j] + T[3 * i + 1] * R.m[3 * j + 1] + T[3 * i + 2] * R.m[3 * j + 2];
+                    icw += m * ((i == j ? cc : 0.f) - cv[i] * cv[j]);
+                    IA.a[sidx(i, j)] = active ? icw : 0.f;
+                }
+            // ang-lin block m*[c]x, lin-lin block m*1
+            IA.a[sidx(0, 3)] = 0.f;         IA.a[sidx(0, 4)] = -m * cw.z;  IA.a[sidx(0, 5)] = m * cw.y;
+            IA.a[sidx(1, 3)] = m * cw.z;    IA.a[sidx(1, 4)] = 0.f;        IA.a[sidx(1, 5)] = -m * cw.x;
+            IA.a[sidx(2, 3)] = -m * cw.y;   IA.a[sidx(2, 4)] = m * cw.x;   IA.a[sidx(2, 5)] = 0.f;
+            IA.a[sidx(3, 3)] = m; IA.a[sidx(3, 4)] = 0.f; IA.a[sidx(3, 5)] = 0.f;
+            IA.a[sidx(4, 4)] = m; IA.a[sidx(4, 5)] = 0.f;
+            IA.a[sidx(5, 5)] = m;
+            // bias: v x* (I v) - gravity wrench
+            const V6 h = s6mul(IA, v);
+            const V3 w = ang(v), vl = lin(v);
+            const V3 ba = cross(w, ang(h)) + cross(vl, lin(h));
+            const V3 bl = cross(w, lin(h));
+            const V3 fg = m * grav;
+            const V3 tg = cross(cw, fg);
+            pA = mk6(ba - tg, bl - fg);
+        }
+        {
+            const int s0 = active ? M.sph_start[li] : 0;
+            const int sc = active ? M.sph_count[li] : 0;
+            for (int k = 0; k < M.max_sph_per_link; ++k) {
+                Contact ct;
+                if (k < sc && contact_eval(M, s0 + k, R, p, v, b, root_z, dt, ct)) {
+                    const V3 tq = cross(ct.r, ct.F0);
+                    pA.a[0] -= tq.x; pA.a[1] -= tq.y; pA.a[2] -= tq.z;
+                    pA.a[3] -= ct.F0.x; pA.a[4] -= ct.F0.y; pA.a[5] -= ct.F0.z;
+                    // I += sum_k C_k u_k u_k^T with u_k = (r x e_k, e_k)
+                    const float Cd[3] = {ct.C.x, ct.C.y, ct.C.z};
+                    const float u[3][3] = {{0.f, ct.r.z, -ct.r.y}, {-ct.r.z, 0.f, ct.r.x}, {ct.r.y, -ct.r.x, 0.f}};
+#pragma unroll
+                    for (int e = 0; e < 3; ++e) {
+#pragma unroll
+                        for (int i = 0; i < 3; ++i) {
+#pragma unroll
+                            for (int j = i; j < 3; ++j) IA.a[sidx(i, j)] = fmaf(Cd[e] * u[e][i], u[e][j], IA.a[sidx(i, j)]);
+                            IA.a[sidx(i, 3 + e)] = fmaf(Cd[e], u[e][i], IA.a[sidx(i, 3 + e)]);
+                        }
+                        IA.a[sidx(3 + e, 3 + e)] += Cd[e];
+                    }
+                }
+            }
+        }
+
+        // ---- joint-space force and implicit diagonal ----------------------------------------------
+        float tau0 = 0.f, dextra = 1.f;
+        if (is_joint) {
+            const float Ks = M.stiffness[li], Dj = M.damping[li];
+            const float qn = fmaf(dt, qd, q);  // position the springs see at the end of the step
+            float Kimp = Ks, Dimp = Dj;
+            tau0 = effort - Ks * (qn - M.sref[li]) - Dj * qd;
+            const float lo = M.lo[li], hi = M.hi[li];
+            if (q < lo) {
+                tau0 += -M.k_lim * (qn - lo) - M.d_lim * qd;
+                Kimp += M.k_lim; Dimp += M.d_lim;
+            } else if (q > hi) {
+                tau0 += -M.k_lim * (qn - hi) - M.d_lim * qd;
+                Kimp += M.k_lim; Dimp += M.d_lim;
+            }
+            dextra = M.armature[li] + dt * (Dimp + dt * Kimp);
+        }
+
+        // ---- pass 2: articulated inertia, bottom-up -------------------------------------------------
+        V6 U = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
+        float dinv = 0.f, u = 0.f;
+        for (int l = max_depth; l >= 1; --l) {
+            if (level == l) {
+                U = s6mul(IA, s);
+                const float d = dot6(s, U) + dextra;
+                dinv = 1.f / d;
+                u = tau0 - dot6(s, pA);
+                // I^a = I^A - U U^T / d   (in place)
+#pragma unroll
+                for (int i = 0; i < 6; ++i) {
+                    const float ui = U.a[i] * dinv;
+#pragma unroll
+                    for (int j = i; j < 6; ++j) IA.a[sidx(i, j)] = fmaf(-ui, U.a[j], IA.a[sidx(i, j)]);
+                }
+                // p^a = p^A + I^a c + U u / d
+                const V6 Iac = s6mul(IA, c);
+                const float ud = u * dinv;
+#pragma unroll
+                for (int i = 0; i < 6; ++i) pA.a[i] = pA.a[i] + Iac.a[i] + U.a[i] * ud;
+            }
+            const int nch = M.maxch_at_level[l - 1];
+            for (int k = 0; k < nch; ++k) {
+                const int ch = (level == l - 1) ? M.child[k][li] : -1;
+                const bool valid = ch >= 0;
+                const int src = valid ? ch : lane;
+#pragma unroll
+                for (int j = 0; j < 21; ++j) {
+                    const float t = shfl(IA.a[j], src);
+                    if (valid) IA.a[j] += t;
+                }
+#pragma unroll
+                for (int j = 0; j < 6; ++j) {
+                    const float t = shfl(pA.a[j], src);
+                    if (valid) pA.a[j] += t;
+                }
+            }
+        }
+
+        // ---- root: solve I^A a = -p^A (6x6 Cholesky, lane 0) ----------------------------------------
+        V6 a = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
+        if (lane == 0) {
+            float Lm[6][6];
+#pragma unroll
+            for (int i = 0; i < 6; ++i)
+#pragma unroll
+                for (int j = 0; j <= i; ++j) Lm[i][j] = IA.a[sidx(j, i)];
+            float invd[6];
+#pragma unroll
+            for (int j = 0; j < 6; ++j) {
+                float dj = Lm[j][j];
+#pragma unroll
+                for (int k = 0; k < j; ++k) dj = fmaf(-Lm[j][k], Lm[j][k], dj);
+                const float ljj = sqrtf(dj);
+                invd[j] = 1.f / ljj;
+                Lm[j][j] = ljj;
+#pragma unroll
+                for (int i = j + 1; i < 6; ++i) {
+                    float t = Lm[i][j];
+#pragma unroll
+                    for (int k = 0; k < j; ++k) t = fmaf(-Lm[i][k], Lm[j][k], t);
+                    Lm[i][j] = t * invd[j];
+                }
+            }
+            float y[6];
+#pragma unroll
+            for (int i = 0; i < 6; ++i) {
+                float t = -pA.a[i];
+#pragma unroll
+                for (int k = 0; k < i; ++k) t = fmaf(-Lm[i][k], y[k], t);
+                y[i] = t * invd[i];
+            }
+#pragma unroll
+            for (int i = 5; i >= 0; --i) {
+                float t = y[i];
+#pragma unroll
+                for (int k = i + 1; k < 6; ++k) t = fmaf(-Lm[k][i], a.a[k], t);
+                a.a[i] = t * invd[i];
+            }
+        }
+
+        // ---- pass 3: accelerations, top-down -----------------------------------------------------------
+        float qdd = 0.f;
+        for (int l = 1; l <= max_depth; ++l) {
+            const bool mine = (level == l);
+            const int src = mine ? parent : lane;
+            V6 pa;
+#pragma unroll
+            for (int k = 0; k < 6; ++k) pa.a[k] = shfl(a.a[k], src);
+            if (mine) {
+#pragma unroll
+                for (int k = 0; k < 6; ++k) pa.a[k] += c.a[k];
+                qdd = (u - dot6(U, pa)) * dinv;
+#pragma unroll
+                for (int k = 0; k < 6; ++k) a.a[k] = fmaf(s.a[k], qdd, pa.a[k]);
+            }
+        }
+
+        // ---- foot force sensors: net ground wrench on the sensor link, in the link frame ----------------
+        if (last && A.sens != nullptr) {
+            const int sidx_ = active ? M.sensor_of_link[li] : -1;
+            if (sidx_ >= 0) {
+                V3 F = {0.f, 0.f, 0.f}, Tq = {0.f, 0.f, 0.f};
+                const int s0 = M.sph_start[li], sc = M.sph_count[li];
+                for (int k = 0; k < sc; ++k) {
+                    Contact ct;
+                    if (contact_eval(M, s0 + k, R, p, v, b, root_z, dt, ct)) {
+                        const V3 ap = lin(a) + cross(ang(a), ct.r);
+                        const V3 f = {ct.F0.x - ct.C.x * ap.x, ct.F0.y - ct.C.y * ap.y, ct.F0.z - ct.C.z * ap.z};
+                        F = F + f;
+                        Tq = Tq + cross(ct.r - p, f);
+                    }
+                }
+                const V3 Fl = mulTv(R, F), Tl = mulTv(R, Tq);
+                float* o = A.sens + (env * M.num_sensors + sidx_) * 6;
+                o[0] = Fl.x; o[1] = Fl.y; o[2] = Fl.z; o[3] = Tl.x; o[4] = Tl.y; o[5] = Tl.z;
+            }
+        }
+
+        // ---- integrate (semi-implicit Euler) ----------------------------------------------------------------
+        if (is_joint) {
+            qd = fmaf(dt, qdd, qd);
+            qd = fminf(fmaxf(qd, -M.max_qd), M.max_qd);
+            q = fmaf(dt, qd, q);
+        }
+        if (lane == 0) {
+            const V3 w0 = ang(rvel), v0 = lin(rvel);
+            const V3 vdot = lin(a) + cross(w0, v0);  // classical acceleration of the root origin
+            float damp = 1.f - dt * M.ang_damp;
+            damp = damp < 0.f ? 0.f : damp;
+            const V3 w1 = damp * (w0 + dt * ang(a));
+            const V3 v1 = v0 + dt * vdot;
+            rvel = mk6(w1, v1);
+            rpos = rpos + dt * v1;
+            const float wn = sqrtf(dot(w1, w1));
+            const float th = 0.5f * dt * wn;
+            float sh, ch;
+            sincosf(th, &sh, &ch);
+            const float k = wn > 1e-9f ? sh / wn : 0.5f * dt;
+            Q4 dq = {ch, k * w1.x, k * w1.y, k * w1.z};
+            Q4 nq = qmul(dq, rquat);
+            const float inv = rsqrtf(nq.w * nq.w + nq.x * nq.x + nq.y * nq.y + nq.z * nq.z);
+            rquat = {nq.w * inv, nq.x * inv, nq.y * inv, nq.z * inv};
+        }
+    }
+
+    // ---- non-finite guard: park the env below the termination height so K1 flags it for reset ----
+    bool bad = false;
+    if (is_joint) bad = !(isfinite(q) && isfinite(qd));
+    if (lane == 0) {
+        bad = !(isfinite(rpos.x) && isfinite(rpos.y) && isfinite(rpos.z) && isfinite(rquat.w) && isfinite(rquat.x) &&
+                isfinite(rquat.y) && isfinite(rquat.z));
+#pragma unroll
+        for (int k = 0; k < 6; ++k) bad = bad || !isfinite(rvel.a[k]);
+    }
+    if (__any_sync(0xffffffffu, bad)) {
+        q = 0.f; qd = 0.f;
+        rpos = {0.f, 0.f, -1.f};
+        rquat = {1.f, 0.f, 0.f, 0.f};
+        rvel = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
+        if (A.sens != nullptr && lane < M.num_sensors * 6) A.sens[env * M.num_sensors * 6 + lane] = 0.f;
+    }
+
+    // ---- store state ---------------------------------------------------------------------------------------
+    if (is_joint) {
+        A.q[env * D + dofi] = q;
+        A.qd[env * D + dofi] = qd;
+    }
+    if (lane == 0) {
+        A.pos[env * 3] = rpos.x; A.pos[env * 3 + 1] = rpos.y; A.pos[env * 3 + 2] = rpos.z;
+        *reinterpret_cast<float4*>(A.quat + env * 4) = make_float4(rquat.w, rquat.x, rquat.y, rquat.z);
+        float* vv = A.vel + env * 6;
+        vv[0] = rvel.a[3]; vv[1] = rvel.a[4]; vv[2] = rvel.a[5];
+        vv[3] = rvel.a[0]; vv[4] = rvel.a[1]; vv[5] = rvel.a[2];
+    }
+}
+
+__global__ void clamp_actions_kernel(const float* __restrict__ in, float* __restrict__ out, float clip, long long n) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        const float v = in[i];
+        out[i] = v < -clip ? -clip : (v > clip ? clip : v);  // torch.clamp (vec_env_rlgames.py:57)
+    }
+}
+
+}  // namespace
+
+int k2_clamp_actions(const float* in, float* out, float clip, int64_t count, cudaStream_t stream) {
+    if (!in || !out) return fail(OIGE_E_NULL, "clamp_actions: null pointer");
+    const unsigned blocks = (unsigned)((count + 255) / 256);
+    clamp_actions_kernel<<<blocks, 256, 0, stream>>>(in, out, clip, count);
+    count_launch();
+    return check_launch("clamp_actions_kernel");
+}
+
+int k2_step(const OigeModel* model, const OigeTaskParams* P, const OigeState* st, const float* actions, int64_t n,
+            int32_t substeps, float dt, cudaStream_t stream) {
+    if (P->num_dof != model->num_dof)
+        return fail(OIGE_E_SHAPE, "articulation_step: params.num_dof %d != model dofs %d", P->num_dof, model->num_dof);
+    K2Args A;
+    A.pos = st->root_pos; A.quat = st->root_quat; A.vel = st->root_vel; A.q = st->dof_pos; A.qd = st->dof_vel;
+    A.sens = st->sensors; A.actions = actions; A.n = n; A.substeps = substeps; A.dt = dt;
+    if (!A.pos || !A.quat || !A.vel || !A.q || !A.qd) return fail(OIGE_E_NULL, "articulation_step: null state pointer");
+    if (reinterpret_cast<uintptr_t>(A.quat) & 15u) return fail(OIGE_E_ALIGN, "articulation_step: root_quat not 16B aligned");
+    if (model->num_sensors > 0 && P->num_sensors != model->num_sensors)
+        return fail(OIGE_E_SHAPE, "articulation_step: params.num_sensors %d != model %d", P->num_sensors, model->num_sensors);
+    const unsigned blocks = (unsigned)((n + kWarpsPerBlock - 1) / kWarpsPerBlock);
+    articulation_step_kernel<<<blocks, kWarpsPerBlock * 32, 0, stream>>>(
+        reinterpret_cast<const DevModel*>(model->dev_table), *P, A);
+    count_launch();
+    return check_launch("articulation_step_kernel");
+}
+
+OigeModel* k2_model_create(const OigeModelDesc* d) {
+    const int L = d->num_links;
+    if (L < 1 || L > OIGE_MAX_LINKS || d->num_spheres < 0 || d->num_spheres > OIGE_MAX_SPHERES ||
+        d->num_sensors < 0 || d->num_sensors > OIGE_MAX_SENSORS) {
+        set_error("oige_model_create: counts out of range (links %d spheres %d sensors %d)", L, d->num_spheres,
+                  d->num_sensors);
+        return nullptr;
+    }
+    DevModel* h = new DevModel();
+    memset(h, 0, sizeof(DevModel));
+    h->num_links = L; h->num_spheres = d->num_spheres; h->num_sensors = d->num_sensors;
+    for (int k = 0; k < kMaxChildren; ++k)
+        for (int i = 0; i < 32; ++i) h->child[k][i] = -1;
+    int nchild[32] = {0};
+    bool ok = d->parent[0] == -1;
+    for (int i = 0; i < L && ok; ++i) {
+        h->parent[i] = d->parent[i];
+        h->dof[i] = d->dof_index[i];
+        h->sensor_of_link[i] = -1;
+        if (i == 0) { h->level[0] = 0; continue; }
+        const int p = d->parent[i];
+        if (p < 0 || p >= i) { ok = false; break; }
+        if (d->dof_index[i] < 0 || d->dof_index[i] >= L - 1) { ok = false; break; }
+        h->level[i] = h->level[p] + 1;
+        if (h->level[i] >= kMaxLevels || nchild[p] >= kMaxChildren) { ok = false; break; }
+        h->child[nchild[p]++][p] = i;
+        if (h->level[i] > h->max_depth) h->max_depth = h->level[i];
+    }
+    if (!ok) {
+        set_error("oige_model_create: malformed tree (need parent[0]=-1, parent[i]<i, <=%d children, depth<%d)",
+                  kMaxChildren, kMaxLevels);
+        delete h;
+        return nullptr;
+    }
+    for (int i = 0; i < L; ++i)
+        if (nchild[i] > h->maxch_at_level[h->level[i]]) h->maxch_at_level[h->level[i]] = nchild[i];
+    for (int i = 0; i < L; ++i) {
+        for (int k = 0; k < 3; ++k) { h->jpos[k][i] = d->joint_pos[i][k]; h->axis[k][i] = d->joint_axis[i][k]; h->com[k][i] = d->com[i][k]; }
+        for (int k = 0; k < 4; ++k) h->jquat[k][i] = d->joint_quat[i][k];
+        for (int k = 0; k < 6; ++k) h->inertia[k][i] = d->inertia[i][k];
+        h->mass[i] = d->mass[i]; h->armature[i] = d->armature[i]; h->damping[i] = d->damping[i];
+        h->stiffness[i] = d->stiffness[i]; h->sref[i] = d->spring_ref[i]; h->lo[i] = d->limit_lower[i]; h->hi[i] = d->limit_upper[i];
+    }
+    h->jquat[0][0] = 1.f;
+    // spheres sorted by link (stable)
+    int pos = 0;
+    for (int i = 0; i < L; ++i) {
+        h->sph_start[i] = pos;
+        for (int s = 0; s < d->num_spheres; ++s) {
+            if (d->sphere_link[s] != i) continue;
+            for (int k = 0; k < 3; ++k) h->sph_pos[k][pos] = d->sphere_pos[s][k];
+            h->sph_r[pos] = d->sphere_radius[s];
+            ++pos;
+        }
+        h->sph_count[i] = pos - h->sph_start[i];
+        if (h->sph_count[i] > h->max_sph_per_link) h->max_sph_per_link = h->sph_count[i];
+    }
+    if (pos != d->num_spheres) {
+        set_error("oige_model_create: sphere_link out of range");
+        delete h;
+        return nullptr;
+    }
+    for (int s = 0; s < d->num_sensors; ++s) {
+        if (d->sensor_link[s] < 0 || d->sensor_link[s] >= L) {
+            set_error("oige_model_create: sensor_link out of range");
+            delete h;
+            return nullptr;
+        }
+        h->sensor_of_link[d->sensor_link[s]] = s;
+    }
+    for (int k = 0; k < 3; ++k) h->gravity[k] = d->gravity[k];
+    h->k_c = d->contact_stiffness; h->d_c = d->contact_damping; h->mu = d->friction_mu; h->c_visc = d->friction_viscous;
+    h->k_lim = d->limit_stiffness; h->d_lim = d->limit_damping; h->max_qd = d->max_joint_velocity; h->ang_damp = d->angular_damping;
+
+    void* dev = nullptr;
+    cudaError_t e = cudaMalloc(&dev, sizeof(DevModel));
+    if (e == cudaSuccess) e = cudaMemcpy(dev, h, sizeof(DevModel), cudaMemcpyHostToDevice);
+    delete h;
+    if (e != cudaSuccess) {
+        set_error("oige_model_create: %s", cudaGetErrorString(e));
+        if (dev) cudaFree(dev);
+        return nullptr;
+    }
+    OigeModel* m = new OigeModel();
+    m->dev_table = dev; m->num_links = L; m->num_dof = L - 1; m->num_sensors = d->num_sensors;
+    return m;
+}
+
+void k2_model_destroy(OigeModel* m) {
+    if (m->dev_table) cudaFree(m->dev_table);
+    delete m;
+}
+
+}  // namespace oige

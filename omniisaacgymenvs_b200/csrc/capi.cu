@@ -1,0 +1,178 @@
+// C ABI of liboige_b200.so (declared in include/oige_b200.h).  Thin argument checking + dispatch;
+// the kernels live in obs_reward_reset.cu (K1), articulation_step.cu (K2), reset_idx.cu (K3).
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include "oige_common.cuh"
+
+namespace oige {
+
+static thread_local char g_err[512] = "";
+static std::atomic<uint64_t> g_launches{0};
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+int check_launch(const char* what) {
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) return OIGE_OK;
+    set_error("%s: %s", what, cudaGetErrorString(e));
+    return (int)e;
+}
+
+void count_launch(uint64_t n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+int sm_count() {
+    static int cached = -1;
+    if (cached < 0) {
+        int dev = 0, n = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess ||
+            cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+            return 148;
+        cached = n;
+    }
+    return cached;
+}
+
+// kernels' host-side dispatchers
+int k1_dispatch(const OigeTaskParams*, const OigeState*, const OigeTaskBuffers*, int64_t, cudaStream_t, int);
+int k3_masked(const OigeTaskParams*, const OigeState*, const OigeTaskBuffers*, const OigeResetInit*, const float*,
+              const float*, uint64_t, uint64_t, int64_t, int64_t, cudaStream_t);
+int k3_idx(const OigeTaskParams*, const OigeState*, const OigeTaskBuffers*, const OigeResetInit*, const int64_t*,
+           int64_t, const float*, const float*, uint64_t, uint64_t, int64_t, cudaStream_t);
+int k2_step(const OigeModel*, const OigeTaskParams*, const OigeState*, const float*, int64_t, int32_t, float,
+            cudaStream_t);
+int k2_clamp_actions(const float* in, float* out, float clip, int64_t count, cudaStream_t);
+OigeModel* k2_model_create(const OigeModelDesc*);
+void k2_model_destroy(OigeModel*);
+
+static int check_common(const char* who, const OigeTaskParams* p, const OigeState* s, const OigeTaskBuffers* b,
+                        int64_t n) {
+    if (!p || !s || !b) return fail(OIGE_E_NULL, "%s: null struct pointer", who);
+    if (n < 0 || n > (int64_t)1 << 31) return fail(OIGE_E_RANGE, "%s: n_envs %lld out of range", who, (long long)n);
+    if (p->num_dof < 1 || p->num_dof > OIGE_MAX_DOF) return fail(OIGE_E_SHAPE, "%s: num_dof %d", who, p->num_dof);
+    return OIGE_OK;
+}
+
+}  // namespace oige
+
+using namespace oige;
+
+extern "C" {
+
+int oige_abi_version(void) { return OIGE_ABI_VERSION; }
+const char* oige_last_error(void) { return g_err; }
+uint64_t oige_kernel_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int oige_obs_reward_reset_f32(const OigeTaskParams* params, const OigeState* state, const OigeTaskBuffers* buf,
+                              int64_t n_envs, void* stream) {
+    if (int rc = check_common("oige_obs_reward_reset_f32", params, state, buf, n_envs)) return rc;
+    if (n_envs == 0) return OIGE_OK;
+    return k1_dispatch(params, state, buf, n_envs, (cudaStream_t)stream, 0);
+}
+
+// same as above with an explicit tile size (32/64/128) -- used by the benchmark's tile sweep
+int oige_obs_reward_reset_tile_f32(const OigeTaskParams* params, const OigeState* state, const OigeTaskBuffers* buf,
+                                   int64_t n_envs, int32_t tile, void* stream) {
+    if (int rc = check_common("oige_obs_reward_reset_tile_f32", params, state, buf, n_envs)) return rc;
+    if (n_envs == 0) return OIGE_OK;
+    return k1_dispatch(params, state, buf, n_envs, (cudaStream_t)stream, tile);
+}
+
+int oige_reset_masked_f32(const OigeTaskParams* params, const OigeState* state, const OigeTaskBuffers* buf,
+                          const OigeResetInit* init, const float* rand_pos, const float* rand_vel, uint64_t seed,
+                          uint64_t counter, int64_t env_id_offset, int64_t n_envs, void* stream) {
+    if (int rc = check_common("oige_reset_masked_f32", params, state, buf, n_envs)) return rc;
+    if (n_envs == 0) return OIGE_OK;
+    return k3_masked(params, state, buf, init, rand_pos, rand_vel, seed, counter, env_id_offset, n_envs,
+                     (cudaStream_t)stream);
+}
+
+int oige_reset_idx_f32(const OigeTaskParams* params, const OigeState* state, const OigeTaskBuffers* buf,
+                       const OigeResetInit* init, const int64_t* env_ids, int64_t k, const float* rand_pos,
+                       const float* rand_vel, uint64_t seed, uint64_t counter, int64_t env_id_offset, void* stream) {
+    if (int rc = check_common("oige_reset_idx_f32", params, state, buf, k)) return rc;
+    if (k == 0) return OIGE_OK;
+    return k3_idx(params, state, buf, init, env_ids, k, rand_pos, rand_vel, seed, counter, env_id_offset,
+                  (cudaStream_t)stream);
+}
+
+OigeModel* oige_model_create(const OigeModelDesc* desc) {
+    if (!desc) {
+        set_error("oige_model_create: null desc");
+        return nullptr;
+    }
+    return k2_model_create(desc);
+}
+
+void oige_model_destroy(OigeModel* model) {
+    if (model) k2_model_destroy(model);
+}
+
+int oige_articulation_step_f32(const OigeModel* model, const OigeTaskParams* params, const OigeState* state,
+                               const float* actions, int64_t n_envs, int32_t substeps, float dt, void* stream) {
+    if (!model || !params || !state || !actions) return fail(OIGE_E_NULL, "oige_articulation_step_f32: null argument");
+    if (n_envs < 0 || n_envs > (int64_t)1 << 26) return fail(OIGE_E_RANGE, "n_envs %lld", (long long)n_envs);
+    if (substeps < 1 || substeps > 64) return fail(OIGE_E_RANGE, "substeps %d not in [1,64]", substeps);
+    if (!(dt > 0.0f)) return fail(OIGE_E_RANGE, "dt must be > 0");
+    if (n_envs == 0) return OIGE_OK;
+    return k2_step(model, params, state, actions, n_envs, substeps, dt, (cudaStream_t)stream);
+}
+
+int oige_env_step_f32(const OigeModel* model, const OigeTaskParams* params, const OigeState* state,
+                      const OigeTaskBuffers* buf, const OigeResetInit* init, const float* actions_in,
+                      float clip_actions, uint64_t seed, uint64_t counter, int64_t env_id_offset, int64_t n_envs,
+                      int32_t substeps, float dt, void* stream) {
+    if (int rc = check_common("oige_env_step_f32", params, state, buf, n_envs)) return rc;
+    if (!model || !init || !actions_in) return fail(OIGE_E_NULL, "oige_env_step_f32: null argument");
+    if (substeps < 1 || substeps > 64) return fail(OIGE_E_RANGE, "substeps %d not in [1,64]", substeps);
+    if (n_envs == 0) return OIGE_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    // VecEnvRLGames.step: clamp -> pre_physics_step (reset flagged envs, store actions, efforts)
+    //                     -> control_frequency_inv x world.step -> post_physics_step
+    if (int rc = k2_clamp_actions(actions_in, buf->actions, clip_actions, n_envs * params->num_dof, s)) return rc;
+    if (int rc = k3_masked(params, state, buf, init, nullptr, nullptr, seed, counter, env_id_offset, n_envs, s))
+        return rc;
+    if (int rc = k2_step(model, params, state, buf->actions, n_envs, substeps, dt, s)) return rc;
+    return k1_dispatch(params, state, buf, n_envs, s, 0);
+}
+
+int oige_env_step_host_f32(const OigeModel* model, const OigeTaskParams* params, const OigeState* state,
+                           const OigeTaskBuffers* buf, const OigeResetInit* init, const float* actions_host,
+                           float* actions_dev_staging, float* obs_host, float* rew_host, int64_t* reset_host,
+                           float clip_actions, uint64_t seed, uint64_t counter, int64_t env_id_offset,
+                           int64_t n_envs, int32_t substeps, float dt, void* stream) {
+    if (int rc = check_common("oige_env_step_host_f32", params, state, buf, n_envs)) return rc;
+    if (!actions_host || !actions_dev_staging || !obs_host || !rew_host || !reset_host)
+        return fail(OIGE_E_NULL, "oige_env_step_host_f32: null host/staging buffer");
+    cudaStream_t s = (cudaStream_t)stream;
+    const size_t na = (size_t)n_envs * params->num_dof * sizeof(float);
+    cudaError_t e = cudaMemcpyAsync(actions_dev_staging, actions_host, na, cudaMemcpyHostToDevice, s);
+    if (e != cudaSuccess) return fail((int)e, "H2D actions: %s", cudaGetErrorString(e));
+    if (int rc = oige_env_step_f32(model, params, state, buf, init, actions_dev_staging, clip_actions, seed, counter,
+                                   env_id_offset, n_envs, substeps, dt, stream))
+        return rc;
+    e = cudaMemcpyAsync(obs_host, buf->obs, (size_t)n_envs * params->num_obs * sizeof(float),
+                        cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(rew_host, buf->rew, (size_t)n_envs * sizeof(float), cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess)
+        e = cudaMemcpyAsync(reset_host, buf->reset_buf, (size_t)n_envs * sizeof(int64_t), cudaMemcpyDeviceToHost, s);
+    if (e != cudaSuccess) return fail((int)e, "D2H results: %s", cudaGetErrorString(e));
+    return OIGE_OK;
+}
+
+}  // extern "C"

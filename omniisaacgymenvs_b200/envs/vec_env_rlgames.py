@@ -1,0 +1,71 @@
+"""VecEnvRLGames -- the wrapper rl_games drives (reference: envs/vec_env_rlgames.py:36-89).
+
+Same surface (``set_task``, ``step``, ``reset``, ``num_states``, ``state_space``) and the same
+per-step order: clamp actions -> pre_physics_step -> control_frequency_inv x world.step ->
+post_physics_step -> clamp/copy to rl_device.  When the task is a stock locomotion task the whole
+sequence runs as ONE C-ABI call (`oige_env_step_f32`: K3 reset, K2 articulation, K1
+obs/reward/reset) with no host sync; any task that overrides the hooks takes the generic path.
+"""
+import ctypes as C
+from datetime import datetime
+
+import torch
+
+from omniisaacgymenvs_b200 import _lib
+from omniisaacgymenvs_b200.envs.vec_env_base import VecEnvBase
+
+
+class VecEnvRLGames(VecEnvBase):
+    def _process_data(self):
+        # vec_env_rlgames.py:41-46.  The obs clamp already happened inside K1 (clip_obs is a kernel
+        # parameter); what is left are the hand-off copies to rl_device.
+        dev = self._task.rl_device
+        self._obs = self._obs.to(dev).clone()
+        self._rew = self._rew.to(dev).clone()
+        self._states = torch.clamp(self._states, -self._task.clip_obs, self._task.clip_obs).to(dev).clone()
+        self._resets = self._resets.to(dev).clone()
+        self._extras = self._extras.copy()
+
+    def set_task(self, task, backend="numpy", sim_params=None, init_sim=True) -> None:
+        super().set_task(task, backend, sim_params, init_sim)
+        self.num_states = self._task.num_states
+        self.state_space = self._task.state_space
+
+    def step(self, actions):
+        task = self._task
+        if task.randomize_actions or task.randomize_observations:
+            raise RuntimeError("domain randomisation is not part of this build (SURVEY.md section 8(f) N3)")
+        if getattr(task, "supports_fused_step", False) and task.fused_step_enabled():
+            actions = actions.to(task.device)
+            task.fused_step(actions, self._world.get_physics_dt())
+            self.sim_frame_count += task.control_frequency_inv
+            self._world.current_time_step_index += task.control_frequency_inv
+            self._obs, self._rew, self._resets, self._extras = task.obs_buf, task.rew_buf, task.reset_buf, task.extras
+        else:
+            actions = torch.clamp(actions, -task.clip_actions, task.clip_actions).to(task.device).clone()
+            task.pre_physics_step(actions)
+            for _ in range(task.control_frequency_inv):
+                self._world.step(render=self._render)
+                self.sim_frame_count += 1
+            self._obs, self._rew, self._resets, self._extras = task.post_physics_step()
+        self._states = task.get_states()
+        self._process_data()
+        obs_dict = {"obs": self._obs, "states": self._states}
+        return obs_dict, self._rew, self._resets, self._extras
+
+    def reset(self):
+        """Flags every env for reset and steps once with zero actions (vec_env_rlgames.py:80-89)."""
+        now = datetime.now().strftime("%Y-%m-%d %H:%M:%S")
+        print(f"[{now}] Running RL reset")
+        self._task.reset()
+        actions = torch.zeros((self.num_envs, self._task.num_actions), device=self._task.device)
+        obs_dict, _, _, _ = self.step(actions)
+        return obs_dict
+
+    # ---- host-buffer entry point (what a CPU-side trainer would call) -------------------------
+    def step_host(self, actions_host: torch.Tensor, obs_host: torch.Tensor, rew_host: torch.Tensor,
+                  reset_host: torch.Tensor) -> None:
+        """Whole step with HOST (ideally pinned) buffers through `oige_env_step_host_f32`:
+        H2D actions, K3+K2+K1, D2H obs/rew/resets, all asynchronous on the current stream."""
+        self._task.fused_step_host(actions_host, obs_host, rew_host, reset_host, self._world.get_physics_dt())
+        self.sim_frame_count += self._task.control_frequency_inv

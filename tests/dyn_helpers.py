@@ -1,0 +1,86 @@
+"""Helpers for the K2 (articulation step) parity tests: run the CUDA kernel through the C ABI and
+the float64 CPU oracle on the same state."""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from omniisaacgymenvs_b200 import _lib
+from omniisaacgymenvs_b200.robots.model import build_model, fill_desc
+from oracle import dynamics as dyn
+from oracle import locomotion_oracle as lo
+
+
+def random_state(model, n, seed, height=None, qd_scale=1.0, root_vel_scale=0.5, tilt=0.3):
+    """Random but physically sane state: joints inside their limits, moderate velocities."""
+    rng = np.random.default_rng(seed)
+    lim = model.dof_limits().astype(np.float64)
+    D = model.num_dof
+    q = lim[:, 0] + (0.15 + 0.7 * rng.random((n, D))) * (lim[:, 1] - lim[:, 0])
+    qd = qd_scale * rng.normal(size=(n, D))
+    pos = np.zeros((n, 3))
+    pos[:, :2] = rng.normal(size=(n, 2)) * 3.0
+    pos[:, 2] = height if height is not None else model.spawn_height
+    axis = rng.normal(size=(n, 3))
+    axis /= np.linalg.norm(axis, axis=1, keepdims=True)
+    ang = tilt * rng.normal(size=(n, 1))
+    quat = np.concatenate([np.cos(ang / 2), np.sin(ang / 2) * axis], axis=1)
+    vel = root_vel_scale * rng.normal(size=(n, 6))
+    actions = rng.uniform(-1, 1, size=(n, D))
+    f32 = lambda a: np.ascontiguousarray(a.astype(np.float32))
+    return {"pos": f32(pos), "quat": f32(quat), "vel": f32(vel), "q": f32(q), "qd": f32(qd), "actions": f32(actions)}
+
+
+def unit_params(model, spec):
+    p = _lib.OigeTaskParams()
+    p.num_dof, p.num_sensors = model.num_dof, model.num_sensors
+    p.num_obs = 12 + 3 * model.num_dof + 6 * model.num_sensors
+    p.power_scale = spec.power_scale
+    for k in range(model.num_dof):
+        p.joint_gears[k] = float(model.joint_gears[k])
+    return p
+
+
+def run_gpu(cuda_lib, model, spec, st, substeps, dt, device="cuda:0", calls=1):
+    dev = torch.device(device)
+    desc = _lib.OigeModelDesc()
+    fill_desc(model, desc)
+    with torch.cuda.device(dev):
+        handle = cuda_lib.oige_model_create(C.byref(desc))
+    assert handle, cuda_lib.oige_last_error()
+    t = {k: torch.from_numpy(v.copy()).to(dev) for k, v in st.items()}
+    n = st["pos"].shape[0]
+    sens = torch.zeros((n, model.num_sensors, 6), device=dev)
+    state = _lib.OigeState(t["pos"].data_ptr(), t["quat"].data_ptr(), t["vel"].data_ptr(), t["q"].data_ptr(),
+                           t["qd"].data_ptr(), sens.data_ptr())
+    p = unit_params(model, spec)
+    for _ in range(calls):
+        rc = cuda_lib.oige_articulation_step_f32(handle, C.byref(p), C.byref(state), t["actions"].data_ptr(), n,
+                                                 substeps, dt, _lib.current_stream_ptr(dev))
+        _lib.check(rc, "oige_articulation_step_f32")
+    torch.cuda.synchronize(dev)
+    cuda_lib.oige_model_destroy(handle)
+    out = {k: v.cpu().numpy().astype(np.float64) for k, v in t.items() if k != "actions"}
+    out["sensors"] = sens.cpu().numpy().astype(np.float64)
+    return out
+
+
+def run_oracle(model, spec, st, substeps, dt, calls=1, threads=8):
+    desc = dyn.make_desc(model)
+    d = {k: np.ascontiguousarray(v.astype(np.float64)) for k, v in st.items()}
+    gears = model.joint_gears.astype(np.float32)
+    # efforts formed in fp32 exactly as the kernel / reference do: (a * gear) * power_scale
+    eff = ((st["actions"] * gears).astype(np.float32) * np.float32(spec.power_scale)).astype(np.float64)
+    eff = np.ascontiguousarray(eff)
+    n = st["pos"].shape[0]
+    sens = np.zeros((n, model.num_sensors, 6))
+    for _ in range(calls):
+        bad = dyn.step(desc, d["pos"], d["quat"], d["vel"], d["q"], d["qd"], eff, sens, substeps, dt, threads)
+        assert bad == 0, f"oracle: {bad} envs with a non-SPD system"
+    out = {k: d[k] for k in ("pos", "quat", "vel", "q", "qd")}
+    out["sensors"] = sens
+    return out
+
+
+def specs(robot):
+    return build_model(robot), lo.SPECS[robot]

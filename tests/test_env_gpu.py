@@ -1,0 +1,178 @@
+"""GPU: the drop-in surface (VecEnvRLGames / RLTask / ArticulationView) end to end."""
+import numpy as np
+import pytest
+import torch
+
+import helpers
+from omniisaacgymenvs_b200.utils.task_util import make_env
+from oracle import locomotion_oracle as lo
+
+pytestmark = pytest.mark.gpu
+
+
+def _snapshot(task):
+    v = task.get_robot()
+    return {k: getattr(v, k).clone() for k in ("root_pos", "root_quat", "root_vel", "dof_pos", "dof_vel", "sensor_forces")}
+
+
+@pytest.mark.parametrize("robot,obs,act", [("Humanoid", 87, 21), ("Ant", 60, 8)])
+def test_env_surface_and_shapes(cuda_lib, robot, obs, act):
+    env, task = make_env(robot, num_envs=256)
+    assert env.num_envs == 256 and task.num_observations == obs and task.num_actions == act
+    assert env.observation_space.shape == (obs,) and env.action_space.shape == (act,)
+    assert env.num_states == 0 and env.get_number_of_agents() == 1
+    d = env.reset()
+    assert d["obs"].shape == (256, obs) and d["states"].shape == (256, 0)
+    o, r, done, info = env.step(torch.rand(256, act, device=task.device) * 2 - 1)
+    assert o["obs"].shape == (256, obs) and r.shape == (256,) and done.shape == (256,) and done.dtype == torch.int64
+    assert isinstance(info, dict) and torch.isfinite(o["obs"]).all() and torch.isfinite(r).all()
+    v = task.get_robot()
+    p, q = v.get_world_poses(clone=False)
+    assert p.shape == (256, 3) and q.shape == (256, 4) and v.get_velocities(clone=False).shape == (256, 6)
+    assert v.get_joint_positions(clone=False).shape == (256, act)
+    assert v._physics_view.get_force_sensor_forces().shape == (256, task._model.num_sensors, 6)
+    assert v.get_dof_limits().shape == (256, act, 2) and v.num_dof == act and v.count == 256
+    assert p.data_ptr() == v.root_pos.data_ptr(), "clone=False must hand out the live buffer"
+
+
+@pytest.mark.parametrize("robot", ["Humanoid", "Ant"])
+def test_fused_step_equals_hook_by_hook_path(cuda_lib, robot):
+    """oige_env_step_f32 (one call) vs pre_physics_step -> world.step x2 -> post_physics_step."""
+    n = 512
+    env_a, task_a = make_env(robot, num_envs=n, seed=3)
+    env_b, task_b = make_env(robot, num_envs=n, seed=3)
+    task_b.fused_step_enabled = lambda: False  # force the generic path
+    g = torch.Generator(device="cpu").manual_seed(0)
+    env_a.reset(); env_b.reset()
+    for step in range(40):
+        a = (torch.rand(n, task_a.num_actions, generator=g) * 2.4 - 1.2).to(task_a.device)  # exercises the clamp
+        oa, ra, da, _ = env_a.step(a)
+        ob, rb, db, _ = env_b.step(a)
+        assert torch.equal(oa["obs"], ob["obs"]), f"obs differ at step {step}"
+        assert torch.equal(ra, rb) and torch.equal(da, db)
+    sa, sb = _snapshot(task_a), _snapshot(task_b)
+    for k in sa:
+        assert torch.equal(sa[k], sb[k]), k
+    assert torch.equal(task_a.progress_buf, task_b.progress_buf)
+
+
+def test_individual_hooks_equal_fused_post_physics_step(cuda_lib):
+    n = 300
+    env_a, task_a = make_env("Humanoid", num_envs=n, seed=1)
+    env_b, task_b = make_env("Humanoid", num_envs=n, seed=1)
+    a = torch.rand(n, 21, device=task_a.device) * 2 - 1
+    for env, task in ((env_a, task_a), (env_b, task_b)):
+        task.pre_physics_step(a.clone())
+        env._world.step(); env._world.step()
+    task_a.post_physics_step()
+    # reference order, hook by hook (tasks/base/rl_task.py:242-249)
+    task_b.progress_buf[:] += 1
+    task_b.get_observations(); task_b.calculate_metrics(); task_b.is_done()
+    for k in ("obs_buf", "rew_buf", "reset_buf", "progress_buf", "potentials", "prev_potentials", "up_vec", "heading_vec"):
+        assert torch.equal(getattr(task_a, k), getattr(task_b, k)), k
+
+
+@pytest.mark.parametrize("robot", ["Humanoid", "Ant"])
+def test_post_physics_step_matches_oracle_on_live_state(cuda_lib, robot):
+    """After real physics steps, K1's outputs equal the oracle evaluated on the same state tensors."""
+    n = 1024
+    env, task = make_env(robot, num_envs=n, seed=5)
+    env.reset()
+    spec = lo.SPECS[robot]
+    for _ in range(10):
+        a = torch.rand(n, task.num_actions, device=task.device) * 2 - 1
+        pot_before = None
+        env.step(a)
+    v = task.get_robot()
+    # state going INTO the next post_physics_step: run physics by hand, then compare K1 vs oracle
+    a = torch.rand(n, task.num_actions, device=task.device) * 2 - 1
+    task.pre_physics_step(a)
+    env._world.step(); env._world.step()
+    s = {"pos": v.root_pos, "quat": v.root_quat, "vel": v.root_vel, "dof_pos": v.dof_pos, "dof_vel": v.dof_vel,
+         "sensors": v.sensor_forces, "actions": task.actions, "potentials": task.potentials,
+         "progress_buf": task.progress_buf, "reset_buf": task.reset_buf, "targets": task.targets,
+         "inv_start_rot": task.inv_start_rot, "basis_vec0": task.basis_vec0, "basis_vec1": task.basis_vec1,
+         "dof_lo": task.dof_limits_lower, "dof_hi": task.dof_limits_upper}
+    s = {k: t.detach().cpu().clone() for k, t in s.items()}
+    ref = lo.post_physics_step(spec, s)
+    task.post_physics_step()
+    got = {"obs": task.obs_buf, "rew": task.rew_buf, "reset_buf": task.reset_buf, "progress_buf": task.progress_buf,
+           "potentials": task.potentials, "prev_potentials": task.prev_potentials, "up_vec": task.up_vec,
+           "heading_vec": task.heading_vec}
+    got = {k: t.detach().cpu() for k, t in got.items()}
+    helpers.assert_k1_matches(got, ref, robot)
+
+
+def test_sharded_envs_equal_rows_of_the_unsharded_run(cuda_lib):
+    """env i of a G-way job must not depend on G.  Shard 1 of 2 (run alone on this
+    GPU) == rows [N/2, N) of the 1-way run, bit for bit, resets included."""
+    n = 512
+    env_full, task_full = make_env("Humanoid", num_envs=n, seed=11)
+    env_half, task_half = make_env("Humanoid", num_envs=n // 2, seed=11, env_id_offset=n // 2, global_num_envs=n)
+    assert torch.equal(task_full.initial_root_pos[n // 2:], task_half.initial_root_pos)
+    env_full.reset(); env_half.reset()
+    g = torch.Generator().manual_seed(2)
+    for step in range(60):
+        a = (torch.rand(n, 21, generator=g) * 2 - 1).to(task_full.device)
+        of, rf, df, _ = env_full.step(a)
+        oh, rh, dh_, _ = env_half.step(a[n // 2:].contiguous())
+        assert torch.equal(of["obs"][n // 2:], oh["obs"]), f"step {step}"
+        assert torch.equal(rf[n // 2:], rh) and torch.equal(df[n // 2:], dh_)
+    assert int(task_full.read_episode_stats(reset=False)[3]) == n * 61
+
+
+def test_resets_happen_and_episode_stats_accumulate(cuda_lib):
+    n = 2048
+    env, task = make_env("Humanoid", num_envs=n, seed=0, overrides={"task.env.episodeLength": 20})
+    env.reset()
+    task.read_episode_stats()
+    total_done = 0
+    for _ in range(50):
+        _, _, done, _ = env.step(torch.rand(n, 21, device=task.device) * 2 - 1)
+        total_done += int(done.sum())
+    st = task.read_episode_stats()
+    assert total_done > n  # every env times out at least twice in 50 steps of 20-step episodes
+    assert int(st[1]) == total_done and int(st[3]) == 50 * n
+    assert 1.0 <= float(st[2]) / float(st[1]) <= 20.0
+    assert int(task.progress_buf.max()) <= 20
+
+
+def test_humanoid_random_policy_falls_and_ant_stays_up(cuda_lib):
+    """Plausibility of the stand-in physics: a random-policy humanoid falls below 0.8 m within a few
+    hundred steps in most envs; a zero-action ant settles above its 0.31 m termination height."""
+    env, task = make_env("Humanoid", num_envs=1024, seed=0)
+    env.reset()
+    fell = torch.zeros(1024, dtype=torch.bool, device=task.device)
+    for _ in range(300):
+        _, _, done, _ = env.step(torch.rand(1024, 21, device=task.device) * 2 - 1)
+        fell |= (done != 0) & (task.progress_buf < 999)
+    assert float(fell.float().mean()) > 0.5
+    env, task = make_env("Ant", num_envs=256, seed=0)
+    env.reset()
+    for _ in range(200):
+        _, _, done, _ = env.step(torch.zeros(256, 8, device=task.device))
+    z = task.get_robot().root_pos[:, 2]
+    assert float(z.min()) > 0.31 and int(task.reset_buf.sum()) == 0
+
+
+def test_step_host_round_trip(cuda_lib):
+    n = 512
+    env_a, task_a = make_env("Humanoid", num_envs=n, seed=4)
+    env_b, task_b = make_env("Humanoid", num_envs=n, seed=4)
+    env_a.reset(); env_b.reset()
+    a = torch.rand(n, 21) * 2 - 1
+    ah = a.clone().pin_memory()
+    obs_h = torch.empty(n, 87).pin_memory()
+    rew_h = torch.empty(n).pin_memory()
+    rst_h = torch.empty(n, dtype=torch.int64).pin_memory()
+    env_a.step_host(ah, obs_h, rew_h, rst_h)
+    torch.cuda.synchronize()
+    o, r, d, _ = env_b.step(a.to(task_b.device))
+    assert torch.equal(obs_h, o["obs"].cpu()) and torch.equal(rew_h, r.cpu()) and torch.equal(rst_h, d.cpu())
+
+
+def test_cpu_tensors_are_rejected_not_silently_computed(cuda_lib):
+    env, task = make_env("Ant", num_envs=64)
+    env.reset()
+    with pytest.raises(RuntimeError):
+        task.reset_idx(torch.arange(4), rand_pos=torch.rand(4, 8), rand_vel=torch.rand(4, 8))
