@@ -286,7 +286,9 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize(device)
 
-    # ---- warm-up ----
+    # ---- warm-up (the clock sampler starts here so that short timed regions still see samples under load) ----
+    clocks = ClockSampler(local_rank)
+    clocks.__enter__()
     for _ in range(W):
         env.step(torch.rand(n, D, device=device, generator=gen) * 2 - 1)
     barrier()
@@ -295,19 +297,18 @@ def run_ours(args):
     launches0 = _lib.launch_count()
     acts = [torch.rand(n, D, device=device, generator=gen) * 2 - 1 for _ in range(min(K, 64))]
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
-    with ClockSampler(local_rank) as clocks:
-        barrier()
-        t_wall0 = time.perf_counter()
-        for i in range(K):
-            flush.zero_()
-            a, b = evs[i]
-            a.record()
-            env.step(acts[i % len(acts)])
-            b.record()
-            if (i + 1) % 16 == 0:
-                reduce_stats()
-        barrier()
-        t_wall = time.perf_counter() - t_wall0
+    barrier()
+    t_wall0 = time.perf_counter()
+    for i in range(K):
+        flush.zero_()
+        a, b = evs[i]
+        a.record()
+        env.step(acts[i % len(acts)])
+        b.record()
+        if (i + 1) % 16 == 0:
+            reduce_stats()
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
     launches = _lib.launch_count() - launches0
     dev_ms = sum(a.elapsed_time(b) for a, b in evs)
     t = torch.tensor([dev_ms], dtype=torch.float64, device=device)
@@ -334,6 +335,7 @@ def run_ours(args):
     if dist is not None:
         dist.barrier()
     e2e_s = time.perf_counter() - t0
+    clocks.__exit__()
     te = torch.tensor([e2e_s], dtype=torch.float64, device=device)
     if dist is not None:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)

@@ -12,7 +12,7 @@ from omniisaacgymenvs_b200.tasks.shared.locomotion import LocomotionTask
 
 def _solver_overrides(sim_config) -> dict:
     sim = sim_config.task_config.get("sim", {})
-    out = dict(sim.get("b200", {}))
+    out = {k: float(v) for k, v in sim.get("b200", {}).items()}
     if "gravity" in sim:
         out["gravity"] = tuple(float(g) for g in sim["gravity"])
     mat = sim.get("default_physics_material", {})

@@ -90,7 +90,10 @@ def test_substeps_in_one_launch_equal_separate_launches(cuda_lib):
         assert np.array_equal(a[k], b[k]), k
 
 
-def test_free_flight_conserves_momentum_without_gravity(cuda_lib):
+def test_free_flight_momentum_without_gravity(cuda_lib):
+    """No gravity, no contact: linear momentum is conserved by the continuous dynamics; the first-order
+    integrator drifts by O(dt^2) per step in generalized coordinates.  The kernel must (a) show the SAME
+    drift as the float64 oracle (agreement 1e-3 m/s) and (b) stay within the integrator's bound."""
     model, spec = dh.specs("Humanoid")
     model.gravity = (0.0, 0.0, 0.0)
     model.damping[:] = 0
@@ -99,10 +102,12 @@ def test_free_flight_conserves_momentum_without_gravity(cuda_lib):
     st["actions"][:] = 0
     com0 = _com_velocity(model, spec, st)
     g = dh.run_gpu(cuda_lib, model, spec, st, 2, DT, calls=16)
-    st1 = {k: g[k].astype(np.float32) for k in ("pos", "quat", "vel", "q", "qd")}
-    st1["actions"] = st["actions"]
-    com1 = _com_velocity(model, spec, st1)
-    assert np.abs(com1 - com0).max() < 5e-3
+    o = dh.run_oracle(model, spec, st, 2, DT, calls=16)
+    as_state = lambda r: dict({k: r[k].astype(np.float32) for k in ("pos", "quat", "vel", "q", "qd")}, actions=st["actions"])
+    com_g = _com_velocity(model, spec, as_state(g))
+    com_o = _com_velocity(model, spec, as_state(o))
+    assert np.abs(com_g - com_o).max() < 1e-3
+    assert np.abs(com_g - com0).max() < 0.1
 
 
 def _com_velocity(model, spec, st):
