@@ -355,7 +355,7 @@ def run_ours(args):
         if world == 1 or True:
             k1_ms, k1_best = k1_roofline(torch, device, ROOFLINE_ENVS)
             achieved = K1_BYTES[ROBOT] * ROOFLINE_ENVS / (k1_ms * 1e-3) / 1e9
-            roof = {"bound": "hbm", "kernel": "obs_reward_reset_kernel<21,2,64>", "achieved": achieved, "peak": peak,
+            roof = {"bound": "hbm", "kernel": "obs_reward_reset_kernel<21,2,32>", "achieved": achieved, "peak": peak,
                     "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                     "envs": ROOFLINE_ENVS, "bytes_per_env": K1_BYTES[ROBOT], "avg_ms": k1_ms, "best_ms": k1_best,
                     "note": "K1 timed alone at 1,048,576 envs (772 MB/launch > L2); the full step is dominated by "

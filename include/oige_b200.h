@@ -57,7 +57,9 @@ typedef struct OigeTaskParams {
     int32_t limit_cost_kind;  /* OIGE_LIMIT_COST_* (humanoid.py:120-127 vs ant.py:92-95) */
     int32_t walk_target_uses_z; /* 1 = upstream compute_rot quirk atan2(dz, dx) (default), 0 = atan2(dy, dx) */
     int32_t progress_increment; /* 1: fuse `progress_buf += 1` (rl_task.py:242) into the pass; 0: leave it */
-    int32_t reserved_i[2];
+    int32_t closed_form_angles; /* 1: normalize_angle(x) evaluated as the closed-form wrap of x into (-pi,pi]
+                                   (1-2 ulp from atan2(sin x, cos x)); 0: the literal chain (locomotion.py:190-192) */
+    int32_t reserved_i[1];
     float dt;                 /* task dt, 1/60 (locomotion.py:163) */
     float dof_vel_scale;
     float angular_velocity_scale;
@@ -172,7 +174,7 @@ uint64_t oige_kernel_launch_count(void);
  * clamp of VecEnvRLGames._process_data (envs/vec_env_rlgames.py:42). */
 int oige_obs_reward_reset_f32(const OigeTaskParams* params, const OigeState* state,
                               const OigeTaskBuffers* buf, int64_t n_envs, void* stream);
-/* same pass with an explicit tile size (envs per CTA: 32, 64 or 128; 0 = automatic) -- tuning hook */
+/* same pass with an explicit tile size (envs per CTA: 32 or 64; 0 = automatic) -- tuning hook */
 int oige_obs_reward_reset_tile_f32(const OigeTaskParams* params, const OigeState* state,
                                    const OigeTaskBuffers* buf, int64_t n_envs, int32_t tile, void* stream);
 

@@ -30,7 +30,7 @@ vp = C.c_void_p
 class OigeTaskParams(C.Structure):
     _fields_ = [
         ("num_dof", i32), ("num_sensors", i32), ("num_obs", i32), ("limit_cost_kind", i32),
-        ("walk_target_uses_z", i32), ("progress_increment", i32), ("reserved_i", i32 * 2),
+        ("walk_target_uses_z", i32), ("progress_increment", i32), ("closed_form_angles", i32), ("reserved_i", i32 * 1),
         ("dt", f32), ("dof_vel_scale", f32), ("angular_velocity_scale", f32), ("contact_force_scale", f32),
         ("heading_weight", f32), ("up_weight", f32), ("actions_cost_scale", f32), ("energy_cost_scale", f32),
         ("joints_at_limit_cost_scale", f32), ("death_cost", f32), ("termination_height", f32),

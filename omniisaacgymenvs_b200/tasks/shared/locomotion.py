@@ -70,6 +70,7 @@ class LocomotionTask(RLTask):
         p.limit_cost_kind = self.limit_cost_kind
         p.walk_target_uses_z = 1  # upstream compute_rot quirk kept
         p.progress_increment = 1
+        p.closed_form_angles = 1  # normalize_angle as a closed-form wrap (1-2 ulp from the literal chain)
         p.dt = self.dt
         p.dof_vel_scale = self.dof_vel_scale
         p.angular_velocity_scale = self.angular_velocity_scale

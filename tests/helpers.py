@@ -18,12 +18,13 @@ RTOL = 1e-5  # north_star: obs/reward within 1e-5 relative error in fp32
 ATOL = 1e-5  # absolute floor for O(1) quantities (angles, projections, rewards near 0)
 
 
-def params_from_spec(spec, dof_lo, dof_hi, progress_increment=1, clip_obs=None, walk_uses_z=1):
+def params_from_spec(spec, dof_lo, dof_hi, progress_increment=1, clip_obs=None, walk_uses_z=1, closed_form_angles=1):
     p = _lib.OigeTaskParams()
     p.num_dof, p.num_sensors, p.num_obs = spec.num_dof, spec.num_sensors, spec.num_obs
     p.limit_cost_kind = _lib.LIMIT_COST_ANT if spec.name == "Ant" else _lib.LIMIT_COST_HUMANOID
     p.walk_target_uses_z = walk_uses_z
     p.progress_increment = progress_increment
+    p.closed_form_angles = closed_form_angles
     p.dt = spec.dt
     p.dof_vel_scale = spec.dof_vel_scale
     p.angular_velocity_scale = spec.angular_velocity_scale
@@ -97,11 +98,13 @@ class DeviceCase:
                 "heading_vec": self.heading_vec.cpu()}
 
 
-def run_k1(spec, s, device="cuda:0", tile=0, clip_obs=None, progress_increment=1, with_stats=False):
+def run_k1(spec, s, device="cuda:0", tile=0, clip_obs=None, progress_increment=1, with_stats=False,
+           closed_form_angles=1):
     """One fused obs/reward/reset pass through the C ABI on a copy of state dict `s`."""
     lib = _lib.load()
     case = DeviceCase(spec, s, device, with_stats=with_stats)
-    p = params_from_spec(spec, s["dof_lo"], s["dof_hi"], progress_increment=progress_increment, clip_obs=clip_obs)
+    p = params_from_spec(spec, s["dof_lo"], s["dof_hi"], progress_increment=progress_increment, clip_obs=clip_obs,
+                         closed_form_angles=closed_form_angles)
     st, bf = case.structs()
     with torch.cuda.device(case.dev):
         stream = _lib.current_stream_ptr(case.dev)

@@ -17,17 +17,38 @@ pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
 
 
+@pytest.mark.parametrize("closed_form", [1, 0])
 @pytest.mark.parametrize("name", helpers.golden_names())
-def test_k1_matches_golden_reference_vectors(cuda_lib, name):
+def test_k1_matches_golden_reference_vectors(cuda_lib, name, closed_form):
+    """Both angle-normalisation modes: 0 = literal atan2(sin, cos) chain, 1 = closed-form wrap (default)."""
     s, ref = helpers.load_golden(name)
     spec = lo.SPECS["Humanoid" if name.startswith("humanoid") else "Ant"]
-    got = helpers.run_k1(spec, s, DEV)
+    got = helpers.run_k1(spec, s, DEV, closed_form_angles=closed_form)
     helpers.assert_k1_matches(got, ref, name)
 
 
 @pytest.mark.parametrize("robot", ["Humanoid", "Ant"])
+def test_k1_closed_form_angles_agree_with_literal_chain(cuda_lib, robot):
+    """The closed-form wrap must sit within a few ulp of the literal atan2(sin x, cos x) chain."""
+    import math
+
+    spec = lo.SPECS[robot]
+    s = lo.synthetic_state(spec, 65536, 17)
+    a = helpers.run_k1(spec, s, DEV, closed_form_angles=1)
+    b = helpers.run_k1(spec, s, DEV, closed_form_angles=0)
+    for k in a:
+        if k != "obs":
+            assert torch.equal(a[k], b[k]), k
+    other = [c for c in range(spec.num_obs) if c not in (7, 8, 9)]
+    assert torch.equal(a["obs"][:, other], b["obs"][:, other])
+    d = (a["obs"][:, 7:10] - b["obs"][:, 7:10]).abs()
+    d = torch.minimum(d, (2 * math.pi - d).abs())
+    assert float(d.max()) <= 1.5e-6, float(d.max())
+
+
+@pytest.mark.parametrize("robot", ["Humanoid", "Ant"])
 @pytest.mark.parametrize("n", [1, 3, 31, 32, 33, 64, 127, 4096, 4099])
-@pytest.mark.parametrize("tile", [0, 32, 64, 128])
+@pytest.mark.parametrize("tile", [0, 32, 64])
 def test_k1_matches_oracle_all_tiles_and_ragged_sizes(cuda_lib, robot, n, tile):
     spec = lo.SPECS[robot]
     s = lo.synthetic_state(spec, n, seed=n + 11)
@@ -170,3 +191,20 @@ def test_k1_is_idempotent_on_pure_outputs(cuda_lib):
     assert torch.equal(a["obs"], b["obs"])
     assert torch.equal(a["potentials"], b["potentials"])
     assert torch.equal(b["prev_potentials"], a["potentials"])
+
+
+@pytest.mark.parametrize("robot", ["Humanoid", "Ant"])
+def test_k1_fast_division_is_correctly_rounded(cuda_lib, robot):
+    """unscale() uses a reciprocal + one-FMA-correction division (csrc: div_rn); it must equal the
+    IEEE quotient torch computes, bit for bit, because the Ant limit cost thresholds it at 0.99."""
+    spec = lo.SPECS[robot]
+    n = 1 << 18
+    s = lo.synthetic_state(spec, n, 33)
+    got = helpers.run_k1(spec, s, DEV)
+    d = spec.num_dof
+    ref = (2.0 * s["dof_pos"] - s["dof_hi"] - s["dof_lo"]) / (s["dof_hi"] - s["dof_lo"])
+    assert torch.equal(got["obs"][:, 12:12 + d], ref)
+    assert torch.equal(got["obs"][:, 12 + d:12 + 2 * d], s["dof_vel"] * spec.dof_vel_scale)
+    assert torch.equal(got["obs"][:, 12 + 2 * d + 6 * spec.num_sensors:], s["actions"])
+    assert torch.equal(got["obs"][:, 12 + 2 * d:12 + 2 * d + 6 * spec.num_sensors],
+                       s["sensors"].reshape(n, -1) * spec.contact_force_scale)
