@@ -33,6 +33,9 @@ ROBOT = "Humanoid"
 K1_BYTES = {"Humanoid": 772, "Ant": 556}      # SURVEY.md section 8(d) algorithmic bytes per env-step (K1)
 STEP_BYTES = {"Humanoid": 944}                # informational: fused full step
 ROOFLINE_ENVS = 1 << 20
+# dram__bytes_read.sum + dram__bytes_write.sum of one K1 launch at 1,048,576 envs, from the ncu --set full
+# capture summarised in profiles/r1_ncu_full.txt (390.1 MB + 367.4 MB); algorithmic bytes are 809.5 MB
+K1_TRAFFIC_BYTES_1M = 757.6e6
 
 
 def read_peaks():
@@ -47,23 +50,51 @@ def read_peaks():
 
 
 class ClockSampler:
-    """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
+    """Samples SM clock and throttle reasons while the benchmark runs (NVML; nvidia-smi as a fallback)."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index: int):
         self.index, self.samples, self._stop, self._t = index, [], threading.Event(), None
+        self.sm_max = None
+        self._nvml = None
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            visible = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(visible.split(",")[index]) if visible and visible.split(",")[index].isdigit() else index
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.sm_max = float(pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM))
+            self._nvml = pynvml
+        except Exception:
+            self._nvml = None
+
+    def _sample_nvml(self):
+        n = self._nvml
+        sm = float(n.nvmlDeviceGetClockInfo(self._h, n.NVML_CLOCK_SM))
+        try:
+            r = int(n.nvmlDeviceGetCurrentClocksEventReasons(self._h))
+        except Exception:
+            r = int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self._h))
+        flags = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40}
+        self.samples.append((sm, [k for k, bit in flags.items() if r & bit]))
+
+    def _sample_smi(self):
+        out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
+                              str(self.index)], capture_output=True, text=True, timeout=5).stdout.strip()
+        f = [x.strip() for x in out.split(",")]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        self.sm_max = float(f[1])
+        self.samples.append((float(f[0]), [n for i, n in enumerate(names) if f[2 + i].lower().startswith("active")]))
 
     def _run(self):
         while not self._stop.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
-                                      str(self.index)], capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.samples.append([x.strip() for x in out.split(",")])
+                self._sample_nvml() if self._nvml is not None else self._sample_smi()
             except Exception:
                 pass
-            self._stop.wait(0.1)
+            self._stop.wait(0.002 if self._nvml is not None else 0.1)
 
     def __enter__(self):
         self._t = threading.Thread(target=self._run, daemon=True)
@@ -74,14 +105,15 @@ class ClockSampler:
         self._stop.set()
         self._t.join(timeout=6)
 
-    def summary(self):
-        sm = [float(s[0]) for s in self.samples if s and s[0].replace(".", "").isdigit()]
-        mx = [float(s[1]) for s in self.samples if len(s) > 1 and s[1].replace(".", "").isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for i, n in enumerate(names) if any(len(s) > 2 + i and s[2 + i].lower().startswith("active")
-                                                         for s in self.samples)]
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(self.samples)}
+    def mark(self):
+        return len(self.samples)
+
+    def summary(self, lo=0, hi=None):
+        part = self.samples[lo:hi]
+        sm = [s[0] for s in part]
+        reasons = sorted({r for s in part for r in s[1]})
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": self.sm_max, "reasons": reasons,
+                "samples": len(part), "source": "nvml" if self._nvml is not None else "nvidia-smi"}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -177,7 +209,10 @@ def k1_roofline(torch, device, n_envs, iters=20, warmup=5):
     from omniisaacgymenvs_b200 import _lib
     from omniisaacgymenvs_b200.utils.task_util import make_env
 
-    env, task = make_env(ROBOT, num_envs=n_envs, device_id=device.index or 0)
+    import contextlib
+
+    with contextlib.redirect_stdout(sys.stderr):
+        env, task = make_env(ROBOT, num_envs=n_envs, device_id=device.index or 0)
     v = task.get_robot()
     g = torch.Generator(device=device).manual_seed(0)
     # synthetic state of SURVEY.md 8(d): everything random, heights straddling the termination height
@@ -261,25 +296,22 @@ def run_ours(args):
     from omniisaacgymenvs_b200.utils.task_util import make_env
 
     n = args.envs_per_gpu
-    env, task = make_env(ROBOT, num_envs=n, device_id=local_rank, seed=42, env_id_offset=rank * n,
-                         global_num_envs=world * n)
-    env.reset()
+    import contextlib
+
+    with contextlib.redirect_stdout(sys.stderr):  # stdout carries exactly one JSON line
+        env, task = make_env(ROBOT, num_envs=n, device_id=local_rank, seed=42, env_id_offset=rank * n,
+                             global_num_envs=world * n)
+        env.reset()
     K, W = args.steps, max(args.warmup, 3)
     D = task.num_actions
     gen = torch.Generator(device=device).manual_seed(1234 + rank)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)  # > 126 MB L2
-    side = torch.cuda.Stream(device=device)
-    stats_total = torch.zeros(4, dtype=torch.float64, device=device)
+    from omniisaacgymenvs_b200.utils.distributed import EpisodeStatsReducer, max_over_ranks
+
+    reducer = EpisodeStatsReducer(device)
 
     def reduce_stats():
-        s = task.read_episode_stats()
-        if dist is not None:
-            side.wait_stream(torch.cuda.current_stream(device))
-            with torch.cuda.stream(side):
-                dist.all_reduce(s)
-                stats_total.add_(s)
-        else:
-            stats_total.add_(s)
+        reducer.reduce(task.read_episode_stats())
 
     def barrier():
         if dist is not None:
@@ -298,6 +330,7 @@ def run_ours(args):
     acts = [torch.rand(n, D, device=device, generator=gen) * 2 - 1 for _ in range(min(K, 64))]
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
     barrier()
+    clk_lo = clocks.mark()
     t_wall0 = time.perf_counter()
     for i in range(K):
         flush.zero_()
@@ -309,16 +342,14 @@ def run_ours(args):
             reduce_stats()
     barrier()
     t_wall = time.perf_counter() - t_wall0
+    clk_hi = clocks.mark()
     launches = _lib.launch_count() - launches0
     dev_ms = sum(a.elapsed_time(b) for a, b in evs)
-    t = torch.tensor([dev_ms], dtype=torch.float64, device=device)
-    if dist is not None:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    dev_ms = float(t.item())
+    dev_ms = max_over_ranks(dev_ms, device)
     ms_per_step = dev_ms / K
     value = world * n * K / (dev_ms / 1e3)
     reduce_stats()
-    torch.cuda.current_stream(device).wait_stream(side)
+    episode_stats = reducer.result()
 
     # ---- end-to-end: HOST buffers through the C-ABI host entry point, copies inside the timed region ----
     a_host = [(torch.rand(n, D) * 2 - 1).pin_memory() for _ in range(4)]
@@ -336,17 +367,13 @@ def run_ours(args):
         dist.barrier()
     e2e_s = time.perf_counter() - t0
     clocks.__exit__()
-    te = torch.tensor([e2e_s], dtype=torch.float64, device=device)
-    if dist is not None:
-        dist.all_reduce(te, op=dist.ReduceOp.MAX)
-    e2e_value = world * n * K / float(te.item())
+    e2e_value = world * n * K / max_over_ranks(e2e_s, device)
     h2d = n * D * 4
     d2h = n * task.num_observations * 4 + n * 4 + n * 8
 
     line = None
     if rank == 0:
         breakdown = step_breakdown(torch, env, task, acts[0])
-        stats = stats_total.tolist()
         del env, task
         torch.cuda.empty_cache()
         peak, peak_src = read_peaks()
@@ -356,7 +383,7 @@ def run_ours(args):
             k1_ms, k1_best = k1_roofline(torch, device, ROOFLINE_ENVS)
             achieved = K1_BYTES[ROBOT] * ROOFLINE_ENVS / (k1_ms * 1e-3) / 1e9
             roof = {"bound": "hbm", "kernel": "obs_reward_reset_kernel<21,2,32>", "achieved": achieved, "peak": peak,
-                    "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                    "unit": "GB/s", "frac": achieved / peak, "traffic": K1_TRAFFIC_BYTES_1M if ROOFLINE_ENVS == (1 << 20) else None, "peak_source": peak_src,
                     "envs": ROOFLINE_ENVS, "bytes_per_env": K1_BYTES[ROBOT], "avg_ms": k1_ms, "best_ms": k1_best,
                     "note": "K1 timed alone at 1,048,576 envs (772 MB/launch > L2); the full step is dominated by "
                             "K2 which is issue/latency-bound (no HBM or tensor roofline applies), see step_breakdown"}
@@ -375,14 +402,12 @@ def run_ours(args):
                        "envs_per_gpu": n, "global_envs": world * n, "parallelism": f"env-index sharding x{world}",
                        "l2": "flushed between steps (256 MiB memset outside the per-step CUDA-event pairs)",
                        "actions": "uniform random policy, device-resident"},
-            "clocks": clocks.summary(),
+            "clocks": clocks.summary(clk_lo, clk_hi),
             "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(launches),
             "roofline": roof, "cpu_baseline": cpu, "step_breakdown": breakdown,
             "wall_s_timed_region": t_wall,
-            "episode_stats": {"sum_reward": stats[0], "episodes_finished": stats[1],
-                              "mean_episode_length": (stats[2] / stats[1]) if stats[1] else None,
-                              "env_steps": stats[3]},
+            "episode_stats": episode_stats,
         }
     if dist is not None:
         dist.barrier()
