@@ -215,8 +215,10 @@ int oige_env_step_f32(const OigeModel* model, const OigeTaskParams* params, cons
 
 /* ---- the same step with HOST buffers (the call rl_games would make with CPU tensors) ----
  * actions_host [N,D] -> H2D into actions_dev_staging; after the step obs/rew/reset_buf are copied
- * D2H into the host buffers.  All copies are cudaMemcpyAsync on `stream` (pinned host memory
- * gives true asynchrony); the caller synchronises the stream before reading the outputs. */
+ * D2H into the host buffers.  Internally the env range is cut into 4 tile-aligned chunks, each on
+ * a library-owned stream (H2D -> K3 -> K2 -> K1 -> D2H), so copies overlap kernels; `stream` waits for
+ * all of them.  Pinned host memory gives true asynchrony; the caller synchronises `stream` before
+ * reading the outputs.  Results are identical to oige_env_step_f32 (envs are independent). */
 int oige_env_step_host_f32(const OigeModel* model, const OigeTaskParams* params, const OigeState* state,
                            const OigeTaskBuffers* buf, const OigeResetInit* init,
                            const float* actions_host, float* actions_dev_staging,

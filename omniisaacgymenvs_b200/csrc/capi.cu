@@ -68,6 +68,29 @@ static int check_common(const char* who, const OigeTaskParams* p, const OigeStat
     return OIGE_OK;
 }
 
+// lazily created per-device copy/compute pipeline of oige_env_step_host_f32
+constexpr int kHostChunks = 4;
+struct HostPipe {
+    cudaStream_t streams[kHostChunks];
+    cudaEvent_t start, done[kHostChunks];
+};
+static HostPipe* host_pipe() {
+    static HostPipe* pipes[64] = {nullptr};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    if (!pipes[dev]) {
+        HostPipe* p = new HostPipe();
+        bool ok = cudaEventCreateWithFlags(&p->start, cudaEventDisableTiming) == cudaSuccess;
+        for (int i = 0; i < kHostChunks && ok; ++i) {
+            ok = cudaStreamCreateWithFlags(&p->streams[i], cudaStreamNonBlocking) == cudaSuccess &&
+                 cudaEventCreateWithFlags(&p->done[i], cudaEventDisableTiming) == cudaSuccess;
+        }
+        if (!ok) { delete p; return nullptr; }
+        pipes[dev] = p;
+    }
+    return pipes[dev];
+}
+
 }  // namespace oige
 
 using namespace oige;
@@ -157,21 +180,49 @@ int oige_env_step_host_f32(const OigeModel* model, const OigeTaskParams* params,
                            float clip_actions, uint64_t seed, uint64_t counter, int64_t env_id_offset,
                            int64_t n_envs, int32_t substeps, float dt, void* stream) {
     if (int rc = check_common("oige_env_step_host_f32", params, state, buf, n_envs)) return rc;
-    if (!actions_host || !actions_dev_staging || !obs_host || !rew_host || !reset_host)
+    if (!actions_host || !actions_dev_staging || !obs_host || !rew_host || !reset_host || !init || !model)
         return fail(OIGE_E_NULL, "oige_env_step_host_f32: null host/staging buffer");
-    cudaStream_t s = (cudaStream_t)stream;
-    const size_t na = (size_t)n_envs * params->num_dof * sizeof(float);
-    cudaError_t e = cudaMemcpyAsync(actions_dev_staging, actions_host, na, cudaMemcpyHostToDevice, s);
-    if (e != cudaSuccess) return fail((int)e, "H2D actions: %s", cudaGetErrorString(e));
-    if (int rc = oige_env_step_f32(model, params, state, buf, init, actions_dev_staging, clip_actions, seed, counter,
-                                   env_id_offset, n_envs, substeps, dt, stream))
-        return rc;
-    e = cudaMemcpyAsync(obs_host, buf->obs, (size_t)n_envs * params->num_obs * sizeof(float),
-                        cudaMemcpyDeviceToHost, s);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(rew_host, buf->rew, (size_t)n_envs * sizeof(float), cudaMemcpyDeviceToHost, s);
-    if (e == cudaSuccess)
-        e = cudaMemcpyAsync(reset_host, buf->reset_buf, (size_t)n_envs * sizeof(int64_t), cudaMemcpyDeviceToHost, s);
-    if (e != cudaSuccess) return fail((int)e, "D2H results: %s", cudaGetErrorString(e));
+    if (n_envs == 0) return OIGE_OK;
+    cudaStream_t user = (cudaStream_t)stream;
+    HostPipe* hp = host_pipe();
+    if (!hp) return fail((int)cudaErrorUnknown, "oige_env_step_host_f32: cannot create copy/compute streams");
+    // Envs are independent, so the step is cut into kHostChunks contiguous env ranges, each on its own
+    // stream: H2D(actions) -> K3 -> K2 -> K1 -> D2H(obs, rew, resets).  Chunk c's D2H overlaps chunk c+1's
+    // kernels and chunk c+2's H2D (separate copy engines per direction).  Results are identical to the
+    // one-launch step: every kernel is row-wise and reset noise is keyed by the global env id.
+    const int D = params->num_dof, S = params->num_sensors, OBS = params->num_obs;
+    int64_t per = ((n_envs + kHostChunks - 1) / kHostChunks + 31) / 32 * 32;  // tile-aligned chunk size
+    if (n_envs < 4096) per = n_envs;                                           // too small to be worth splitting
+    cudaError_t e = cudaEventRecord(hp->start, user);
+    if (e != cudaSuccess) return fail((int)e, "event record: %s", cudaGetErrorString(e));
+    int used = 0;
+    for (int64_t off = 0; off < n_envs; off += per, ++used) {
+        const int64_t cnt = (n_envs - off) < per ? (n_envs - off) : per;
+        cudaStream_t s = hp->streams[used];
+        cudaStreamWaitEvent(s, hp->start, 0);
+        OigeState st = *state;
+        st.root_pos += off * 3; st.root_quat += off * 4; st.root_vel += off * 6;
+        st.dof_pos += off * D; st.dof_vel += off * D;
+        if (st.sensors) st.sensors += off * 6 * S;
+        OigeTaskBuffers bf = *buf;
+        bf.obs += off * OBS; bf.rew += off; bf.reset_buf += off; bf.progress_buf += off; bf.potentials += off;
+        bf.prev_potentials += off; bf.up_vec += off * 3; bf.heading_vec += off * 3; bf.actions += off * D;
+        OigeResetInit in = *init;
+        in.initial_root_pos += off * 3; in.initial_root_rot += off * 4; in.initial_dof_pos += off * D;
+        float* stage = actions_dev_staging + off * D;
+        e = cudaMemcpyAsync(stage, actions_host + off * D, (size_t)cnt * D * sizeof(float), cudaMemcpyHostToDevice, s);
+        if (e != cudaSuccess) return fail((int)e, "H2D actions: %s", cudaGetErrorString(e));
+        if (int rc = oige_env_step_f32(model, params, &st, &bf, &in, stage, clip_actions, seed, counter,
+                                       env_id_offset + off, cnt, substeps, dt, (void*)s))
+            return rc;
+        e = cudaMemcpyAsync(obs_host + off * OBS, bf.obs, (size_t)cnt * OBS * sizeof(float), cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(rew_host + off, bf.rew, (size_t)cnt * sizeof(float), cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess)
+            e = cudaMemcpyAsync(reset_host + off, bf.reset_buf, (size_t)cnt * sizeof(int64_t), cudaMemcpyDeviceToHost, s);
+        if (e != cudaSuccess) return fail((int)e, "D2H results: %s", cudaGetErrorString(e));
+        cudaEventRecord(hp->done[used], s);
+        cudaStreamWaitEvent(user, hp->done[used], 0);  // the caller's stream observes the whole step
+    }
     return OIGE_OK;
 }
 

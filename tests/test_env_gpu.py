@@ -155,8 +155,9 @@ def test_humanoid_random_policy_falls_and_ant_stays_up(cuda_lib):
     assert float(z.min()) > 0.31 and int(task.reset_buf.sum()) == 0
 
 
-def test_step_host_round_trip(cuda_lib):
-    n = 512
+@pytest.mark.parametrize("n", [512, 20000])
+def test_step_host_round_trip(cuda_lib, n):
+    """n=20000 exercises the chunked multi-stream pipeline (ragged last chunk) of oige_env_step_host_f32."""
     env_a, task_a = make_env("Humanoid", num_envs=n, seed=4)
     env_b, task_b = make_env("Humanoid", num_envs=n, seed=4)
     env_a.reset(); env_b.reset()
@@ -165,10 +166,13 @@ def test_step_host_round_trip(cuda_lib):
     obs_h = torch.empty(n, 87).pin_memory()
     rew_h = torch.empty(n).pin_memory()
     rst_h = torch.empty(n, dtype=torch.int64).pin_memory()
-    env_a.step_host(ah, obs_h, rew_h, rst_h)
-    torch.cuda.synchronize()
-    o, r, d, _ = env_b.step(a.to(task_b.device))
-    assert torch.equal(obs_h, o["obs"].cpu()) and torch.equal(rew_h, r.cpu()) and torch.equal(rst_h, d.cpu())
+    for _ in range(3):
+        env_a.step_host(ah, obs_h, rew_h, rst_h)
+        torch.cuda.synchronize()
+        o, r, d, _ = env_b.step(a.to(task_b.device))
+        assert torch.equal(obs_h, o["obs"].cpu()) and torch.equal(rew_h, r.cpu()) and torch.equal(rst_h, d.cpu())
+    va, vb = task_a.get_robot(), task_b.get_robot()
+    assert torch.equal(va.dof_pos, vb.dof_pos) and torch.equal(va.root_pos, vb.root_pos)
 
 
 def test_cpu_tensors_are_rejected_not_silently_computed(cuda_lib):
