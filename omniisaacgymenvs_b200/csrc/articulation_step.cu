@@ -38,15 +38,17 @@ namespace {
 constexpr int kWarpsPerBlock = 4;
 constexpr int kMaxLevels = 16;
 constexpr int kMaxChildren = 4;
+constexpr int kMaxJump = 4;  // 2^4 = 16 >= kMaxLevels
 
 struct DevModel {
     int num_links, num_spheres, num_sensors, max_depth;
-    int max_sph_per_link, pad0, pad1, pad2;
+    int max_sph_per_link, jump_rounds, pad1, pad2;
     int parent[32];
     int dof[32];
     int level[32];
     int child[kMaxChildren][32];
     int maxch_at_level[kMaxLevels];  // max #children over parents at this level
+    int anc[kMaxJump][32];           // 2^k-th ancestor (clamped at the root) for pointer jumping
     int sph_start[32];
     int sph_count[32];
     int sensor_of_link[32];
@@ -219,54 +221,99 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
         const bool last = (step == A.substeps - 1);
         const float root_z = shfl(rpos.z, 0);
 
-        // ---- pass 1: kinematics, top-down -----------------------------------------------------
-        Q4 quat = rquat;
+        // ---- pass 1: kinematics by POINTER JUMPING (log2(depth) rounds instead of depth levels) -------
+        // Every lane starts with its transform relative to its parent, T_i = (R_i, p_i); round k
+        // composes it with the transform of its 2^k-th ancestor (T_i <- T_anc o T_i), so after
+        // ceil(log2(depth)) rounds all transforms are relative to the root.  The root carries the
+        // identity, so links that already reached it are left unchanged.
+        M3 R;
         V3 p = {0.f, 0.f, 0.f};
-        V6 v = rvel;
-        V6 b = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
+        {
+            Q4 ql = {1.f, 0.f, 0.f, 0.f};
+            if (is_joint) {
+                float sh, ch;
+                sincosf(0.5f * q, &sh, &ch);
+                ql = qmul(jquat, Q4{ch, sh * axis.x, sh * axis.y, sh * axis.z});
+                p = jpos;
+            }
+            R = qmat(ql);
+        }
+        for (int k = 0; k < M.jump_rounds; ++k) {
+            const int an = active ? M.anc[k][li] : lane;
+            M3 Ra;
+            V3 pa;
+#pragma unroll
+            for (int j = 0; j < 9; ++j) Ra.m[j] = shfl(R.m[j], an);
+            pa = {shfl(p.x, an), shfl(p.y, an), shfl(p.z, an)};
+            p = pa + mulv(Ra, p);
+            M3 Rn;
+#pragma unroll
+            for (int r = 0; r < 3; ++r)
+#pragma unroll
+                for (int cidx = 0; cidx < 3; ++cidx)
+                    Rn.m[3 * r + cidx] = Ra.m[3 * r] * R.m[cidx] + Ra.m[3 * r + 1] * R.m[3 + cidx] + Ra.m[3 * r + 2] * R.m[6 + cidx];
+            R = Rn;
+        }
+        {   // root-relative -> world-aligned axes about O (the root origin)
+            const M3 R0l = qmat(rquat);
+            M3 R0;
+#pragma unroll
+            for (int j = 0; j < 9; ++j) R0.m[j] = shfl(R0l.m[j], 0);
+            p = mulv(R0, p);
+            M3 Rn;
+#pragma unroll
+            for (int r = 0; r < 3; ++r)
+#pragma unroll
+                for (int cidx = 0; cidx < 3; ++cidx)
+                    Rn.m[3 * r + cidx] = R0.m[3 * r] * R.m[cidx] + R0.m[3 * r + 1] * R.m[3 + cidx] + R0.m[3 * r + 2] * R.m[6 + cidx];
+            R = Rn;
+        }
+        // joint motion subspace, velocities (prefix sums of s_j qd_j over the ancestor path, same jumps)
         V6 s = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
-        V6 c = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
-        if (lane == 0) {
-            const V3 wxv = cross(ang(rvel), lin(rvel));
-            b = {{0.f, 0.f, 0.f, -wxv.x, -wxv.y, -wxv.z}};
-        }
-        Q4 ql = {1.f, 0.f, 0.f, 0.f};
+        V6 v = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
         if (is_joint) {
-            float sh, ch;
-            sincosf(0.5f * q, &sh, &ch);
-            ql = qmul(jquat, Q4{ch, sh * axis.x, sh * axis.y, sh * axis.z});
+            const V3 aw = mulv(R, axis);
+            s = mk6(aw, cross(p, aw));
+#pragma unroll
+            for (int k = 0; k < 6; ++k) v.a[k] = s.a[k] * qd;
         }
-        for (int l = 1; l <= max_depth; ++l) {
-            const bool mine = (level == l);
-            const int src = mine ? parent : lane;
-            const Q4 pq = {shfl(quat.w, src), shfl(quat.x, src), shfl(quat.y, src), shfl(quat.z, src)};
-            const V3 pp = {shfl(p.x, src), shfl(p.y, src), shfl(p.z, src)};
-            V6 pv, pb;
+        for (int k = 0; k < M.jump_rounds; ++k) {
+            const int an = active ? M.anc[k][li] : lane;
 #pragma unroll
-            for (int k = 0; k < 6; ++k) {
-                pv.a[k] = shfl(v.a[k], src);
-                pb.a[k] = shfl(b.a[k], src);
+            for (int j = 0; j < 6; ++j) {
+                const float t = shfl(v.a[j], an);
+                v.a[j] += (an != lane) ? t : 0.f;
             }
-            if (mine) {
-                const M3 Rp = qmat(pq);
-                p = pp + mulv(Rp, jpos);
-                quat = qmul(pq, ql);
-                const M3 Ri = qmat(quat);
-                const V3 aw = mulv(Ri, axis);
-                s = mk6(aw, cross(p, aw));
+        }
+        V6 v0;
 #pragma unroll
-                for (int k = 0; k < 6; ++k) v.a[k] = fmaf(s.a[k], qd, pv.a[k]);
-                const V3 w = ang(v), vl = lin(v);
-                const V3 ca = cross(w, aw);
-                const V3 cl = cross(w, lin(s)) + cross(vl, aw);
-                c = mk6(qd * ca, qd * cl);
+        for (int j = 0; j < 6; ++j) {
+            v0.a[j] = shfl(rvel.a[j], 0);
+            v.a[j] += v0.a[j];
+        }
+        // velocity-product accelerations c_i and their path sums b_i (b_root = -(0, w0 x v0))
+        V6 c = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
+        if (is_joint) {
+            const V3 w = ang(v), vl = lin(v), aw = ang(s);
+            const V3 ca = cross(w, aw);
+            const V3 cl = cross(w, lin(s)) + cross(vl, aw);
+            c = mk6(qd * ca, qd * cl);
+        }
+        V6 b = c;
+        for (int k = 0; k < M.jump_rounds; ++k) {
+            const int an = active ? M.anc[k][li] : lane;
 #pragma unroll
-                for (int k = 0; k < 6; ++k) b.a[k] = pb.a[k] + c.a[k];
+            for (int j = 0; j < 6; ++j) {
+                const float t = shfl(b.a[j], an);
+                b.a[j] += (an != lane) ? t : 0.f;
             }
+        }
+        {
+            const V3 wxv = cross(ang(v0), lin(v0));
+            b.a[3] -= wxv.x; b.a[4] -= wxv.y; b.a[5] -= wxv.z;
         }
 
         // ---- per-link spatial inertia, bias force, contacts (all lanes in parallel) -------------
-        const M3 R = qmat(quat);
         S6 IA;
         V6 pA;
         {
@@ -604,6 +651,11 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
     }
     for (int i = 0; i < L; ++i)
         if (nchild[i] > h->maxch_at_level[h->level[i]]) h->maxch_at_level[h->level[i]] = nchild[i];
+    for (int i = 0; i < 32; ++i) h->anc[0][i] = (i < L && i > 0) ? h->parent[i] : (i < L ? 0 : i);
+    for (int k = 1; k < kMaxJump; ++k)
+        for (int i = 0; i < 32; ++i) h->anc[k][i] = i < L ? h->anc[k - 1][h->anc[k - 1][i]] : i;
+    h->jump_rounds = 0;
+    while ((1 << h->jump_rounds) < h->max_depth) ++h->jump_rounds;
     for (int i = 0; i < L; ++i) {
         for (int k = 0; k < 3; ++k) { h->jpos[k][i] = d->joint_pos[i][k]; h->axis[k][i] = d->joint_axis[i][k]; h->com[k][i] = d->com[i][k]; }
         for (int k = 0; k < 4; ++k) h->jquat[k][i] = d->joint_quat[i][k];
