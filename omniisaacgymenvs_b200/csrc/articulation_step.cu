@@ -42,7 +42,7 @@ constexpr int kMaxJump = 4;  // 2^4 = 16 >= kMaxLevels
 
 struct DevModel {
     int num_links, num_spheres, num_sensors, max_depth;
-    int max_sph_per_link, jump_rounds, pad1, pad2;
+    int max_sph_per_link, jump_rounds, pack, pad2;
     int parent[32];
     int dof[32];
     int level[32];
@@ -167,6 +167,7 @@ struct K2Args {
     float dt;
 };
 
+template <bool PACKED>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_constant__ OigeTaskParams P,
                          const __grid_constant__ K2Args A) {
@@ -178,17 +179,24 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
     }
     __syncthreads();
 
+    // Small robots are PACKED: a warp carries `pack` = floor(32 / num_links) environments side by side
+    // (Ant: 3 x 9 lanes, Humanoid: 1 x 22).  Lane = (slot, link); every shuffle source is offset by the
+    // slot's first lane, so the packed envs run the same instruction stream without interacting.
     const int lane = threadIdx.x & 31;
-    const long long env = (long long)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
-    if (env >= A.n) return;  // warp-uniform
-
     const int L = M.num_links;
-    const bool active = lane < L;
-    const int li = active ? lane : 0;  // clamp so table reads stay in range
+    const int pack = PACKED ? M.pack : 1;
+    const long long warp_id = (long long)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
+    if (warp_id * pack >= A.n) return;  // warp-uniform
+    const int slot = PACKED ? lane / L : (lane < L ? 0 : 1);
+    const long long env = warp_id * pack + slot;
+    const bool active = slot < pack && env < A.n;
+    const int li = active ? lane - slot * L : 0;  // link index (clamped so table reads stay in range)
+    const int ebase = active ? slot * L : lane;   // first lane of this env (inactive lanes talk to themselves)
+    const bool is_root = active && li == 0;
     const int level = active ? M.level[li] : -1;
-    const int parent = active && lane > 0 ? M.parent[li] : lane;
+    const int parent = active && li > 0 ? ebase + M.parent[li] : lane;
     const int dofi = active ? M.dof[li] : -1;
-    const bool is_joint = active && lane > 0;
+    const bool is_joint = active && li > 0;
     const float dt = A.dt;
     const int D = P.num_dof;
 
@@ -202,7 +210,7 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
     V3 rpos = {0.f, 0.f, 0.f};
     Q4 rquat = {1.f, 0.f, 0.f, 0.f};
     V6 rvel = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};  // (ang, lin)
-    if (lane == 0) {
+    if (is_root) {
         rpos = {A.pos[env * 3], A.pos[env * 3 + 1], A.pos[env * 3 + 2]};
         const float4 t = *reinterpret_cast<const float4*>(A.quat + env * 4);
         rquat = {t.x, t.y, t.z, t.w};
@@ -219,7 +227,7 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
 
     for (int step = 0; step < A.substeps; ++step) {
         const bool last = (step == A.substeps - 1);
-        const float root_z = shfl(rpos.z, 0);
+        const float root_z = shfl(rpos.z, ebase);
 
         // ---- pass 1: kinematics by POINTER JUMPING (log2(depth) rounds instead of depth levels) -------
         // Every lane starts with its transform relative to its parent, T_i = (R_i, p_i); round k
@@ -239,7 +247,7 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
             R = qmat(ql);
         }
         for (int k = 0; k < M.jump_rounds; ++k) {
-            const int an = active ? M.anc[k][li] : lane;
+            const int an = active ? ebase + M.anc[k][li] : lane;
             M3 Ra;
             V3 pa;
 #pragma unroll
@@ -258,7 +266,7 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
             const M3 R0l = qmat(rquat);
             M3 R0;
 #pragma unroll
-            for (int j = 0; j < 9; ++j) R0.m[j] = shfl(R0l.m[j], 0);
+            for (int j = 0; j < 9; ++j) R0.m[j] = shfl(R0l.m[j], ebase);
             p = mulv(R0, p);
             M3 Rn;
 #pragma unroll
@@ -278,7 +286,7 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
             for (int k = 0; k < 6; ++k) v.a[k] = s.a[k] * qd;
         }
         for (int k = 0; k < M.jump_rounds; ++k) {
-            const int an = active ? M.anc[k][li] : lane;
+            const int an = active ? ebase + M.anc[k][li] : lane;
 #pragma unroll
             for (int j = 0; j < 6; ++j) {
                 const float t = shfl(v.a[j], an);
@@ -288,7 +296,7 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
         V6 v0;
 #pragma unroll
         for (int j = 0; j < 6; ++j) {
-            v0.a[j] = shfl(rvel.a[j], 0);
+            v0.a[j] = shfl(rvel.a[j], ebase);
             v.a[j] += v0.a[j];
         }
         // velocity-product accelerations c_i and their path sums b_i (b_root = -(0, w0 x v0))
@@ -301,7 +309,7 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
         }
         V6 b = c;
         for (int k = 0; k < M.jump_rounds; ++k) {
-            const int an = active ? M.anc[k][li] : lane;
+            const int an = active ? ebase + M.anc[k][li] : lane;
 #pragma unroll
             for (int j = 0; j < 6; ++j) {
                 const float t = shfl(b.a[j], an);
@@ -427,7 +435,7 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
             for (int k = 0; k < nch; ++k) {
                 const int ch = (level == l - 1) ? M.child[k][li] : -1;
                 const bool valid = ch >= 0;
-                const int src = valid ? ch : lane;
+                const int src = valid ? ebase + ch : lane;
 #pragma unroll
                 for (int j = 0; j < 21; ++j) {
                     const float t = shfl(IA.a[j], src);
@@ -441,9 +449,9 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
             }
         }
 
-        // ---- root: solve I^A a = -p^A (6x6 Cholesky, lane 0) ----------------------------------------
+        // ---- root: solve I^A a = -p^A (6x6 Cholesky, root lane) -------------------------------------
         V6 a = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
-        if (lane == 0) {
+        if (is_root) {
             float Lm[6][6];
 #pragma unroll
             for (int i = 0; i < 6; ++i)
@@ -527,7 +535,7 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
             qd = fminf(fmaxf(qd, -M.max_qd), M.max_qd);
             q = fmaf(dt, qd, q);
         }
-        if (lane == 0) {
+        if (is_root) {
             const V3 w0 = ang(rvel), v0 = lin(rvel);
             const V3 vdot = lin(a) + cross(w0, v0);  // classical acceleration of the root origin
             float damp = 1.f - dt * M.ang_damp;
@@ -551,18 +559,21 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
     // ---- non-finite guard: park the env below the termination height so K1 flags it for reset ----
     bool bad = false;
     if (is_joint) bad = !(isfinite(q) && isfinite(qd));
-    if (lane == 0) {
+    if (is_root) {
         bad = !(isfinite(rpos.x) && isfinite(rpos.y) && isfinite(rpos.z) && isfinite(rquat.w) && isfinite(rquat.x) &&
                 isfinite(rquat.y) && isfinite(rquat.z));
 #pragma unroll
         for (int k = 0; k < 6; ++k) bad = bad || !isfinite(rvel.a[k]);
     }
-    if (__any_sync(0xffffffffu, bad)) {
+    const unsigned bad_lanes = __ballot_sync(0xffffffffu, bad);
+    const unsigned env_lanes = active ? (((L >= 32 ? 0u : (1u << L)) - 1u) << ebase) : 0u;
+    if (bad_lanes & env_lanes) {  // any lane of THIS env
         q = 0.f; qd = 0.f;
         rpos = {0.f, 0.f, -1.f};
         rquat = {1.f, 0.f, 0.f, 0.f};
         rvel = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
-        if (A.sens != nullptr && lane < M.num_sensors * 6) A.sens[env * M.num_sensors * 6 + lane] = 0.f;
+        if (A.sens != nullptr)
+            for (int k = li; k < M.num_sensors * 6; k += L) A.sens[env * M.num_sensors * 6 + k] = 0.f;
     }
 
     // ---- store state ---------------------------------------------------------------------------------------
@@ -570,7 +581,7 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
         A.q[env * D + dofi] = q;
         A.qd[env * D + dofi] = qd;
     }
-    if (lane == 0) {
+    if (is_root) {
         A.pos[env * 3] = rpos.x; A.pos[env * 3 + 1] = rpos.y; A.pos[env * 3 + 2] = rpos.z;
         *reinterpret_cast<float4*>(A.quat + env * 4) = make_float4(rquat.w, rquat.x, rquat.y, rquat.z);
         float* vv = A.vel + env * 6;
@@ -608,9 +619,15 @@ int k2_step(const OigeModel* model, const OigeTaskParams* P, const OigeState* st
     if (reinterpret_cast<uintptr_t>(A.quat) & 15u) return fail(OIGE_E_ALIGN, "articulation_step: root_quat not 16B aligned");
     if (model->num_sensors > 0 && P->num_sensors != model->num_sensors)
         return fail(OIGE_E_SHAPE, "articulation_step: params.num_sensors %d != model %d", P->num_sensors, model->num_sensors);
-    const unsigned blocks = (unsigned)((n + kWarpsPerBlock - 1) / kWarpsPerBlock);
-    articulation_step_kernel<<<blocks, kWarpsPerBlock * 32, 0, stream>>>(
-        reinterpret_cast<const DevModel*>(model->dev_table), *P, A);
+    const int pack = 32 / model->num_links;
+    const long long warps = (n + pack - 1) / pack;
+    const unsigned blocks = (unsigned)((warps + kWarpsPerBlock - 1) / kWarpsPerBlock);
+    if (pack > 1)
+        articulation_step_kernel<true><<<blocks, kWarpsPerBlock * 32, 0, stream>>>(
+            reinterpret_cast<const DevModel*>(model->dev_table), *P, A);
+    else
+        articulation_step_kernel<false><<<blocks, kWarpsPerBlock * 32, 0, stream>>>(
+            reinterpret_cast<const DevModel*>(model->dev_table), *P, A);
     count_launch();
     return check_launch("articulation_step_kernel");
 }
@@ -654,6 +671,7 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
     for (int i = 0; i < 32; ++i) h->anc[0][i] = (i < L && i > 0) ? h->parent[i] : (i < L ? 0 : i);
     for (int k = 1; k < kMaxJump; ++k)
         for (int i = 0; i < 32; ++i) h->anc[k][i] = i < L ? h->anc[k - 1][h->anc[k - 1][i]] : i;
+    h->pack = 32 / L;  // environments carried side by side by one warp
     h->jump_rounds = 0;
     while ((1 << h->jump_rounds) < h->max_depth) ++h->jump_rounds;
     for (int i = 0; i < L; ++i) {
