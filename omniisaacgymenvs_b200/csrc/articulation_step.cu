@@ -22,6 +22,7 @@
 // Tensor cores are not used: the per-env matrices are 6x6 and the work is a latency-bound tree
 // recursion, not a dense contraction.
 #include <math.h>
+#include <stdlib.h>
 
 #include "oige_common.cuh"
 
@@ -30,6 +31,7 @@ struct OigeModel {
     int num_links;
     int num_dof;
     int num_sensors;
+    int tpe_ok;
 };
 
 namespace oige {
@@ -39,16 +41,23 @@ constexpr int kWarpsPerBlock = 4;
 constexpr int kMaxLevels = 16;
 constexpr int kMaxChildren = 4;
 constexpr int kMaxJump = 4;  // 2^4 = 16 >= kMaxLevels
+constexpr int kMaxSlots = 8;
+constexpr long long kTpeMinEnvs = 8192;  // measured crossover, see profiles/
+constexpr int kHasHeavy = 1, kIsHead = 2, kFirstLight = 4;
 
 struct DevModel {
     int num_links, num_spheres, num_sensors, max_depth;
-    int max_sph_per_link, jump_rounds, pack, pad2;
+    int max_sph_per_link, jump_rounds, pack, tpe_ok;
     int parent[32];
     int dof[32];
     int level[32];
     int child[kMaxChildren][32];
     int maxch_at_level[kMaxLevels];  // max #children over parents at this level
     int anc[kMaxJump][32];           // 2^k-th ancestor (clamped at the root) for pointer jumping
+    // thread-per-env kernel: post-order (heavy child last) and hand-over slots of the light children
+    int order2[32];
+    int tflags[32];                  // kHasHeavy | kIsHead | kFirstLight
+    int light_slot[32];              // slot of a link that has light children, else -1
     int sph_start[32];
     int sph_count[32];
     int sensor_of_link[32];
@@ -166,6 +175,181 @@ struct K2Args {
     int substeps;
     float dt;
 };
+
+// ---- building blocks shared by the warp-per-env and the thread-per-env kernels ---------------------
+
+// World-frame spatial inertia of link i about O (symmetric 6x6) and its bias force
+// p = v x* (I v) - gravity wrench.  R, p: link frame in the O-frame; v: spatial velocity.
+__device__ __forceinline__ void link_inertia_bias(const DevModel& M, int li, const M3& R, V3 p, const V6& v, V3 grav,
+                                                  S6& IA, V6& pA) {
+    const float m = M.mass[li];
+    const V3 cl = {M.com[0][li], M.com[1][li], M.com[2][li]};
+    const V3 cw = p + mulv(R, cl);
+    // Ic_world = R Iloc R^T
+    const float ixx = M.inertia[0][li], iyy = M.inertia[1][li], izz = M.inertia[2][li];
+    const float ixy = M.inertia[3][li], ixz = M.inertia[4][li], iyz = M.inertia[5][li];
+    float T[9];  // T = R * Iloc
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+        const float r0 = R.m[3 * r], r1 = R.m[3 * r + 1], r2 = R.m[3 * r + 2];
+        T[3 * r + 0] = r0 * ixx + r1 * ixy + r2 * ixz;
+        T[3 * r + 1] = r0 * ixy + r1 * iyy + r2 * iyz;
+        T[3 * r + 2] = r0 * ixz + r1 * iyz + r2 * izz;
+    }
+    const float cc = dot(cw, cw);
+    const float cv[3] = {cw.x, cw.y, cw.z};
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = i; j < 3; ++j) {
+            float icw = T[3 * i] * R.m[3 * j] + T[3 * i + 1] * R.m[3 * j + 1] + T[3 * i + 2] * R.m[3 * j + 2];
+            icw += m * ((i == j ? cc : 0.f) - cv[i] * cv[j]);
+            IA.a[sidx(i, j)] = icw;
+        }
+    // ang-lin block m*[c]x, lin-lin block m*1
+    IA.a[sidx(0, 3)] = 0.f;         IA.a[sidx(0, 4)] = -m * cw.z;  IA.a[sidx(0, 5)] = m * cw.y;
+    IA.a[sidx(1, 3)] = m * cw.z;    IA.a[sidx(1, 4)] = 0.f;        IA.a[sidx(1, 5)] = -m * cw.x;
+    IA.a[sidx(2, 3)] = -m * cw.y;   IA.a[sidx(2, 4)] = m * cw.x;   IA.a[sidx(2, 5)] = 0.f;
+    IA.a[sidx(3, 3)] = m; IA.a[sidx(3, 4)] = 0.f; IA.a[sidx(3, 5)] = 0.f;
+    IA.a[sidx(4, 4)] = m; IA.a[sidx(4, 5)] = 0.f;
+    IA.a[sidx(5, 5)] = m;
+    const V6 h = s6mul(IA, v);
+    const V3 w = ang(v), vl = lin(v);
+    const V3 ba = cross(w, ang(h)) + cross(vl, lin(h));
+    const V3 bl = cross(w, lin(h));
+    const V3 fg = m * grav;
+    const V3 tg = cross(cw, fg);
+    pA = mk6(ba - tg, bl - fg);
+}
+
+// Adds the linearly-implicit ground contacts of link li: P^T C P to the inertia, -wrench(F0) to the bias.
+// `nloop` = loop bound (uniform across a warp-per-env warp: the model's max spheres per link).
+__device__ __forceinline__ void link_contacts(const DevModel& M, int li, const M3& R, V3 p, const V6& v, const V6& b,
+                                              float root_z, float dt, S6& IA, V6& pA, int nloop = -1) {
+    const int s0 = M.sph_start[li];
+    const int sc = M.sph_count[li];
+    const int n = nloop < 0 ? sc : nloop;
+    for (int k = 0; k < n; ++k) {
+        Contact ct;
+        if (k < sc && contact_eval(M, s0 + k, R, p, v, b, root_z, dt, ct)) {
+            const V3 tq = cross(ct.r, ct.F0);
+            pA.a[0] -= tq.x; pA.a[1] -= tq.y; pA.a[2] -= tq.z;
+            pA.a[3] -= ct.F0.x; pA.a[4] -= ct.F0.y; pA.a[5] -= ct.F0.z;
+            // I += sum_k C_k u_k u_k^T with u_k = (r x e_k, e_k)
+            const float Cd[3] = {ct.C.x, ct.C.y, ct.C.z};
+            const float u[3][3] = {{0.f, ct.r.z, -ct.r.y}, {-ct.r.z, 0.f, ct.r.x}, {ct.r.y, -ct.r.x, 0.f}};
+#pragma unroll
+            for (int e = 0; e < 3; ++e) {
+#pragma unroll
+                for (int i = 0; i < 3; ++i) {
+#pragma unroll
+                    for (int j = i; j < 3; ++j) IA.a[sidx(i, j)] = fmaf(Cd[e] * u[e][i], u[e][j], IA.a[sidx(i, j)]);
+                    IA.a[sidx(i, 3 + e)] = fmaf(Cd[e], u[e][i], IA.a[sidx(i, 3 + e)]);
+                }
+                IA.a[sidx(3 + e, 3 + e)] += Cd[e];
+            }
+        }
+    }
+}
+
+// Joint-space force at the end-of-step position (actuation + passive spring/damper + limit penalty)
+// and the implicit diagonal term armature + dt D + dt^2 K.
+__device__ __forceinline__ void joint_force(const DevModel& M, int li, float q, float qd, float effort, float dt,
+                                            float& tau0, float& dextra) {
+    const float Ks = M.stiffness[li], Dj = M.damping[li];
+    const float qn = fmaf(dt, qd, q);  // position the springs see at the end of the step
+    float Kimp = Ks, Dimp = Dj;
+    tau0 = effort - Ks * (qn - M.sref[li]) - Dj * qd;
+    const float lo = M.lo[li], hi = M.hi[li];
+    if (q < lo) {
+        tau0 += -M.k_lim * (qn - lo) - M.d_lim * qd;
+        Kimp += M.k_lim; Dimp += M.d_lim;
+    } else if (q > hi) {
+        tau0 += -M.k_lim * (qn - hi) - M.d_lim * qd;
+        Kimp += M.k_lim; Dimp += M.d_lim;
+    }
+    dextra = M.armature[li] + dt * (Dimp + dt * Kimp);
+}
+
+// a = -(I^A)^-1 p^A for the floating root: 6x6 Cholesky in registers.
+__device__ __forceinline__ void chol6_solve(const S6& IA, const V6& pA, V6& a) {
+    float Lm[6][6];
+#pragma unroll
+    for (int i = 0; i < 6; ++i)
+#pragma unroll
+        for (int j = 0; j <= i; ++j) Lm[i][j] = IA.a[sidx(j, i)];
+    float invd[6];
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+        float dj = Lm[j][j];
+#pragma unroll
+        for (int k = 0; k < j; ++k) dj = fmaf(-Lm[j][k], Lm[j][k], dj);
+        const float ljj = sqrtf(dj);
+        invd[j] = 1.f / ljj;
+        Lm[j][j] = ljj;
+#pragma unroll
+        for (int i = j + 1; i < 6; ++i) {
+            float t = Lm[i][j];
+#pragma unroll
+            for (int k = 0; k < j; ++k) t = fmaf(-Lm[i][k], Lm[j][k], t);
+            Lm[i][j] = t * invd[j];
+        }
+    }
+    float y[6];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+        float t = -pA.a[i];
+#pragma unroll
+        for (int k = 0; k < i; ++k) t = fmaf(-Lm[i][k], y[k], t);
+        y[i] = t * invd[i];
+    }
+#pragma unroll
+    for (int i = 5; i >= 0; --i) {
+        float t = y[i];
+#pragma unroll
+        for (int k = i + 1; k < 6; ++k) t = fmaf(-Lm[k][i], a.a[k], t);
+        a.a[i] = t * invd[i];
+    }
+}
+
+// Net ground wrench on link li (force, torque about the link origin) in the link frame -> out[6].
+__device__ __forceinline__ void sensor_wrench(const DevModel& M, int li, const M3& R, V3 p, const V6& v, const V6& b,
+                                              const V6& a, float root_z, float dt, float* out) {
+    V3 F = {0.f, 0.f, 0.f}, Tq = {0.f, 0.f, 0.f};
+    const int s0 = M.sph_start[li], sc = M.sph_count[li];
+    for (int k = 0; k < sc; ++k) {
+        Contact ct;
+        if (contact_eval(M, s0 + k, R, p, v, b, root_z, dt, ct)) {
+            const V3 ap = lin(a) + cross(ang(a), ct.r);
+            const V3 f = {ct.F0.x - ct.C.x * ap.x, ct.F0.y - ct.C.y * ap.y, ct.F0.z - ct.C.z * ap.z};
+            F = F + f;
+            Tq = Tq + cross(ct.r - p, f);
+        }
+    }
+    const V3 Fl = mulTv(R, F), Tl = mulTv(R, Tq);
+    out[0] = Fl.x; out[1] = Fl.y; out[2] = Fl.z; out[3] = Tl.x; out[4] = Tl.y; out[5] = Tl.z;
+}
+
+// Semi-implicit Euler for the floating root (exponential map for the quaternion).
+__device__ __forceinline__ void integrate_root(const DevModel& M, const V6& a, float dt, V3& rpos, Q4& rquat, V6& rvel) {
+    const V3 w0 = ang(rvel), v0 = lin(rvel);
+    const V3 vdot = lin(a) + cross(w0, v0);  // classical acceleration of the root origin
+    float damp = 1.f - dt * M.ang_damp;
+    damp = damp < 0.f ? 0.f : damp;
+    const V3 w1 = damp * (w0 + dt * ang(a));
+    const V3 v1 = v0 + dt * vdot;
+    rvel = mk6(w1, v1);
+    rpos = rpos + dt * v1;
+    const float wn = sqrtf(dot(w1, w1));
+    const float th = 0.5f * dt * wn;
+    float sh, ch;
+    sincosf(th, &sh, &ch);
+    const float k = wn > 1e-9f ? sh / wn : 0.5f * dt;
+    const Q4 dq = {ch, k * w1.x, k * w1.y, k * w1.z};
+    const Q4 nq = qmul(dq, rquat);
+    const float inv = rsqrtf(nq.w * nq.w + nq.x * nq.x + nq.y * nq.y + nq.z * nq.z);
+    rquat = {nq.w * inv, nq.x * inv, nq.y * inv, nq.z * inv};
+}
 
 template <bool PACKED>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
@@ -324,90 +508,12 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
         // ---- per-link spatial inertia, bias force, contacts (all lanes in parallel) -------------
         S6 IA;
         V6 pA;
-        {
-            const float m = active ? M.mass[li] : 0.f;
-            const V3 cl = {M.com[0][li], M.com[1][li], M.com[2][li]};
-            const V3 cw = p + mulv(R, cl);
-            // Ic_world = R diag/sym(I) R^T
-            const float ixx = M.inertia[0][li], iyy = M.inertia[1][li], izz = M.inertia[2][li];
-            const float ixy = M.inertia[3][li], ixz = M.inertia[4][li], iyz = M.inertia[5][li];
-            float T[9];  // T = R * Iloc
-#pragma unroll
-            for (int r = 0; r < 3; ++r) {
-                const float r0 = R.m[3 * r], r1 = R.m[3 * r + 1], r2 = R.m[3 * r + 2];
-                T[3 * r + 0] = r0 * ixx + r1 * ixy + r2 * ixz;
-                T[3 * r + 1] = r0 * ixy + r1 * iyy + r2 * iyz;
-                T[3 * r + 2] = r0 * ixz + r1 * iyz + r2 * izz;
-            }
-            const float cc = dot(cw, cw);
-            const float cv[3] = {cw.x, cw.y, cw.z};
-#pragma unroll
-            for (int i = 0; i < 3; ++i)
-#pragma unroll
-                for (int j = i; j < 3; ++j) {
-                    float icw = T[3 * i] * R.m[3 * j] + T[3 * i + 1] * R.m[3 * j + 1] + T[3 * i + 2] * R.m[3 * j + 2];
-                    icw += m * ((i == j ? cc : 0.f) - cv[i] * cv[j]);
-                    IA.a[sidx(i, j)] = active ? icw : 0.f;
-                }
-            // ang-lin block m*[c]x, lin-lin block m*1
-            IA.a[sidx(0, 3)] = 0.f;         IA.a[sidx(0, 4)] = -m * cw.z;  IA.a[sidx(0, 5)] = m * cw.y;
-            IA.a[sidx(1, 3)] = m * cw.z;    IA.a[sidx(1, 4)] = 0.f;        IA.a[sidx(1, 5)] = -m * cw.x;
-            IA.a[sidx(2, 3)] = -m * cw.y;   IA.a[sidx(2, 4)] = m * cw.x;   IA.a[sidx(2, 5)] = 0.f;
-            IA.a[sidx(3, 3)] = m; IA.a[sidx(3, 4)] = 0.f; IA.a[sidx(3, 5)] = 0.f;
-            IA.a[sidx(4, 4)] = m; IA.a[sidx(4, 5)] = 0.f;
-            IA.a[sidx(5, 5)] = m;
-            // bias: v x* (I v) - gravity wrench
-            const V6 h = s6mul(IA, v);
-            const V3 w = ang(v), vl = lin(v);
-            const V3 ba = cross(w, ang(h)) + cross(vl, lin(h));
-            const V3 bl = cross(w, lin(h));
-            const V3 fg = m * grav;
-            const V3 tg = cross(cw, fg);
-            pA = mk6(ba - tg, bl - fg);
-        }
-        {
-            const int s0 = active ? M.sph_start[li] : 0;
-            const int sc = active ? M.sph_count[li] : 0;
-            for (int k = 0; k < M.max_sph_per_link; ++k) {
-                Contact ct;
-                if (k < sc && contact_eval(M, s0 + k, R, p, v, b, root_z, dt, ct)) {
-                    const V3 tq = cross(ct.r, ct.F0);
-                    pA.a[0] -= tq.x; pA.a[1] -= tq.y; pA.a[2] -= tq.z;
-                    pA.a[3] -= ct.F0.x; pA.a[4] -= ct.F0.y; pA.a[5] -= ct.F0.z;
-                    // I += sum_k C_k u_k u_k^T with u_k = (r x e_k, e_k)
-                    const float Cd[3] = {ct.C.x, ct.C.y, ct.C.z};
-                    const float u[3][3] = {{0.f, ct.r.z, -ct.r.y}, {-ct.r.z, 0.f, ct.r.x}, {ct.r.y, -ct.r.x, 0.f}};
-#pragma unroll
-                    for (int e = 0; e < 3; ++e) {
-#pragma unroll
-                        for (int i = 0; i < 3; ++i) {
-#pragma unroll
-                            for (int j = i; j < 3; ++j) IA.a[sidx(i, j)] = fmaf(Cd[e] * u[e][i], u[e][j], IA.a[sidx(i, j)]);
-                            IA.a[sidx(i, 3 + e)] = fmaf(Cd[e], u[e][i], IA.a[sidx(i, 3 + e)]);
-                        }
-                        IA.a[sidx(3 + e, 3 + e)] += Cd[e];
-                    }
-                }
-            }
-        }
+        link_inertia_bias(M, li, R, p, v, grav, IA, pA);
+        link_contacts(M, li, R, p, v, b, root_z, dt, IA, pA, M.max_sph_per_link);
 
         // ---- joint-space force and implicit diagonal ----------------------------------------------
         float tau0 = 0.f, dextra = 1.f;
-        if (is_joint) {
-            const float Ks = M.stiffness[li], Dj = M.damping[li];
-            const float qn = fmaf(dt, qd, q);  // position the springs see at the end of the step
-            float Kimp = Ks, Dimp = Dj;
-            tau0 = effort - Ks * (qn - M.sref[li]) - Dj * qd;
-            const float lo = M.lo[li], hi = M.hi[li];
-            if (q < lo) {
-                tau0 += -M.k_lim * (qn - lo) - M.d_lim * qd;
-                Kimp += M.k_lim; Dimp += M.d_lim;
-            } else if (q > hi) {
-                tau0 += -M.k_lim * (qn - hi) - M.d_lim * qd;
-                Kimp += M.k_lim; Dimp += M.d_lim;
-            }
-            dextra = M.armature[li] + dt * (Dimp + dt * Kimp);
-        }
+        if (is_joint) joint_force(M, li, q, qd, effort, dt, tau0, dextra);
 
         // ---- pass 2: articulated inertia, bottom-up -------------------------------------------------
         V6 U = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
@@ -451,45 +557,7 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
 
         // ---- root: solve I^A a = -p^A (6x6 Cholesky, root lane) -------------------------------------
         V6 a = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
-        if (is_root) {
-            float Lm[6][6];
-#pragma unroll
-            for (int i = 0; i < 6; ++i)
-#pragma unroll
-                for (int j = 0; j <= i; ++j) Lm[i][j] = IA.a[sidx(j, i)];
-            float invd[6];
-#pragma unroll
-            for (int j = 0; j < 6; ++j) {
-                float dj = Lm[j][j];
-#pragma unroll
-                for (int k = 0; k < j; ++k) dj = fmaf(-Lm[j][k], Lm[j][k], dj);
-                const float ljj = sqrtf(dj);
-                invd[j] = 1.f / ljj;
-                Lm[j][j] = ljj;
-#pragma unroll
-                for (int i = j + 1; i < 6; ++i) {
-                    float t = Lm[i][j];
-#pragma unroll
-                    for (int k = 0; k < j; ++k) t = fmaf(-Lm[i][k], Lm[j][k], t);
-                    Lm[i][j] = t * invd[j];
-                }
-            }
-            float y[6];
-#pragma unroll
-            for (int i = 0; i < 6; ++i) {
-                float t = -pA.a[i];
-#pragma unroll
-                for (int k = 0; k < i; ++k) t = fmaf(-Lm[i][k], y[k], t);
-                y[i] = t * invd[i];
-            }
-#pragma unroll
-            for (int i = 5; i >= 0; --i) {
-                float t = y[i];
-#pragma unroll
-                for (int k = i + 1; k < 6; ++k) t = fmaf(-Lm[k][i], a.a[k], t);
-                a.a[i] = t * invd[i];
-            }
-        }
+        if (is_root) chol6_solve(IA, pA, a);
 
         // ---- pass 3: accelerations, top-down -----------------------------------------------------------
         float qdd = 0.f;
@@ -511,22 +579,7 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
         // ---- foot force sensors: net ground wrench on the sensor link, in the link frame ----------------
         if (last && A.sens != nullptr) {
             const int sidx_ = active ? M.sensor_of_link[li] : -1;
-            if (sidx_ >= 0) {
-                V3 F = {0.f, 0.f, 0.f}, Tq = {0.f, 0.f, 0.f};
-                const int s0 = M.sph_start[li], sc = M.sph_count[li];
-                for (int k = 0; k < sc; ++k) {
-                    Contact ct;
-                    if (contact_eval(M, s0 + k, R, p, v, b, root_z, dt, ct)) {
-                        const V3 ap = lin(a) + cross(ang(a), ct.r);
-                        const V3 f = {ct.F0.x - ct.C.x * ap.x, ct.F0.y - ct.C.y * ap.y, ct.F0.z - ct.C.z * ap.z};
-                        F = F + f;
-                        Tq = Tq + cross(ct.r - p, f);
-                    }
-                }
-                const V3 Fl = mulTv(R, F), Tl = mulTv(R, Tq);
-                float* o = A.sens + (env * M.num_sensors + sidx_) * 6;
-                o[0] = Fl.x; o[1] = Fl.y; o[2] = Fl.z; o[3] = Tl.x; o[4] = Tl.y; o[5] = Tl.z;
-            }
+            if (sidx_ >= 0) sensor_wrench(M, li, R, p, v, b, a, root_z, dt, A.sens + (env * M.num_sensors + sidx_) * 6);
         }
 
         // ---- integrate (semi-implicit Euler) ----------------------------------------------------------------
@@ -535,25 +588,7 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
             qd = fminf(fmaxf(qd, -M.max_qd), M.max_qd);
             q = fmaf(dt, qd, q);
         }
-        if (is_root) {
-            const V3 w0 = ang(rvel), v0 = lin(rvel);
-            const V3 vdot = lin(a) + cross(w0, v0);  // classical acceleration of the root origin
-            float damp = 1.f - dt * M.ang_damp;
-            damp = damp < 0.f ? 0.f : damp;
-            const V3 w1 = damp * (w0 + dt * ang(a));
-            const V3 v1 = v0 + dt * vdot;
-            rvel = mk6(w1, v1);
-            rpos = rpos + dt * v1;
-            const float wn = sqrtf(dot(w1, w1));
-            const float th = 0.5f * dt * wn;
-            float sh, ch;
-            sincosf(th, &sh, &ch);
-            const float k = wn > 1e-9f ? sh / wn : 0.5f * dt;
-            Q4 dq = {ch, k * w1.x, k * w1.y, k * w1.z};
-            Q4 nq = qmul(dq, rquat);
-            const float inv = rsqrtf(nq.w * nq.w + nq.x * nq.x + nq.y * nq.y + nq.z * nq.z);
-            rquat = {nq.w * inv, nq.x * inv, nq.y * inv, nq.z * inv};
-        }
+        if (is_root) integrate_root(M, a, dt, rpos, rquat, rvel);
     }
 
     // ---- non-finite guard: park the env below the termination height so K1 flags it for reset ----
@@ -590,6 +625,287 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
     }
 }
 
+// ================================================================================================
+// K2-T: the same articulation step with ONE THREAD PER ENVIRONMENT (lane = env).
+//
+// The warp-per-env kernel above is latency-optimal for few environments, but a lane-per-link warp
+// issues every instruction of the tree recursion for all 32 lanes while 1-4 links are active, so its
+// issue cost is ~4500 warp-instructions per env-substep.  Here every lane does useful work: a warp
+// advances 32 envs at ~17k instructions per substep (~530 per env).  All lanes of a warp visit the
+// links in the same order, so the model-table reads are shared-memory broadcasts and the control
+// flow is uniform except for contact activation.  Per-link intermediates that must survive between
+// the passes live in per-thread local memory (interleaved by the hardware, hence coalesced):
+//   fk[i]  = R(9) p(3) v(6) b(6)              forward kinematics, written in pass 1, read in pass 2
+//   pu[i]  = U(6) 1/d u s(6) c(6)             written in pass 2, read in pass 3
+// Articulated inertias travel up a heavy path in REGISTERS (links are visited in post-order with the
+// heavy child last, so a link directly follows its heavy child); only light children (chain heads)
+// go through a small slot array.  Same equations, same contact model, same integrator as above.
+// ================================================================================================
+template <int MAXL>
+__global__ void __launch_bounds__(128)
+articulation_step_tpe_kernel(const DevModel* __restrict__ gmodel, const __grid_constant__ OigeTaskParams P,
+                             const __grid_constant__ K2Args A) {
+    __shared__ __align__(16) DevModel M;
+    {
+        const int4* src = reinterpret_cast<const int4*>(gmodel);
+        int4* dst = reinterpret_cast<int4*>(&M);
+        for (int i = threadIdx.x; i < (int)(sizeof(DevModel) / 16); i += blockDim.x) dst[i] = src[i];
+    }
+    __syncthreads();
+    const long long env = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (env >= A.n) return;
+
+    const int L = M.num_links, D = P.num_dof;
+    const float dt = A.dt;
+    const V3 grav = {M.gravity[0], M.gravity[1], M.gravity[2]};
+
+    float fk[MAXL][24];
+    float pu[MAXL][20];
+    float slotI[kMaxSlots][27];
+    float slotA[kMaxSlots][6];
+    float qv[MAXL], qdv[MAXL], eff[MAXL];
+
+    for (int i = 1; i < L; ++i) {
+        const int d = M.dof[i];
+        qv[i] = A.q[env * D + d];
+        qdv[i] = A.qd[env * D + d];
+        eff[i] = A.actions[env * D + d] * P.joint_gears[d] * P.power_scale;  // locomotion.py:109
+    }
+    V3 rpos = {A.pos[env * 3], A.pos[env * 3 + 1], A.pos[env * 3 + 2]};
+    Q4 rquat;
+    {
+        const float4 t = *reinterpret_cast<const float4*>(A.quat + env * 4);
+        rquat = {t.x, t.y, t.z, t.w};
+    }
+    V6 rvel;
+    {
+        const float* vv = A.vel + env * 6;
+        rvel = {{vv[3], vv[4], vv[5], vv[0], vv[1], vv[2]}};
+    }
+
+    for (int step = 0; step < A.substeps; ++step) {
+        const bool last = (step == A.substeps - 1);
+        const float root_z = rpos.z;
+        const M3 R0 = qmat(rquat);
+        V6 b0;
+        {
+            const V3 wxv = cross(ang(rvel), lin(rvel));
+            b0 = {{0.f, 0.f, 0.f, -wxv.x, -wxv.y, -wxv.z}};
+        }
+        // ---- pass 1: kinematics in index order (parent[i] < i) ----------------------------------
+        for (int i = 1; i < L; ++i) {
+            const int pa = M.parent[i];
+            M3 Rp;
+            V3 pp;
+            V6 pv, pb;
+            if (pa == 0) {
+                Rp = R0; pp = {0.f, 0.f, 0.f}; pv = rvel; pb = b0;
+            } else {
+#pragma unroll
+                for (int k = 0; k < 9; ++k) Rp.m[k] = fk[pa][k];
+                pp = {fk[pa][9], fk[pa][10], fk[pa][11]};
+#pragma unroll
+                for (int k = 0; k < 6; ++k) { pv.a[k] = fk[pa][12 + k]; pb.a[k] = fk[pa][18 + k]; }
+            }
+            const V3 axis = {M.axis[0][i], M.axis[1][i], M.axis[2][i]};
+            float sh, ch;
+            sincosf(0.5f * qv[i], &sh, &ch);
+            const Q4 ql = qmul(Q4{M.jquat[0][i], M.jquat[1][i], M.jquat[2][i], M.jquat[3][i]},
+                               Q4{ch, sh * axis.x, sh * axis.y, sh * axis.z});
+            const M3 Rl = qmat(ql);
+            const V3 p = pp + mulv(Rp, V3{M.jpos[0][i], M.jpos[1][i], M.jpos[2][i]});
+            M3 R;
+#pragma unroll
+            for (int r = 0; r < 3; ++r)
+#pragma unroll
+                for (int cc = 0; cc < 3; ++cc)
+                    R.m[3 * r + cc] = Rp.m[3 * r] * Rl.m[cc] + Rp.m[3 * r + 1] * Rl.m[3 + cc] + Rp.m[3 * r + 2] * Rl.m[6 + cc];
+            const V3 aw = mulv(R, axis);
+            const V6 s = mk6(aw, cross(p, aw));
+            const float qd = qdv[i];
+            V6 v;
+#pragma unroll
+            for (int k = 0; k < 6; ++k) v.a[k] = fmaf(s.a[k], qd, pv.a[k]);
+            const V3 w = ang(v), vl = lin(v);
+            const V3 ca = cross(w, aw);
+            const V3 cl = cross(w, lin(s)) + cross(vl, aw);
+#pragma unroll
+            for (int k = 0; k < 9; ++k) fk[i][k] = R.m[k];
+            fk[i][9] = p.x; fk[i][10] = p.y; fk[i][11] = p.z;
+#pragma unroll
+            for (int k = 0; k < 6; ++k) fk[i][12 + k] = v.a[k];
+            fk[i][18] = pb.a[0] + qd * ca.x; fk[i][19] = pb.a[1] + qd * ca.y; fk[i][20] = pb.a[2] + qd * ca.z;
+            fk[i][21] = pb.a[3] + qd * cl.x; fk[i][22] = pb.a[4] + qd * cl.y; fk[i][23] = pb.a[5] + qd * cl.z;
+        }
+
+        // ---- pass 2: articulated inertia, post-order with the heavy child last ---------------------
+        S6 carryI;
+        V6 carryP;
+#pragma unroll
+        for (int k = 0; k < 21; ++k) carryI.a[k] = 0.f;
+#pragma unroll
+        for (int k = 0; k < 6; ++k) carryP.a[k] = 0.f;
+        for (int k2 = 0; k2 <= L - 1; ++k2) {
+            const int i = (k2 < L - 1) ? M.order2[k2] : 0;  // the root closes the sweep
+            M3 R;
+            V3 p;
+            V6 v, b;
+            if (i == 0) {
+                R = R0; p = {0.f, 0.f, 0.f}; v = rvel; b = b0;
+            } else {
+#pragma unroll
+                for (int k = 0; k < 9; ++k) R.m[k] = fk[i][k];
+                p = {fk[i][9], fk[i][10], fk[i][11]};
+#pragma unroll
+                for (int k = 0; k < 6; ++k) { v.a[k] = fk[i][12 + k]; b.a[k] = fk[i][18 + k]; }
+            }
+            S6 IA;
+            V6 pA;
+            link_inertia_bias(M, i, R, p, v, grav, IA, pA);
+            link_contacts(M, i, R, p, v, b, root_z, dt, IA, pA);
+            const int flags = M.tflags[i];
+            if (flags & kHasHeavy) {
+#pragma unroll
+                for (int k = 0; k < 21; ++k) IA.a[k] += carryI.a[k];
+#pragma unroll
+                for (int k = 0; k < 6; ++k) pA.a[k] += carryP.a[k];
+            }
+            const int myslot = M.light_slot[i];
+            if (myslot >= 0) {  // light children finished earlier and left their I^a here
+#pragma unroll
+                for (int k = 0; k < 21; ++k) IA.a[k] += slotI[myslot][k];
+#pragma unroll
+                for (int k = 0; k < 6; ++k) pA.a[k] += slotI[myslot][21 + k];
+            }
+            if (i == 0) {
+                carryI = IA; carryP = pA;  // root: solved below
+                break;
+            }
+            const V3 axis = {M.axis[0][i], M.axis[1][i], M.axis[2][i]};
+            const V3 aw = mulv(R, axis);
+            const V6 s = mk6(aw, cross(p, aw));
+            const float q = qv[i], qd = qdv[i];
+            V6 c;
+            {
+                const V3 w = ang(v), vl = lin(v);
+                const V3 ca = cross(w, aw);
+                const V3 cl = cross(w, lin(s)) + cross(vl, aw);
+                c = mk6(qd * ca, qd * cl);
+            }
+            float tau0, dextra;
+            joint_force(M, i, q, qd, eff[i], dt, tau0, dextra);
+            const V6 U = s6mul(IA, s);
+            const float dinv = 1.f / (dot6(s, U) + dextra);
+            const float u = tau0 - dot6(s, pA);
+#pragma unroll
+            for (int a1 = 0; a1 < 6; ++a1) {
+                const float ui = U.a[a1] * dinv;
+#pragma unroll
+                for (int a2 = a1; a2 < 6; ++a2) IA.a[sidx(a1, a2)] = fmaf(-ui, U.a[a2], IA.a[sidx(a1, a2)]);
+            }
+            const V6 Iac = s6mul(IA, c);
+            const float ud = u * dinv;
+#pragma unroll
+            for (int k = 0; k < 6; ++k) pA.a[k] = pA.a[k] + Iac.a[k] + U.a[k] * ud;
+#pragma unroll
+            for (int k = 0; k < 6; ++k) { pu[i][k] = U.a[k]; pu[i][8 + k] = s.a[k]; pu[i][14 + k] = c.a[k]; }
+            pu[i][6] = dinv; pu[i][7] = u;
+            if (flags & kIsHead) {  // light child: park I^a in the parent's slot
+                const int ps = M.light_slot[M.parent[i]];
+                if (flags & kFirstLight) {
+#pragma unroll
+                    for (int k = 0; k < 21; ++k) slotI[ps][k] = IA.a[k];
+#pragma unroll
+                    for (int k = 0; k < 6; ++k) slotI[ps][21 + k] = pA.a[k];
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 21; ++k) slotI[ps][k] += IA.a[k];
+#pragma unroll
+                    for (int k = 0; k < 6; ++k) slotI[ps][21 + k] += pA.a[k];
+                }
+            } else {
+                carryI = IA; carryP = pA;
+            }
+        }
+
+        // ---- root: solve I^A a = -p^A (6x6 Cholesky) ----------------------------------------------
+        V6 a0;
+        chol6_solve(carryI, carryP, a0);
+        if (M.light_slot[0] >= 0) {
+#pragma unroll
+            for (int k = 0; k < 6; ++k) slotA[M.light_slot[0]][k] = a0.a[k];
+        }
+
+        // ---- pass 3: accelerations in reverse post-order (parent, then its heavy child) ---------------
+        V6 acarry = a0;
+        for (int k2 = L - 2; k2 >= 0; --k2) {
+            const int i = M.order2[k2];
+            const int flags = M.tflags[i];
+            V6 ap;
+            if (flags & kIsHead) {
+                const int ps = M.light_slot[M.parent[i]];
+#pragma unroll
+                for (int k = 0; k < 6; ++k) ap.a[k] = slotA[ps][k];
+            } else {
+                ap = acarry;
+            }
+            V6 U, s;
+#pragma unroll
+            for (int k = 0; k < 6; ++k) { U.a[k] = pu[i][k]; s.a[k] = pu[i][8 + k]; ap.a[k] += pu[i][14 + k]; }
+            const float qdd = (pu[i][7] - dot6(U, ap)) * pu[i][6];
+            V6 a;
+#pragma unroll
+            for (int k = 0; k < 6; ++k) a.a[k] = fmaf(s.a[k], qdd, ap.a[k]);
+            const int myslot = M.light_slot[i];
+            if (myslot >= 0) {
+#pragma unroll
+                for (int k = 0; k < 6; ++k) slotA[myslot][k] = a.a[k];
+            }
+            if (last && A.sens != nullptr && M.sensor_of_link[i] >= 0) {
+                M3 R;
+                V6 v, b;
+#pragma unroll
+                for (int k = 0; k < 9; ++k) R.m[k] = fk[i][k];
+                const V3 p = {fk[i][9], fk[i][10], fk[i][11]};
+#pragma unroll
+                for (int k = 0; k < 6; ++k) { v.a[k] = fk[i][12 + k]; b.a[k] = fk[i][18 + k]; }
+                sensor_wrench(M, i, R, p, v, b, a, root_z, dt, A.sens + (env * M.num_sensors + M.sensor_of_link[i]) * 6);
+            }
+            // integrate this joint (semi-implicit Euler); q/qd of link i are not read again this substep
+            float qd = fmaf(dt, qdd, qdv[i]);
+            qd = fminf(fmaxf(qd, -M.max_qd), M.max_qd);
+            qdv[i] = qd;
+            qv[i] = fmaf(dt, qd, qv[i]);
+            acarry = a;
+        }
+        integrate_root(M, a0, dt, rpos, rquat, rvel);
+    }
+
+    // ---- non-finite guard + store ---------------------------------------------------------------
+    bool bad = !(isfinite(rpos.x) && isfinite(rpos.y) && isfinite(rpos.z) && isfinite(rquat.w) && isfinite(rquat.x) &&
+                 isfinite(rquat.y) && isfinite(rquat.z));
+#pragma unroll
+    for (int k = 0; k < 6; ++k) bad = bad || !isfinite(rvel.a[k]);
+    for (int i = 1; i < L; ++i) bad = bad || !(isfinite(qv[i]) && isfinite(qdv[i]));
+    if (bad) {
+        rpos = {0.f, 0.f, -1.f};
+        rquat = {1.f, 0.f, 0.f, 0.f};
+        rvel = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
+        if (A.sens != nullptr)
+            for (int k = 0; k < M.num_sensors * 6; ++k) A.sens[env * M.num_sensors * 6 + k] = 0.f;
+    }
+    for (int i = 1; i < L; ++i) {
+        const int d = M.dof[i];
+        A.q[env * D + d] = bad ? 0.f : qv[i];
+        A.qd[env * D + d] = bad ? 0.f : qdv[i];
+    }
+    A.pos[env * 3] = rpos.x; A.pos[env * 3 + 1] = rpos.y; A.pos[env * 3 + 2] = rpos.z;
+    *reinterpret_cast<float4*>(A.quat + env * 4) = make_float4(rquat.w, rquat.x, rquat.y, rquat.z);
+    float* vv = A.vel + env * 6;
+    vv[0] = rvel.a[3]; vv[1] = rvel.a[4]; vv[2] = rvel.a[5];
+    vv[3] = rvel.a[0]; vv[4] = rvel.a[1]; vv[5] = rvel.a[2];
+}
+
 __global__ void clamp_actions_kernel(const float* __restrict__ in, float* __restrict__ out, float clip, long long n) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) {
@@ -608,6 +924,18 @@ int k2_clamp_actions(const float* in, float* out, float clip, int64_t count, cud
     return check_launch("clamp_actions_kernel");
 }
 
+// Kernel choice: OIGE_K2_MODE=warp|thread forces one; otherwise thread-per-env from kTpeMinEnvs envs on.
+static bool use_thread_per_env(int64_t n) {
+    static int mode = -1;
+    if (mode < 0) {
+        const char* e = getenv("OIGE_K2_MODE");
+        mode = (e && e[0] == 'w') ? 1 : (e && e[0] == 't') ? 2 : 0;
+    }
+    if (mode == 1) return false;
+    if (mode == 2) return true;
+    return n >= kTpeMinEnvs;
+}
+
 int k2_step(const OigeModel* model, const OigeTaskParams* P, const OigeState* st, const float* actions, int64_t n,
             int32_t substeps, float dt, cudaStream_t stream) {
     if (P->num_dof != model->num_dof)
@@ -619,6 +947,17 @@ int k2_step(const OigeModel* model, const OigeTaskParams* P, const OigeState* st
     if (reinterpret_cast<uintptr_t>(A.quat) & 15u) return fail(OIGE_E_ALIGN, "articulation_step: root_quat not 16B aligned");
     if (model->num_sensors > 0 && P->num_sensors != model->num_sensors)
         return fail(OIGE_E_SHAPE, "articulation_step: params.num_sensors %d != model %d", P->num_sensors, model->num_sensors);
+    if (model->tpe_ok && use_thread_per_env(n)) {
+        static int bs = 0;
+        if (!bs) { const char* e = getenv("OIGE_TPE_BLOCK"); bs = e ? atoi(e) : 128; if (bs != 32 && bs != 64 && bs != 128) bs = 128; }
+        const unsigned tb = (unsigned)((n + bs - 1) / bs);
+        const DevModel* dm = reinterpret_cast<const DevModel*>(model->dev_table);
+        if (model->num_links <= 12) articulation_step_tpe_kernel<12><<<tb, bs, 0, stream>>>(dm, *P, A);
+        else if (model->num_links <= 24) articulation_step_tpe_kernel<24><<<tb, bs, 0, stream>>>(dm, *P, A);
+        else articulation_step_tpe_kernel<32><<<tb, bs, 0, stream>>>(dm, *P, A);
+        count_launch();
+        return check_launch("articulation_step_tpe_kernel");
+    }
     const int pack = 32 / model->num_links;
     const long long warps = (n + pack - 1) / pack;
     const unsigned blocks = (unsigned)((warps + kWarpsPerBlock - 1) / kWarpsPerBlock);
@@ -672,6 +1011,47 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
     for (int k = 1; k < kMaxJump; ++k)
         for (int i = 0; i < 32; ++i) h->anc[k][i] = i < L ? h->anc[k - 1][h->anc[k - 1][i]] : i;
     h->pack = 32 / L;  // environments carried side by side by one warp
+    {   // heavy-path structure for the thread-per-env kernel
+        int height[32] = {0}, heavy[32], nslots = 0, cnt = 0;
+        for (int i = 0; i < 32; ++i) { heavy[i] = -1; h->light_slot[i] = -1; h->tflags[i] = 0; h->order2[i] = 0; }
+        for (int i = L - 1; i >= 1; --i) {  // parent[i] < i: children are final when i is visited
+            const int p = h->parent[i], cand = height[i] + 1;
+            if (cand > height[p] || (cand == height[p] && i < heavy[p])) { height[p] = cand; heavy[p] = i; }
+        }
+        // iterative post-order, light children first (index order), heavy child last
+        int stack[64], state[64], sp = 0;
+        stack[0] = 0; state[0] = 0; sp = 1;
+        while (sp > 0) {
+            const int node = stack[sp - 1];
+            int& st = state[sp - 1];
+            int next = -1;
+            for (; st < L; ++st) {  // light children in index order
+                if (st > 0 && h->parent[st] == node && st != heavy[node]) { next = st++; break; }
+            }
+            if (next < 0 && st == L) {  // then the heavy child, once
+                st = L + 1;
+                if (heavy[node] >= 0) next = heavy[node];
+            }
+            if (next >= 0) { stack[sp] = next; state[sp] = 0; ++sp; continue; }
+            if (node != 0) h->order2[cnt++] = node;
+            --sp;
+        }
+        h->tpe_ok = (cnt == L - 1) ? 1 : 0;
+        int seen_light[32] = {0};
+        for (int k = 0; k < cnt; ++k) {
+            const int i = h->order2[k], p = h->parent[i];
+            if (heavy[i] >= 0) h->tflags[i] |= kHasHeavy;
+            if (heavy[p] != i) {
+                h->tflags[i] |= kIsHead;
+                if (h->light_slot[p] < 0) {
+                    if (nslots >= kMaxSlots) { h->tpe_ok = 0; break; }
+                    h->light_slot[p] = nslots++;
+                }
+                if (!seen_light[p]) { h->tflags[i] |= kFirstLight; seen_light[p] = 1; }
+            }
+        }
+        if (heavy[0] >= 0) h->tflags[0] |= kHasHeavy;
+    }
     h->jump_rounds = 0;
     while ((1 << h->jump_rounds) < h->max_depth) ++h->jump_rounds;
     for (int i = 0; i < L; ++i) {
@@ -712,6 +1092,7 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
     h->k_c = d->contact_stiffness; h->d_c = d->contact_damping; h->mu = d->friction_mu; h->c_visc = d->friction_viscous;
     h->k_lim = d->limit_stiffness; h->d_lim = d->limit_damping; h->max_qd = d->max_joint_velocity; h->ang_damp = d->angular_damping;
 
+    const int tpe_ok = h->tpe_ok;
     void* dev = nullptr;
     cudaError_t e = cudaMalloc(&dev, sizeof(DevModel));
     if (e == cudaSuccess) e = cudaMemcpy(dev, h, sizeof(DevModel), cudaMemcpyHostToDevice);
@@ -722,7 +1103,7 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
         return nullptr;
     }
     OigeModel* m = new OigeModel();
-    m->dev_table = dev; m->num_links = L; m->num_dof = L - 1; m->num_sensors = d->num_sensors;
+    m->dev_table = dev; m->num_links = L; m->num_dof = L - 1; m->num_sensors = d->num_sensors; m->tpe_ok = tpe_ok;
     return m;
 }
 
