@@ -37,6 +37,9 @@ struct OigeModel {
 namespace oige {
 namespace {
 
+#ifndef TPE_MINBLOCKS
+#define TPE_MINBLOCKS 4
+#endif
 constexpr int kWarpsPerBlock = 4;
 constexpr int kMaxLevels = 16;
 constexpr int kMaxChildren = 4;
@@ -635,14 +638,16 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
 // links in the same order, so the model-table reads are shared-memory broadcasts and the control
 // flow is uniform except for contact activation.  Per-link intermediates that must survive between
 // the passes live in per-thread local memory (interleaved by the hardware, hence coalesced):
-//   fk[i]  = R(9) p(3) v(6) b(6)              forward kinematics, written in pass 1, read in pass 2
-//   pu[i]  = U(6) 1/d u s(6) c(6)             written in pass 2, read in pass 3
+//   fk[i]  = quat(4) p(3) v(6) b(6)           forward kinematics, written in pass 1, read in passes 2, 3
+//   pu[i]  = U(6) 1/d (u - U.c)               written in pass 2, read in pass 3
+// (27 floats per link: the arrays are write-once/read-once per substep, so their size IS the L2/HBM
+// traffic of the kernel; rotation matrices, s and c are recomputed instead of stored.)
 // Articulated inertias travel up a heavy path in REGISTERS (links are visited in post-order with the
 // heavy child last, so a link directly follows its heavy child); only light children (chain heads)
 // go through a small slot array.  Same equations, same contact model, same integrator as above.
 // ================================================================================================
 template <int MAXL>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, TPE_MINBLOCKS)
 articulation_step_tpe_kernel(const DevModel* __restrict__ gmodel, const __grid_constant__ OigeTaskParams P,
                              const __grid_constant__ K2Args A) {
     __shared__ __align__(16) DevModel M;
@@ -659,8 +664,8 @@ articulation_step_tpe_kernel(const DevModel* __restrict__ gmodel, const __grid_c
     const float dt = A.dt;
     const V3 grav = {M.gravity[0], M.gravity[1], M.gravity[2]};
 
-    float fk[MAXL][24];
-    float pu[MAXL][20];
+    float fk[MAXL][19];
+    float pu[MAXL][8];
     float slotI[kMaxSlots][27];
     float slotA[kMaxSlots][6];
     float qv[MAXL], qdv[MAXL], eff[MAXL];
@@ -695,31 +700,26 @@ articulation_step_tpe_kernel(const DevModel* __restrict__ gmodel, const __grid_c
         // ---- pass 1: kinematics in index order (parent[i] < i) ----------------------------------
         for (int i = 1; i < L; ++i) {
             const int pa = M.parent[i];
-            M3 Rp;
+            Q4 qp;
             V3 pp;
             V6 pv, pb;
             if (pa == 0) {
-                Rp = R0; pp = {0.f, 0.f, 0.f}; pv = rvel; pb = b0;
+                qp = rquat; pp = {0.f, 0.f, 0.f}; pv = rvel; pb = b0;
             } else {
+                qp = {fk[pa][0], fk[pa][1], fk[pa][2], fk[pa][3]};
+                pp = {fk[pa][4], fk[pa][5], fk[pa][6]};
 #pragma unroll
-                for (int k = 0; k < 9; ++k) Rp.m[k] = fk[pa][k];
-                pp = {fk[pa][9], fk[pa][10], fk[pa][11]};
-#pragma unroll
-                for (int k = 0; k < 6; ++k) { pv.a[k] = fk[pa][12 + k]; pb.a[k] = fk[pa][18 + k]; }
+                for (int k = 0; k < 6; ++k) { pv.a[k] = fk[pa][7 + k]; pb.a[k] = fk[pa][13 + k]; }
             }
+            const M3 Rp = qmat(qp);
             const V3 axis = {M.axis[0][i], M.axis[1][i], M.axis[2][i]};
             float sh, ch;
             sincosf(0.5f * qv[i], &sh, &ch);
             const Q4 ql = qmul(Q4{M.jquat[0][i], M.jquat[1][i], M.jquat[2][i], M.jquat[3][i]},
                                Q4{ch, sh * axis.x, sh * axis.y, sh * axis.z});
-            const M3 Rl = qmat(ql);
+            const Q4 qi = qmul(qp, ql);
             const V3 p = pp + mulv(Rp, V3{M.jpos[0][i], M.jpos[1][i], M.jpos[2][i]});
-            M3 R;
-#pragma unroll
-            for (int r = 0; r < 3; ++r)
-#pragma unroll
-                for (int cc = 0; cc < 3; ++cc)
-                    R.m[3 * r + cc] = Rp.m[3 * r] * Rl.m[cc] + Rp.m[3 * r + 1] * Rl.m[3 + cc] + Rp.m[3 * r + 2] * Rl.m[6 + cc];
+            const M3 R = qmat(qi);
             const V3 aw = mulv(R, axis);
             const V6 s = mk6(aw, cross(p, aw));
             const float qd = qdv[i];
@@ -729,13 +729,12 @@ articulation_step_tpe_kernel(const DevModel* __restrict__ gmodel, const __grid_c
             const V3 w = ang(v), vl = lin(v);
             const V3 ca = cross(w, aw);
             const V3 cl = cross(w, lin(s)) + cross(vl, aw);
+            fk[i][0] = qi.w; fk[i][1] = qi.x; fk[i][2] = qi.y; fk[i][3] = qi.z;
+            fk[i][4] = p.x; fk[i][5] = p.y; fk[i][6] = p.z;
 #pragma unroll
-            for (int k = 0; k < 9; ++k) fk[i][k] = R.m[k];
-            fk[i][9] = p.x; fk[i][10] = p.y; fk[i][11] = p.z;
-#pragma unroll
-            for (int k = 0; k < 6; ++k) fk[i][12 + k] = v.a[k];
-            fk[i][18] = pb.a[0] + qd * ca.x; fk[i][19] = pb.a[1] + qd * ca.y; fk[i][20] = pb.a[2] + qd * ca.z;
-            fk[i][21] = pb.a[3] + qd * cl.x; fk[i][22] = pb.a[4] + qd * cl.y; fk[i][23] = pb.a[5] + qd * cl.z;
+            for (int k = 0; k < 6; ++k) fk[i][7 + k] = v.a[k];
+            fk[i][13] = pb.a[0] + qd * ca.x; fk[i][14] = pb.a[1] + qd * ca.y; fk[i][15] = pb.a[2] + qd * ca.z;
+            fk[i][16] = pb.a[3] + qd * cl.x; fk[i][17] = pb.a[4] + qd * cl.y; fk[i][18] = pb.a[5] + qd * cl.z;
         }
 
         // ---- pass 2: articulated inertia, post-order with the heavy child last ---------------------
@@ -753,11 +752,10 @@ articulation_step_tpe_kernel(const DevModel* __restrict__ gmodel, const __grid_c
             if (i == 0) {
                 R = R0; p = {0.f, 0.f, 0.f}; v = rvel; b = b0;
             } else {
+                R = qmat(Q4{fk[i][0], fk[i][1], fk[i][2], fk[i][3]});
+                p = {fk[i][4], fk[i][5], fk[i][6]};
 #pragma unroll
-                for (int k = 0; k < 9; ++k) R.m[k] = fk[i][k];
-                p = {fk[i][9], fk[i][10], fk[i][11]};
-#pragma unroll
-                for (int k = 0; k < 6; ++k) { v.a[k] = fk[i][12 + k]; b.a[k] = fk[i][18 + k]; }
+                for (int k = 0; k < 6; ++k) { v.a[k] = fk[i][7 + k]; b.a[k] = fk[i][13 + k]; }
             }
             S6 IA;
             V6 pA;
@@ -808,8 +806,8 @@ articulation_step_tpe_kernel(const DevModel* __restrict__ gmodel, const __grid_c
 #pragma unroll
             for (int k = 0; k < 6; ++k) pA.a[k] = pA.a[k] + Iac.a[k] + U.a[k] * ud;
 #pragma unroll
-            for (int k = 0; k < 6; ++k) { pu[i][k] = U.a[k]; pu[i][8 + k] = s.a[k]; pu[i][14 + k] = c.a[k]; }
-            pu[i][6] = dinv; pu[i][7] = u;
+            for (int k = 0; k < 6; ++k) pu[i][k] = U.a[k];
+            pu[i][6] = dinv; pu[i][7] = u - dot6(U, c);  // pass 3: qdd = (u - U.(a_parent + c)) / d
             if (flags & kIsHead) {  // light child: park I^a in the parent's slot
                 const int ps = M.light_slot[M.parent[i]];
                 if (flags & kFirstLight) {
@@ -849,26 +847,37 @@ articulation_step_tpe_kernel(const DevModel* __restrict__ gmodel, const __grid_c
             } else {
                 ap = acarry;
             }
-            V6 U, s;
+            // recompute s and c from the stored kinematics (cheaper than storing 12 more floats per link)
+            const M3 R = qmat(Q4{fk[i][0], fk[i][1], fk[i][2], fk[i][3]});
+            const V3 p = {fk[i][4], fk[i][5], fk[i][6]};
+            V6 v;
 #pragma unroll
-            for (int k = 0; k < 6; ++k) { U.a[k] = pu[i][k]; s.a[k] = pu[i][8 + k]; ap.a[k] += pu[i][14 + k]; }
+            for (int k = 0; k < 6; ++k) v.a[k] = fk[i][7 + k];
+            const V3 aw = mulv(R, V3{M.axis[0][i], M.axis[1][i], M.axis[2][i]});
+            const V6 s = mk6(aw, cross(p, aw));
+            const float qd0 = qdv[i];
+            V6 U;
+#pragma unroll
+            for (int k = 0; k < 6; ++k) U.a[k] = pu[i][k];
             const float qdd = (pu[i][7] - dot6(U, ap)) * pu[i][6];
             V6 a;
+            {
+                const V3 w = ang(v), vl = lin(v);
+                const V3 ca = cross(w, aw);
+                const V3 cl = cross(w, lin(s)) + cross(vl, aw);
+                const V6 c = mk6(qd0 * ca, qd0 * cl);
 #pragma unroll
-            for (int k = 0; k < 6; ++k) a.a[k] = fmaf(s.a[k], qdd, ap.a[k]);
+                for (int k = 0; k < 6; ++k) a.a[k] = fmaf(s.a[k], qdd, ap.a[k] + c.a[k]);
+            }
             const int myslot = M.light_slot[i];
             if (myslot >= 0) {
 #pragma unroll
                 for (int k = 0; k < 6; ++k) slotA[myslot][k] = a.a[k];
             }
             if (last && A.sens != nullptr && M.sensor_of_link[i] >= 0) {
-                M3 R;
-                V6 v, b;
+                V6 b;
 #pragma unroll
-                for (int k = 0; k < 9; ++k) R.m[k] = fk[i][k];
-                const V3 p = {fk[i][9], fk[i][10], fk[i][11]};
-#pragma unroll
-                for (int k = 0; k < 6; ++k) { v.a[k] = fk[i][12 + k]; b.a[k] = fk[i][18 + k]; }
+                for (int k = 0; k < 6; ++k) b.a[k] = fk[i][13 + k];
                 sensor_wrench(M, i, R, p, v, b, a, root_z, dt, A.sens + (env * M.num_sensors + M.sensor_of_link[i]) * 6);
             }
             // integrate this joint (semi-implicit Euler); q/qd of link i are not read again this substep

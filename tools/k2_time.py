@@ -7,7 +7,7 @@ from omniisaacgymenvs_b200 import _lib
 from omniisaacgymenvs_b200.utils.task_util import make_env
 lib = _lib.load()
 for robot in (sys.argv[1].split(",") if len(sys.argv) > 1 else ["Humanoid", "Ant"]):
-    for n in (16384, 65536):
+    for n in [int(x) for x in os.environ.get("K2_NS", "16384,65536").split(",")]:
         with contextlib.redirect_stdout(io.StringIO()):
             env, task = make_env(robot, num_envs=n)
             env.reset()
