@@ -935,18 +935,17 @@ int k2_clamp_actions(const float* in, float* out, float clip, int64_t count, cud
 
 // Kernel choice: OIGE_K2_MODE=warp|thread forces one; otherwise thread-per-env from kTpeMinEnvs envs on.
 static bool use_thread_per_env(int64_t n) {
-    static int mode = -1;
-    if (mode < 0) {
-        const char* e = getenv("OIGE_K2_MODE");
-        mode = (e && e[0] == 'w') ? 1 : (e && e[0] == 't') ? 2 : 0;
-    }
-    if (mode == 1) return false;
-    if (mode == 2) return true;
+    const char* e = getenv("OIGE_K2_MODE");  // read per call so tests can switch it
+    if (e && e[0] == 'w') return false;
+    if (e && e[0] == 't') return true;
     return n >= kTpeMinEnvs;
 }
 
+// `decision_n`: env count the kernel choice is based on (the whole step's count when the caller
+// processes the envs in chunks, so that chunked and one-shot steps run the SAME kernel and stay
+// bit-identical); <= 0 means n.
 int k2_step(const OigeModel* model, const OigeTaskParams* P, const OigeState* st, const float* actions, int64_t n,
-            int32_t substeps, float dt, cudaStream_t stream) {
+            int32_t substeps, float dt, cudaStream_t stream, int64_t decision_n) {
     if (P->num_dof != model->num_dof)
         return fail(OIGE_E_SHAPE, "articulation_step: params.num_dof %d != model dofs %d", P->num_dof, model->num_dof);
     K2Args A;
@@ -956,9 +955,8 @@ int k2_step(const OigeModel* model, const OigeTaskParams* P, const OigeState* st
     if (reinterpret_cast<uintptr_t>(A.quat) & 15u) return fail(OIGE_E_ALIGN, "articulation_step: root_quat not 16B aligned");
     if (model->num_sensors > 0 && P->num_sensors != model->num_sensors)
         return fail(OIGE_E_SHAPE, "articulation_step: params.num_sensors %d != model %d", P->num_sensors, model->num_sensors);
-    if (model->tpe_ok && use_thread_per_env(n)) {
-        static int bs = 0;
-        if (!bs) { const char* e = getenv("OIGE_TPE_BLOCK"); bs = e ? atoi(e) : 128; if (bs != 32 && bs != 64 && bs != 128) bs = 128; }
+    if (model->tpe_ok && use_thread_per_env(decision_n > 0 ? decision_n : n)) {
+        const int bs = 128;
         const unsigned tb = (unsigned)((n + bs - 1) / bs);
         const DevModel* dm = reinterpret_cast<const DevModel*>(model->dev_table);
         if (model->num_links <= 12) articulation_step_tpe_kernel<12><<<tb, bs, 0, stream>>>(dm, *P, A);

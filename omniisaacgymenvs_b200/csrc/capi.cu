@@ -55,7 +55,7 @@ int k3_masked(const OigeTaskParams*, const OigeState*, const OigeTaskBuffers*, c
 int k3_idx(const OigeTaskParams*, const OigeState*, const OigeTaskBuffers*, const OigeResetInit*, const int64_t*,
            int64_t, const float*, const float*, uint64_t, uint64_t, int64_t, cudaStream_t);
 int k2_step(const OigeModel*, const OigeTaskParams*, const OigeState*, const float*, int64_t, int32_t, float,
-            cudaStream_t);
+            cudaStream_t, int64_t decision_n);
 int k2_clamp_actions(const float* in, float* out, float clip, int64_t count, cudaStream_t);
 OigeModel* k2_model_create(const OigeModelDesc*);
 void k2_model_destroy(OigeModel*);
@@ -153,13 +153,15 @@ int oige_articulation_step_f32(const OigeModel* model, const OigeTaskParams* par
     if (substeps < 1 || substeps > 64) return fail(OIGE_E_RANGE, "substeps %d not in [1,64]", substeps);
     if (!(dt > 0.0f)) return fail(OIGE_E_RANGE, "dt must be > 0");
     if (n_envs == 0) return OIGE_OK;
-    return k2_step(model, params, state, actions, n_envs, substeps, dt, (cudaStream_t)stream);
+    return k2_step(model, params, state, actions, n_envs, substeps, dt, (cudaStream_t)stream, 0);
 }
 
-int oige_env_step_f32(const OigeModel* model, const OigeTaskParams* params, const OigeState* state,
+}  // extern "C" (reopened below)
+
+static int env_step_impl(const OigeModel* model, const OigeTaskParams* params, const OigeState* state,
                       const OigeTaskBuffers* buf, const OigeResetInit* init, const float* actions_in,
                       float clip_actions, uint64_t seed, uint64_t counter, int64_t env_id_offset, int64_t n_envs,
-                      int32_t substeps, float dt, void* stream) {
+                      int32_t substeps, float dt, void* stream, int64_t decision_n) {
     if (int rc = check_common("oige_env_step_f32", params, state, buf, n_envs)) return rc;
     if (!model || !init || !actions_in) return fail(OIGE_E_NULL, "oige_env_step_f32: null argument");
     if (substeps < 1 || substeps > 64) return fail(OIGE_E_RANGE, "substeps %d not in [1,64]", substeps);
@@ -170,8 +172,18 @@ int oige_env_step_f32(const OigeModel* model, const OigeTaskParams* params, cons
     if (int rc = k2_clamp_actions(actions_in, buf->actions, clip_actions, n_envs * params->num_dof, s)) return rc;
     if (int rc = k3_masked(params, state, buf, init, nullptr, nullptr, seed, counter, env_id_offset, n_envs, s))
         return rc;
-    if (int rc = k2_step(model, params, state, buf->actions, n_envs, substeps, dt, s)) return rc;
+    if (int rc = k2_step(model, params, state, buf->actions, n_envs, substeps, dt, s, decision_n)) return rc;
     return k1_dispatch(params, state, buf, n_envs, s, 0);
+}
+
+extern "C" {
+
+int oige_env_step_f32(const OigeModel* model, const OigeTaskParams* params, const OigeState* state,
+                      const OigeTaskBuffers* buf, const OigeResetInit* init, const float* actions_in,
+                      float clip_actions, uint64_t seed, uint64_t counter, int64_t env_id_offset, int64_t n_envs,
+                      int32_t substeps, float dt, void* stream) {
+    return env_step_impl(model, params, state, buf, init, actions_in, clip_actions, seed, counter, env_id_offset,
+                         n_envs, substeps, dt, stream, 0);
 }
 
 int oige_env_step_host_f32(const OigeModel* model, const OigeTaskParams* params, const OigeState* state,
@@ -212,8 +224,8 @@ int oige_env_step_host_f32(const OigeModel* model, const OigeTaskParams* params,
         float* stage = actions_dev_staging + off * D;
         e = cudaMemcpyAsync(stage, actions_host + off * D, (size_t)cnt * D * sizeof(float), cudaMemcpyHostToDevice, s);
         if (e != cudaSuccess) return fail((int)e, "H2D actions: %s", cudaGetErrorString(e));
-        if (int rc = oige_env_step_f32(model, params, &st, &bf, &in, stage, clip_actions, seed, counter,
-                                       env_id_offset + off, cnt, substeps, dt, (void*)s))
+        if (int rc = env_step_impl(model, params, &st, &bf, &in, stage, clip_actions, seed, counter,
+                                   env_id_offset + off, cnt, substeps, dt, (void*)s, n_envs))
             return rc;
         e = cudaMemcpyAsync(obs_host + off * OBS, bf.obs, (size_t)cnt * OBS * sizeof(float), cudaMemcpyDeviceToHost, s);
         if (e == cudaSuccess) e = cudaMemcpyAsync(rew_host + off, bf.rew, (size_t)cnt * sizeof(float), cudaMemcpyDeviceToHost, s);

@@ -16,6 +16,14 @@ pytestmark = pytest.mark.gpu
 DT = 0.0083
 
 
+@pytest.fixture(autouse=True, params=["warp", "thread"])
+def k2_kernel(request, monkeypatch):
+    """Every test runs against BOTH articulation kernels: warp-per-env (lane = link, shuffles) and
+    thread-per-env (lane = env, local-memory link arrays).  OIGE_K2_MODE overrides the size-based choice."""
+    monkeypatch.setenv("OIGE_K2_MODE", request.param)
+    return request.param
+
+
 def _err(a, b):
     return np.abs(a - b).max()
 
@@ -79,6 +87,18 @@ def test_rollout_64_with_contacts_statistical(cuda_lib, robot):
     frac_ok = float((per_env < 2e-2).mean())
     assert frac_ok >= 0.97, f"only {frac_ok:.3f} of envs within 2e-2 after 64 substeps (median {np.median(per_env):.2e})"
     assert np.median(per_env) < 2e-3
+
+
+def test_both_kernels_agree_with_each_other(cuda_lib, monkeypatch):
+    """warp-per-env vs thread-per-env on the same state: same model, different summation orders."""
+    model, spec = dh.specs("Humanoid")
+    st = dh.random_state(model, 256, 11, height=1.3, tilt=0.1)
+    monkeypatch.setenv("OIGE_K2_MODE", "warp")
+    a = dh.run_gpu(cuda_lib, model, spec, st, 2, DT)
+    monkeypatch.setenv("OIGE_K2_MODE", "thread")
+    b = dh.run_gpu(cuda_lib, model, spec, st, 2, DT)
+    assert _err(a["q"], b["q"]) < 5e-5 and _err(a["pos"], b["pos"]) < 5e-5
+    assert (np.abs(a["qd"] - b["qd"]) / np.maximum(1.0, np.abs(a["qd"]))).max() < 5e-3
 
 
 def test_substeps_in_one_launch_equal_separate_launches(cuda_lib):
