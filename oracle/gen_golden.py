@@ -115,6 +115,19 @@ def main() -> None:
             for n in (1, 33, 256):
                 save_case(f"{spec.name.lower()}_s{seed}_n{n}", spec, lo.synthetic_state(spec, n, seed))
         save_case(f"{spec.name.lower()}_edge", spec, edge_state(spec))
+    # method-level episodes through the verbatim task CLASSES (post_reset / pre_physics_step / reset_idx / ...)
+    from omniisaacgymenvs_b200.articulations import grid_env_origins
+    from omniisaacgymenvs_b200.robots.model import build_model
+    from oracle import ref_task_driver
+
+    for robot in ("Humanoid", "Ant"):
+        model = build_model(robot)  # the limits / spawn height are INPUT data of the episode
+        n = 96
+        spawn = torch.from_numpy(grid_env_origins(n, 5.0))
+        spawn[:, 2] += model.spawn_height
+        ep = ref_task_driver.run_episode(robot, n, steps=5, seed=0, dof_limits=torch.from_numpy(model.dof_limits()),
+                                         spawn_pos=spawn)
+        np.savez_compressed(os.path.join(GOLDEN_DIR, f"episode_{robot.lower()}.npz"), **ep)
     print("wrote", len(os.listdir(GOLDEN_DIR)), "fixtures to", GOLDEN_DIR)
 
 

@@ -180,3 +180,56 @@ def test_cpu_tensors_are_rejected_not_silently_computed(cuda_lib):
     env.reset()
     with pytest.raises(RuntimeError):
         task.reset_idx(torch.arange(4), rand_pos=torch.rand(4, 8), rand_vel=torch.rand(4, 8))
+
+
+@pytest.mark.parametrize("robot", ["Humanoid", "Ant"])
+def test_task_classes_reproduce_the_reference_episode(cuda_lib, robot):
+    """OUR LocomotionTask / ArticulationView on the GPU, driven through the episode recorded from the
+    VERBATIM reference task classes (tests/golden/episode_*.npz, oracle/ref_task_driver.py): post_reset
+    constants, reset_idx with the reference's torch.rand draws (bit-exact), efforts (bit-exact), then the
+    fused post_physics_step on the injected state (1e-5, reset flags bit-exact)."""
+    import os
+
+    z = np.load(os.path.join(helpers.GOLDEN_DIR, f"episode_{robot.lower()}.npz"))
+    ep = {k: torch.from_numpy(z[k]) for k in z.files}
+    steps, n = ep["actions"].shape[:2]
+    env, task = make_env(robot, num_envs=n, seed=0)
+    dev = task.device
+    v = task.get_robot()
+    # post_reset constants
+    assert torch.equal(task.initial_root_pos.cpu(), ep["initial_root_pos"])
+    assert torch.equal(task.initial_root_rot.cpu(), ep["initial_root_rot"])
+    assert torch.equal(task.joint_gears.cpu(), ep["joint_gears"])
+    assert torch.equal(task.motor_effort_ratio.cpu(), ep["motor_effort_ratio"])
+    assert torch.equal(task.dof_limits_lower.cpu(), ep["dof_limits_lower"])
+    assert torch.equal(task.dof_limits_upper.cpu(), ep["dof_limits_upper"])
+    assert task.dt == 1.0 / 60.0
+    # post_reset's reset_idx(all) with the reference's draws
+    task.reset_buf.fill_(1)
+    task.reset_idx(torch.arange(n, device=dev), ep["post_reset_rand_pos"].to(dev).contiguous(),
+                   ep["post_reset_rand_vel"].to(dev).contiguous())
+    assert torch.equal(v.dof_pos.cpu(), ep["post_reset_dof_pos"]) and torch.equal(v.dof_vel.cpu(), ep["post_reset_dof_vel"])
+    assert torch.equal(task.potentials.cpu(), ep["post_reset_potentials"])
+    assert int(task.reset_buf.sum()) == 0 and int(task.progress_buf.sum()) == 0
+    for t in range(steps):
+        ids = task.reset_buf.nonzero(as_tuple=False).squeeze(-1)
+        assert torch.equal(ids.cpu(), ep["reset_ids"][t].nonzero(as_tuple=False).squeeze(-1))
+        if len(ids):
+            task.reset_idx(ids, ep["rand_pos"][t].to(dev)[ids].contiguous(), ep["rand_vel"][t].to(dev)[ids].contiguous())
+        for got, key in ((v.dof_pos, "after_reset_dof_pos"), (v.dof_vel, "after_reset_dof_vel"), (v.root_pos, "after_reset_pos"),
+                         (v.root_quat, "after_reset_quat"), (v.root_vel, "after_reset_vel"),
+                         (task.potentials, "after_reset_potentials")):
+            assert torch.equal(got.cpu(), ep[key][t]), f"step {t}: {key}"
+        task.actions.copy_(ep["actions"][t].to(dev))
+        forces = task.actions * task.joint_gears * task.power_scale  # locomotion.py:108-109
+        assert torch.equal(forces.cpu(), ep["efforts"][t])
+        v.root_pos.copy_(ep["inj_pos"][t]); v.root_quat.copy_(ep["inj_quat"][t]); v.root_vel.copy_(ep["inj_vel"][t])
+        v.dof_pos.copy_(ep["inj_dof_pos"][t]); v.dof_vel.copy_(ep["inj_dof_vel"][t]); v.sensor_forces.copy_(ep["inj_sensors"][t])
+        if t == int(ep["progress_override_step"]):
+            task.progress_buf[: n // 4] = task._max_episode_length - 2
+        task.post_physics_step()
+        got = {"obs": task.obs_buf, "rew": task.rew_buf, "reset_buf": task.reset_buf, "progress_buf": task.progress_buf,
+               "potentials": task.potentials, "prev_potentials": task.prev_potentials, "up_vec": task.up_vec,
+               "heading_vec": task.heading_vec}
+        ref = {k: ep[k][t] for k in got}
+        helpers.assert_k1_matches({k: x.detach().cpu() for k, x in got.items()}, ref, f"{robot} step {t}")
