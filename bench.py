@@ -302,6 +302,8 @@ def run_ours(args):
         env, task = make_env(ROBOT, num_envs=n, device_id=local_rank, seed=42, env_id_offset=rank * n,
                              global_num_envs=world * n)
         env.reset()
+        if not args.no_cuda_graph:
+            env.enable_cuda_graph()  # whole step (K3+clamp, K2, K1, hand-off copies) replayed as one graph
     K, W = args.steps, max(args.warmup, 3)
     D = task.num_actions
     gen = torch.Generator(device=device).manual_seed(1234 + rank)
@@ -327,6 +329,7 @@ def run_ours(args):
 
     # ---- timed region: device-resident inputs, per-step event pairs, L2 flushed between steps ----
     launches0 = _lib.launch_count()
+    replays0 = getattr(env, "graph_replays", 0)
     acts = [torch.rand(n, D, device=device, generator=gen) * 2 - 1 for _ in range(min(K, 64))]
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
     barrier()
@@ -344,6 +347,8 @@ def run_ours(args):
     t_wall = time.perf_counter() - t_wall0
     clk_hi = clocks.mark()
     launches = _lib.launch_count() - launches0
+    if getattr(env, "_graph", None) is not None:  # kernels inside graph replays are not host-side launches
+        launches += K * env.graph_kernels
     dev_ms = sum(a.elapsed_time(b) for a, b in evs)
     dev_ms = max_over_ranks(dev_ms, device)
     ms_per_step = dev_ms / K
@@ -356,6 +361,7 @@ def run_ours(args):
     obs_h = torch.empty(n, task.num_observations).pin_memory()
     rew_h = torch.empty(n).pin_memory()
     rst_h = torch.empty(n, dtype=torch.int64).pin_memory()
+    env.disable_cuda_graph()
     for i in range(3):
         env.step_host(a_host[i % 4], obs_h, rew_h, rst_h)
     barrier()
@@ -401,7 +407,8 @@ def run_ours(args):
                                    f"{n} envs/GPU (BASELINE.json configs[2])",
                        "envs_per_gpu": n, "global_envs": world * n, "parallelism": f"env-index sharding x{world}",
                        "l2": "flushed between steps (256 MiB memset outside the per-step CUDA-event pairs)",
-                       "actions": "uniform random policy, device-resident"},
+                       "actions": "uniform random policy, device-resident",
+                       "cuda_graph": not args.no_cuda_graph},
             "clocks": clocks.summary(clk_lo, clk_hi),
             "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(launches),
@@ -426,6 +433,7 @@ def main():
     ap.add_argument("--envs-per-gpu", type=int, default=ENVS_PER_GPU)
     ap.add_argument("--cpu-sample-envs", type=int, default=ENVS_PER_GPU)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-cuda-graph", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference_arm(args)

@@ -111,6 +111,9 @@ typedef struct OigeTaskBuffers {
     float* heading_vec;      /* [N,3] out */
     float* actions;          /* [N,D] the task's stored (clamped) actions */
     double* episode_stats;   /* [OIGE_STATS_SLOTS,4] accumulators or NULL: sum(rew), #done, sum(len at done), #env-steps */
+    uint64_t* reset_counter; /* NULL, or a device scalar: oige_env_step_f32 then takes the Philox reset counter from
+                                it (instead of its `counter` argument) and increments it at the end of the step, so
+                                that the step can be captured once in a CUDA graph and replayed */
 } OigeTaskBuffers;
 
 /* Per-env initial state captured at post_reset (locomotion.py:148-150). */
@@ -206,8 +209,8 @@ int oige_articulation_step_f32(const OigeModel* model, const OigeTaskParams* par
 
 /* ---- whole VecEnvRLGames.step on device buffers (K3 -> K2 -> K1) ----
  * Replaces VecEnvRLGames.step (envs/vec_env_rlgames.py:56-78) minus the rl_device copies:
- * clamps `actions_in` to +-clip_actions into buf->actions, then masked reset, articulation
- * step, fused obs/reward/reset. */
+ * clamps `actions_in` to +-clip_actions into buf->actions (inside the reset kernel), then masked reset,
+ * articulation step, fused obs/reward/reset: three launches, no host synchronisation. */
 int oige_env_step_f32(const OigeModel* model, const OigeTaskParams* params, const OigeState* state,
                       const OigeTaskBuffers* buf, const OigeResetInit* init, const float* actions_in,
                       float clip_actions, uint64_t seed, uint64_t counter, int64_t env_id_offset,

@@ -49,7 +49,7 @@ class OigeState(C.Structure):
 
 class OigeTaskBuffers(C.Structure):
     _fields_ = [("obs", vp), ("rew", vp), ("reset_buf", vp), ("progress_buf", vp), ("potentials", vp),
-                ("prev_potentials", vp), ("up_vec", vp), ("heading_vec", vp), ("actions", vp), ("episode_stats", vp)]
+                ("prev_potentials", vp), ("up_vec", vp), ("heading_vec", vp), ("actions", vp), ("episode_stats", vp), ("reset_counter", vp)]
 
 
 class OigeResetInit(C.Structure):

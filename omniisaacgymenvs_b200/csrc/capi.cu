@@ -49,9 +49,9 @@ int sm_count() {
 }
 
 // kernels' host-side dispatchers
-int k1_dispatch(const OigeTaskParams*, const OigeState*, const OigeTaskBuffers*, int64_t, cudaStream_t, int);
+int k1_dispatch(const OigeTaskParams*, const OigeState*, const OigeTaskBuffers*, int64_t, cudaStream_t, int, bool);
 int k3_masked(const OigeTaskParams*, const OigeState*, const OigeTaskBuffers*, const OigeResetInit*, const float*,
-              const float*, uint64_t, uint64_t, int64_t, int64_t, cudaStream_t);
+              const float*, uint64_t, uint64_t, int64_t, int64_t, cudaStream_t, const float* actions_in, float clip);
 int k3_idx(const OigeTaskParams*, const OigeState*, const OigeTaskBuffers*, const OigeResetInit*, const int64_t*,
            int64_t, const float*, const float*, uint64_t, uint64_t, int64_t, cudaStream_t);
 int k2_step(const OigeModel*, const OigeTaskParams*, const OigeState*, const float*, int64_t, int32_t, float,
@@ -105,7 +105,7 @@ int oige_obs_reward_reset_f32(const OigeTaskParams* params, const OigeState* sta
                               int64_t n_envs, void* stream) {
     if (int rc = check_common("oige_obs_reward_reset_f32", params, state, buf, n_envs)) return rc;
     if (n_envs == 0) return OIGE_OK;
-    return k1_dispatch(params, state, buf, n_envs, (cudaStream_t)stream, 0);
+    return k1_dispatch(params, state, buf, n_envs, (cudaStream_t)stream, 0, false);
 }
 
 // same as above with an explicit tile size (32/64/128) -- used by the benchmark's tile sweep
@@ -113,7 +113,7 @@ int oige_obs_reward_reset_tile_f32(const OigeTaskParams* params, const OigeState
                                    int64_t n_envs, int32_t tile, void* stream) {
     if (int rc = check_common("oige_obs_reward_reset_tile_f32", params, state, buf, n_envs)) return rc;
     if (n_envs == 0) return OIGE_OK;
-    return k1_dispatch(params, state, buf, n_envs, (cudaStream_t)stream, tile);
+    return k1_dispatch(params, state, buf, n_envs, (cudaStream_t)stream, tile, false);
 }
 
 int oige_reset_masked_f32(const OigeTaskParams* params, const OigeState* state, const OigeTaskBuffers* buf,
@@ -122,7 +122,7 @@ int oige_reset_masked_f32(const OigeTaskParams* params, const OigeState* state, 
     if (int rc = check_common("oige_reset_masked_f32", params, state, buf, n_envs)) return rc;
     if (n_envs == 0) return OIGE_OK;
     return k3_masked(params, state, buf, init, rand_pos, rand_vel, seed, counter, env_id_offset, n_envs,
-                     (cudaStream_t)stream);
+                     (cudaStream_t)stream, nullptr, 0.0f);
 }
 
 int oige_reset_idx_f32(const OigeTaskParams* params, const OigeState* state, const OigeTaskBuffers* buf,
@@ -169,11 +169,11 @@ static int env_step_impl(const OigeModel* model, const OigeTaskParams* params, c
     cudaStream_t s = (cudaStream_t)stream;
     // VecEnvRLGames.step: clamp -> pre_physics_step (reset flagged envs, store actions, efforts)
     //                     -> control_frequency_inv x world.step -> post_physics_step
-    if (int rc = k2_clamp_actions(actions_in, buf->actions, clip_actions, n_envs * params->num_dof, s)) return rc;
-    if (int rc = k3_masked(params, state, buf, init, nullptr, nullptr, seed, counter, env_id_offset, n_envs, s))
+    if (int rc = k3_masked(params, state, buf, init, nullptr, nullptr, seed, counter, env_id_offset, n_envs, s,
+                           actions_in, clip_actions))
         return rc;
     if (int rc = k2_step(model, params, state, buf->actions, n_envs, substeps, dt, s, decision_n)) return rc;
-    return k1_dispatch(params, state, buf, n_envs, s, 0);
+    return k1_dispatch(params, state, buf, n_envs, s, 0, decision_n <= 0);  // chunked callers bump the counter themselves
 }
 
 extern "C" {
@@ -219,6 +219,7 @@ int oige_env_step_host_f32(const OigeModel* model, const OigeTaskParams* params,
         OigeTaskBuffers bf = *buf;
         bf.obs += off * OBS; bf.rew += off; bf.reset_buf += off; bf.progress_buf += off; bf.potentials += off;
         bf.prev_potentials += off; bf.up_vec += off * 3; bf.heading_vec += off * 3; bf.actions += off * D;
+        bf.reset_counter = nullptr;  // chunks share the host-provided counter
         OigeResetInit in = *init;
         in.initial_root_pos += off * 3; in.initial_root_rot += off * 4; in.initial_dof_pos += off * D;
         float* stage = actions_dev_staging + off * D;

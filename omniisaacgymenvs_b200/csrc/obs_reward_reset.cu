@@ -102,6 +102,7 @@ struct K1Args {
     long long* reset;
     long long* progress;
     double* stats;  // [OIGE_STATS_SLOTS][4] or null
+    unsigned long long* step_counter;  // device-side reset counter to bump (whole-step calls only) or null
     long long n;
     int use_bulk;
 };
@@ -450,6 +451,7 @@ __global__ void __launch_bounds__(4 * E) obs_reward_reset_kernel(const __grid_co
             atomicAdd(slot + 2, l);
             atomicAdd(slot + 3, (double)cnt);
         }
+        if (A.step_counter != nullptr && blockIdx.x == 0) *A.step_counter += 1;  // K3 of this step already ran
         if (bulk) bulk_wait_read0();  // smem must stay alive until the TMA engine has read it
     }
 }
@@ -482,7 +484,7 @@ inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 
 // Tile size: 32 envs (128 threads, ~26 KB smem -> 8 CTAs/SM); 64-env tiles (256 threads) stay available
 // through oige_obs_reward_reset_tile_f32 for sweeps.
 int k1_dispatch(const OigeTaskParams* P, const OigeState* st, const OigeTaskBuffers* b, int64_t n,
-                cudaStream_t stream, int force_tile) {
+                cudaStream_t stream, int force_tile, bool bump_counter) {
     K1Args A;
     A.pos = st->root_pos; A.quat = st->root_quat; A.vel = st->root_vel;
     A.q = st->dof_pos; A.qd = st->dof_vel; A.sens = st->sensors; A.act = b->actions;
@@ -491,6 +493,7 @@ int k1_dispatch(const OigeTaskParams* P, const OigeState* st, const OigeTaskBuff
     A.reset = reinterpret_cast<long long*>(b->reset_buf);
     A.progress = reinterpret_cast<long long*>(b->progress_buf);
     A.stats = b->episode_stats;
+    A.step_counter = bump_counter ? reinterpret_cast<unsigned long long*>(b->reset_counter) : nullptr;
     A.n = n;
     const void* ptrs[] = {A.pos, A.quat, A.vel, A.q, A.qd, A.sens, A.act, A.pot, A.prev_pot,
                           A.obs, A.rew, A.up, A.head, A.reset, A.progress};

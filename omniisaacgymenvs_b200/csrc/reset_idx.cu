@@ -20,6 +20,9 @@ struct K3Args {
     const float* rand_pos; const float* rand_vel;   // [rows, D] raw uniforms or null
     const long long* env_ids;                        // idx form only
     unsigned long long seed, counter;
+    const unsigned long long* counter_dev;           // if set, overrides `counter` (CUDA-graph replays)
+    const float* actions_in; float* actions_out; float clip;  // masked form: fused action clamp
+    int num_dof;
     long long env_id_offset;
     long long n;                                     // envs (masked) or ids (idx)
 };
@@ -63,13 +66,27 @@ __global__ void __launch_bounds__(128) reset_masked_kernel(const __grid_constant
     const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const long long base = warp * 32;
     if (base >= A.n) return;
+    if (A.actions_in != nullptr) {
+        // VecEnvRLGames.step's torch.clamp(actions, -clip, clip) (envs/vec_env_rlgames.py:57) for the 32 envs
+        // of this warp: one contiguous, coalesced chunk of the [N,D] action tensor
+        const long long cnt = ((A.n - base) < 32 ? (A.n - base) : 32) * A.num_dof;
+        const float* in = A.actions_in + base * A.num_dof;
+        float* out = A.actions_out + base * A.num_dof;
+        for (long long i = lane; i < cnt; i += 32) {
+            const float v = in[i];
+            out[i] = v < -A.clip ? -A.clip : (v > A.clip ? A.clip : v);
+        }
+    }
     const long long e = base + lane;
     const bool flag = (e < A.n) && (A.reset[e] != 0);
     unsigned m = __ballot_sync(0xffffffffu, flag);
+    if (m == 0) return;
+    K3Args B = A;
+    if (A.counter_dev != nullptr) B.counter = *A.counter_dev;
     while (m) {
         const int b = __ffs(m) - 1;
         m &= m - 1;
-        reset_one_env(P, A, base + b, base + b, lane);
+        reset_one_env(P, B, base + b, base + b, lane);
     }
 }
 
@@ -98,11 +115,14 @@ int fill(K3Args& A, const OigeState* st, const OigeTaskBuffers* b, const OigeRes
 
 int k3_masked(const OigeTaskParams* P, const OigeState* st, const OigeTaskBuffers* b, const OigeResetInit* init,
               const float* rand_pos, const float* rand_vel, uint64_t seed, uint64_t counter,
-              int64_t env_id_offset, int64_t n, cudaStream_t stream) {
+              int64_t env_id_offset, int64_t n, cudaStream_t stream, const float* actions_in, float clip) {
     K3Args A{};
     if (int rc = fill(A, st, b, init)) return rc;
     if (P->num_dof < 1 || P->num_dof > OIGE_MAX_DOF) return fail(OIGE_E_SHAPE, "reset: num_dof %d", P->num_dof);
     A.rand_pos = rand_pos; A.rand_vel = rand_vel; A.env_ids = nullptr;
+    A.actions_in = actions_in; A.actions_out = b->actions; A.clip = clip; A.num_dof = P->num_dof;
+    A.counter_dev = actions_in ? reinterpret_cast<const unsigned long long*>(b->reset_counter) : nullptr;
+    if (actions_in && !b->actions) return fail(OIGE_E_NULL, "reset: null actions buffer");
     A.seed = seed; A.counter = counter; A.env_id_offset = env_id_offset; A.n = n;
     const long long warps = (n + 31) / 32;
     const unsigned blocks = (unsigned)((warps + 3) / 4);

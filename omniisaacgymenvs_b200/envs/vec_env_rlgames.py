@@ -31,10 +31,54 @@ class VecEnvRLGames(VecEnvBase):
         self.num_states = self._task.num_states
         self.state_space = self._task.state_space
 
+    # ---- CUDA-graph mode ------------------------------------------------
+    def enable_cuda_graph(self) -> None:
+        """Captures the whole step (K3 with the action clamp, K2, K1 and the rl_device hand-off copies) in
+        ONE CUDA graph.  After this call ``step`` copies the actions into a static buffer and replays the
+        graph: one launch per step instead of three kernels + three copies.  The returned tensors are then
+        STATIC buffers that are overwritten by the next step (rl_games copies them into its own rollout
+        storage right away); everything else behaves as before.  The Philox reset counter lives on the
+        device and is advanced by the step itself, so replays draw fresh reset noise."""
+        task = self._task
+        if not (getattr(task, "supports_fused_step", False) and task.fused_step_enabled()):
+            raise RuntimeError("CUDA-graph mode needs a stock locomotion task (fused step)")
+        dev = torch.device(task.device)
+        self._g_actions = torch.zeros((self.num_envs, task.num_actions), device=dev)
+        dt = self._world.get_physics_dt()
+        # replays must continue the host-side counter sequence: the captured call uses *counter_dev
+        task._reset_counter_dev.fill_(task._reset_counter + 1)
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        self._graph = torch.cuda.CUDAGraph()
+        self.graph_replays = 0
+        launches0 = _lib.launch_count()
+        saved = task._reset_counter
+        with torch.cuda.graph(self._graph, stream=side):
+            task.fused_step(self._g_actions, dt, graph_mode=True)
+            self._obs, self._rew, self._resets = task.obs_buf, task.rew_buf, task.reset_buf
+            self._states = task.get_states()
+            self._extras = task.extras
+            self._process_data()
+        task._reset_counter = saved  # capture does not execute the step
+        self.graph_kernels = _lib.launch_count() - launches0  # kernels of liboige_b200.so inside one replay
+        self._g_out = ({"obs": self._obs, "states": self._states}, self._rew, self._resets)
+        torch.cuda.current_stream(dev).wait_stream(side)
+
+    def disable_cuda_graph(self) -> None:
+        self._graph = None
+
     def step(self, actions):
         task = self._task
         if task.randomize_actions or task.randomize_observations:
             raise RuntimeError("domain randomisation is not part of this build (SURVEY.md section 8(f) N3)")
+        if getattr(self, "_graph", None) is not None:
+            self._g_actions.copy_(actions, non_blocking=True)
+            self._graph.replay()
+            self.graph_replays += 1
+            task._reset_counter += 1  # host mirror of the device-side counter
+            self.sim_frame_count += task.control_frequency_inv
+            self._world.current_time_step_index += task.control_frequency_inv
+            return self._g_out[0], self._g_out[1], self._g_out[2], task.extras.copy()
         if getattr(task, "supports_fused_step", False) and task.fused_step_enabled():
             actions = actions.to(task.device)
             task.fused_step(actions, self._world.get_physics_dt())

@@ -112,7 +112,14 @@ class LocomotionTask(RLTask):
         self._buffers = _lib.OigeTaskBuffers(
             self.obs_buf.data_ptr(), self.rew_buf.data_ptr(), self.reset_buf.data_ptr(), self.progress_buf.data_ptr(),
             self.potentials.data_ptr(), self.prev_potentials.data_ptr(), self.up_vec.data_ptr(),
-            self.heading_vec.data_ptr(), self.actions.data_ptr(), self.episode_stats.data_ptr())
+            self.heading_vec.data_ptr(), self.actions.data_ptr(), self.episode_stats.data_ptr(), None)
+        # CUDA-graph twin: the Philox reset counter lives on the device and is bumped by the step itself
+        self._reset_counter_dev = torch.zeros(1, dtype=torch.int64, device=self._device)
+        self._buffers_graph = _lib.OigeTaskBuffers(
+            self.obs_buf.data_ptr(), self.rew_buf.data_ptr(), self.reset_buf.data_ptr(), self.progress_buf.data_ptr(),
+            self.potentials.data_ptr(), self.prev_potentials.data_ptr(), self.up_vec.data_ptr(),
+            self.heading_vec.data_ptr(), self.actions.data_ptr(), self.episode_stats.data_ptr(),
+            self._reset_counter_dev.data_ptr())
         # staging twins for the individually-callable get_observations / calculate_metrics / is_done
         self._staged_rew = torch.zeros_like(self.rew_buf)
         self._staged_reset = torch.zeros_like(self.reset_buf)
@@ -120,7 +127,7 @@ class LocomotionTask(RLTask):
         self._staged_buffers = _lib.OigeTaskBuffers(
             self.obs_buf.data_ptr(), self._staged_rew.data_ptr(), self._staged_reset.data_ptr(),
             self._staged_progress.data_ptr(), self.potentials.data_ptr(), self.prev_potentials.data_ptr(),
-            self.up_vec.data_ptr(), self.heading_vec.data_ptr(), self.actions.data_ptr(), None)
+            self.up_vec.data_ptr(), self.heading_vec.data_ptr(), self.actions.data_ptr(), None, None)
         self._reset_init = _lib.OigeResetInit(
             self.initial_root_pos.data_ptr(), self.initial_root_rot.data_ptr(), self.initial_dof_pos.data_ptr())
         self._bound = (self.obs_buf.data_ptr(), self.rew_buf.data_ptr(), self.reset_buf.data_ptr(),
@@ -248,8 +255,9 @@ class LocomotionTask(RLTask):
                 and cls.reset_idx is LocomotionTask.reset_idx
                 and self._env._world.is_playing())
 
-    def fused_step(self, actions: torch.Tensor, physics_dt: float) -> None:
-        """VecEnvRLGames.step (envs/vec_env_rlgames.py:56-78) as one C-ABI call."""
+    def fused_step(self, actions: torch.Tensor, physics_dt: float, graph_mode: bool = False) -> None:
+        """VecEnvRLGames.step (envs/vec_env_rlgames.py:56-78) as one C-ABI call.  ``graph_mode`` takes the
+        reset counter from device memory so the call can be captured in a CUDA graph."""
         self._check_bound()
         a = actions
         if a.dtype != torch.float32 or not a.is_contiguous():
@@ -258,7 +266,8 @@ class LocomotionTask(RLTask):
         lib = _lib.load()
         rc = lib.oige_env_step_f32(
             self._robots.model_handle, C.byref(self._params), C.byref(self._robots.state_struct),
-            C.byref(self._buffers), C.byref(self._reset_init), _lib.dptr(a, torch.float32, "actions"),
+            C.byref(self._buffers_graph if graph_mode else self._buffers), C.byref(self._reset_init),
+            _lib.dptr(a, torch.float32, "actions"),
             float(self.clip_actions), self._reset_seed, self._reset_counter, self.env_id_offset, self._num_envs,
             int(self.control_frequency_inv), float(physics_dt), self._stream())
         _lib.check(rc, "oige_env_step_f32")

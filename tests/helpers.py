@@ -87,7 +87,7 @@ class DeviceCase:
                                   self.progress_buf.data_ptr(), self.potentials.data_ptr(),
                                   self.prev_potentials.data_ptr(), self.up_vec.data_ptr(),
                                   self.heading_vec.data_ptr(), self.actions.data_ptr(),
-                                  self.stats.data_ptr() if self.stats is not None else None)
+                                  self.stats.data_ptr() if self.stats is not None else None, None)
         return st, bf
 
     def outputs(self):

@@ -233,3 +233,31 @@ def test_task_classes_reproduce_the_reference_episode(cuda_lib, robot):
                "heading_vec": task.heading_vec}
         ref = {k: ep[k][t] for k in got}
         helpers.assert_k1_matches({k: x.detach().cpu() for k, x in got.items()}, ref, f"{robot} step {t}")
+
+
+@pytest.mark.parametrize("robot,n", [("Humanoid", 512), ("Ant", 4099), ("Humanoid", 16384)])
+def test_cuda_graph_step_equals_eager_step(cuda_lib, robot, n):
+    """enable_cuda_graph(): the whole step captured once and replayed must be bit-identical to the eager
+    step, including the reset noise (device-side Philox counter advanced by the step itself)."""
+    env_a, task_a = make_env(robot, num_envs=n, seed=9, overrides={"task.env.episodeLength": 12})
+    env_b, task_b = make_env(robot, num_envs=n, seed=9, overrides={"task.env.episodeLength": 12})
+    env_a.reset(); env_b.reset()
+    env_b.enable_cuda_graph()
+    g = torch.Generator().manual_seed(0)
+    total_resets = 0
+    for step in range(30):
+        a = (torch.rand(n, task_a.num_actions, generator=g) * 2.4 - 1.2).to(task_a.device)
+        oa, ra, da, _ = env_a.step(a)
+        ob, rb, db, _ = env_b.step(a)
+        assert torch.equal(oa["obs"], ob["obs"]), f"obs differ at step {step}"
+        assert torch.equal(ra, rb) and torch.equal(da, db)
+        total_resets += int(da.sum())
+    assert total_resets > n  # several reset waves went through the graph
+    sa, sb = _snapshot(task_a), _snapshot(task_b)
+    for k in sa:
+        assert torch.equal(sa[k], sb[k]), k
+    assert task_a._reset_counter == task_b._reset_counter
+    env_b.disable_cuda_graph()
+    oa, ra, da, _ = env_a.step(a)
+    ob, rb, db, _ = env_b.step(a)
+    assert torch.equal(oa["obs"], ob["obs"]) and torch.equal(da, db)

@@ -108,7 +108,7 @@ def test_k1_unaligned_views_take_the_plain_path(cuda_lib, robot):
     bf = _lib.OigeTaskBuffers(big.obs[1:].data_ptr(), big.rew[1:].data_ptr(), big.reset_buf[1:].data_ptr(),
                               big.progress_buf[1:].data_ptr(), big.potentials[1:].data_ptr(),
                               big.prev_potentials[1:].data_ptr(), big.up_vec[1:].data_ptr(),
-                              big.heading_vec[1:].data_ptr(), big.actions[1:].data_ptr(), None)
+                              big.heading_vec[1:].data_ptr(), big.actions[1:].data_ptr(), None, None)
     p = helpers.params_from_spec(spec, s["dof_lo"], s["dof_hi"])
     _lib.check(cuda_lib.oige_obs_reward_reset_f32(C.byref(p), C.byref(st), C.byref(bf), n,
                                                   _lib.current_stream_ptr(dev)), "k1")

@@ -1,0 +1,25 @@
+"""Whole-step timing (GPU box): eager vs CUDA-graph VecEnvRLGames.step at several env counts."""
+import os, sys, statistics, io, contextlib
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
+import torch
+from omniisaacgymenvs_b200.utils.task_util import make_env
+for robot in ("Humanoid", "Ant"):
+    for n in (1024, 4096, 16384, 65536):
+        out = [f"{robot} n={n:6d}"]
+        for graph in (False, True):
+            with contextlib.redirect_stdout(io.StringIO()):
+                env, task = make_env(robot, num_envs=n); env.reset()
+            if graph: env.enable_cuda_graph()
+            dev = torch.device(task.device)
+            acts = [torch.rand(n, task.num_actions, device=dev) * 2 - 1 for _ in range(8)]
+            for i in range(20): env.step(acts[i % 8])
+            torch.cuda.synchronize()
+            import time
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0 = time.perf_counter(); e0.record()
+            for i in range(200): env.step(acts[i % 8])
+            e1.record(); torch.cuda.synchronize(); wall = (time.perf_counter() - t0) / 200
+            ms = e0.elapsed_time(e1) / 200
+            out.append(f"{'graph' if graph else 'eager'}: {ms*1e3:7.1f} us/step dev, {wall*1e6:7.1f} us wall ({n/ms/1e3:6.1f} M env-steps/s)")
+            del env, task
+        print(" | ".join(out), flush=True)
