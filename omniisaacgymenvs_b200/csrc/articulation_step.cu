@@ -1,17 +1,24 @@
-// K2 -- batched reduced-coordinate articulation step, one warp per environment (sm_100a).
+// K2 -- batched reduced-coordinate articulation step (sm_100a).
 //
 // Stands in for `set_joint_efforts` + `control_frequency_inv x World.step` of the reference
 // (tasks/shared/locomotion.py:108-114, envs/vec_env_rlgames.py:64-66), i.e. for the PhysX 5 GPU
 // articulation pipeline that cannot be installed here.  See DESIGN.md "K2" for the model.
 //
-//   lane i            = link i of the kinematic tree (lane 0 = floating root, one link per DoF)
+// Two kernels integrate the same equations with the same device functions:
+//   articulation_step_kernel      one WARP per env, lane = link (lane 0 = floating root, one link per
+//                                 DoF); parent<->child exchange by warp shuffles; forward kinematics by
+//                                 pointer jumping; small robots packed several envs per warp.  Lowest
+//                                 latency for few environments.
+//   articulation_step_tpe_kernel  one THREAD per env; per-link intermediates in per-thread local memory,
+//                                 articulated inertias carried up heavy paths in registers.  ~7x fewer
+//                                 issue slots per env: used from 8192 environments on.
+//
 //   spatial vectors   = (angular xyz, linear xyz) in WORLD-aligned axes about the point O that
 //                       coincides with the root origin at the start of the substep, so that
-//                       parent->child propagation needs no frame transforms: the tree recursion
-//                       is pure shuffle + add.
+//                       parent->child propagation needs no frame transforms.
 //   forward dynamics  = articulated-body algorithm: top-down kinematics, bottom-up articulated
-//                       inertia (symmetric 6x6, 21 registers/lane), 6x6 Cholesky at the root,
-//                       top-down accelerations.  Parent/child exchange = warp shuffles.
+//                       inertia (symmetric 6x6, 21 floats), 6x6 Cholesky at the root, top-down
+//                       accelerations.
 //   time stepping     = linearly-implicit Euler: joint springs/dampers/limit penalties and the
 //                       ground-contact spring-damper-friction forces are evaluated at the
 //                       end-of-step velocity, which adds a PSD term to the joint-space inertia
