@@ -96,6 +96,7 @@ typedef struct OigeState {
     float* dof_pos;    /* [N,D] */
     float* dof_vel;    /* [N,D] */
     float* sensors;    /* [N,S,6] force, torque at each foot sensor (sensor frame) */
+    float* dof_pos_targets; /* [N,D] PD position targets (set_joint_position_targets) or NULL = effort control only */
 } OigeState;
 
 /* RL buffers of the task.  Replaces RLTask.cleanup buffers (tasks/base/rl_task.py:98-107) and
@@ -146,6 +147,9 @@ typedef struct OigeModelDesc {
     float spring_ref[OIGE_MAX_LINKS];
     float limit_lower[OIGE_MAX_LINKS];
     float limit_upper[OIGE_MAX_LINKS];
+    float drive_stiffness[OIGE_MAX_LINKS];   /* PD position drive: tau = kp (target - q) - kd qd, |tau| <= max force */
+    float drive_damping[OIGE_MAX_LINKS];
+    float drive_max_force[OIGE_MAX_LINKS];   /* <= 0: unlimited */
     int32_t sphere_link[OIGE_MAX_SPHERES];
     float sphere_pos[OIGE_MAX_SPHERES][3];   /* link frame */
     float sphere_radius[OIGE_MAX_SPHERES];

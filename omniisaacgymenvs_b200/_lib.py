@@ -44,7 +44,7 @@ class OigeTaskParams(C.Structure):
 
 class OigeState(C.Structure):
     _fields_ = [("root_pos", vp), ("root_quat", vp), ("root_vel", vp), ("dof_pos", vp), ("dof_vel", vp),
-                ("sensors", vp)]
+                ("sensors", vp), ("dof_pos_targets", vp)]
 
 
 class OigeTaskBuffers(C.Structure):
@@ -64,7 +64,8 @@ class OigeModelDesc(C.Structure):
         ("joint_axis", (f32 * 3) * MAX_LINKS), ("mass", f32 * MAX_LINKS), ("com", (f32 * 3) * MAX_LINKS),
         ("inertia", (f32 * 6) * MAX_LINKS), ("armature", f32 * MAX_LINKS), ("damping", f32 * MAX_LINKS),
         ("stiffness", f32 * MAX_LINKS), ("spring_ref", f32 * MAX_LINKS), ("limit_lower", f32 * MAX_LINKS),
-        ("limit_upper", f32 * MAX_LINKS),
+        ("limit_upper", f32 * MAX_LINKS), ("drive_stiffness", f32 * MAX_LINKS), ("drive_damping", f32 * MAX_LINKS),
+        ("drive_max_force", f32 * MAX_LINKS),
         ("sphere_link", i32 * MAX_SPHERES), ("sphere_pos", (f32 * 3) * MAX_SPHERES),
         ("sphere_radius", f32 * MAX_SPHERES), ("sensor_link", i32 * MAX_SENSORS),
         ("gravity", f32 * 3), ("contact_stiffness", f32), ("contact_damping", f32), ("friction_mu", f32),

@@ -76,9 +76,10 @@ class ArticulationView:
         self.root_quat[:, 0] = 1.0
         self._dof_limits = torch.from_numpy(model.dof_limits()).to(self._device)
         self._physics_view = _PhysicsView(self)
+        self.dof_pos_targets = None  # allocated by the first set_joint_position_targets (PD position drive)
         self._state_struct = _lib.OigeState(
             self.root_pos.data_ptr(), self.root_quat.data_ptr(), self.root_vel.data_ptr(), self.dof_pos.data_ptr(),
-            self.dof_vel.data_ptr(), self.sensor_forces.data_ptr())
+            self.dof_vel.data_ptr(), self.sensor_forces.data_ptr(), None)
 
     def __del__(self):
         h = getattr(self, "_model_handle", None)
@@ -133,6 +134,14 @@ class ArticulationView:
 
     def set_joint_efforts(self, efforts: torch.Tensor, indices=None) -> None:
         self.dof_efforts[self._idx(indices)] = efforts
+
+    def set_joint_position_targets(self, positions: torch.Tensor, indices=None) -> None:
+        """PD position targets (the Anymal-style actuation, tasks/anymal.py:185-187): from the first call on the
+        articulation kernel applies tau = kp (target - q) - kd qd with the model's drive gains, on top of efforts."""
+        if self.dof_pos_targets is None:
+            self.dof_pos_targets = self.dof_pos.clone()
+            self._state_struct.dof_pos_targets = self.dof_pos_targets.data_ptr()
+        self.dof_pos_targets[self._idx(indices)] = positions
 
     def set_joint_positions(self, positions: torch.Tensor, indices=None) -> None:
         self.dof_pos[self._idx(indices)] = positions

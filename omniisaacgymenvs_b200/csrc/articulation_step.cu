@@ -78,6 +78,7 @@ struct DevModel {
     float com[3][32];
     float inertia[6][32];  // xx yy zz xy xz yz
     float armature[32], damping[32], stiffness[32], sref[32], lo[32], hi[32];
+    float drive_kp[32], drive_kd[32], drive_fmax[32];
     float sph_pos[3][OIGE_MAX_SPHERES];
     float sph_r[OIGE_MAX_SPHERES];
     float gravity[4];
@@ -181,6 +182,7 @@ __device__ __forceinline__ bool contact_eval(const DevModel& M, int s, const M3&
 struct K2Args {
     float* pos; float* quat; float* vel; float* q; float* qd; float* sens;
     const float* actions;
+    const float* targets;  // [N,D] PD position targets or null
     long long n;
     int substeps;
     float dt;
@@ -265,7 +267,7 @@ __device__ __forceinline__ void link_contacts(const DevModel& M, int li, const M
 // Joint-space force at the end-of-step position (actuation + passive spring/damper + limit penalty)
 // and the implicit diagonal term armature + dt D + dt^2 K.
 __device__ __forceinline__ void joint_force(const DevModel& M, int li, float q, float qd, float effort, float dt,
-                                            float& tau0, float& dextra) {
+                                            bool has_target, float target, float& tau0, float& dextra) {
     const float Ks = M.stiffness[li], Dj = M.damping[li];
     const float qn = fmaf(dt, qd, q);  // position the springs see at the end of the step
     float Kimp = Ks, Dimp = Dj;
@@ -277,6 +279,18 @@ __device__ __forceinline__ void joint_force(const DevModel& M, int li, float q, 
     } else if (q > hi) {
         tau0 += -M.k_lim * (qn - hi) - M.d_lim * qd;
         Kimp += M.k_lim; Dimp += M.d_lim;
+    }
+    if (has_target) {
+        // PD position drive (ArticulationView.set_joint_position_targets): implicit like the passive spring,
+        // unless it saturates at the drive's force limit, where it acts as a constant torque
+        const float kp = M.drive_kp[li], kd = M.drive_kd[li], fmax = M.drive_fmax[li];
+        const float tpd = kp * (target - qn) - kd * qd;
+        if (fmax > 0.f && fabsf(tpd) > fmax) {
+            tau0 += copysignf(fmax, tpd);
+        } else {
+            tau0 += tpd;
+            Kimp += kp; Dimp += kd;
+        }
     }
     dextra = M.armature[li] + dt * (Dimp + dt * Kimp);
 }
@@ -395,11 +409,12 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
     const int D = P.num_dof;
 
     // ---- load state -------------------------------------------------------------------------
-    float q = 0.f, qd = 0.f, effort = 0.f;
+    float q = 0.f, qd = 0.f, effort = 0.f, target = 0.f;
     if (is_joint) {
         q = A.q[env * D + dofi];
         qd = A.qd[env * D + dofi];
         effort = A.actions[env * D + dofi] * P.joint_gears[dofi] * P.power_scale;  // locomotion.py:109
+        if (A.targets != nullptr) target = A.targets[env * D + dofi];
     }
     V3 rpos = {0.f, 0.f, 0.f};
     Q4 rquat = {1.f, 0.f, 0.f, 0.f};
@@ -523,7 +538,7 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
 
         // ---- joint-space force and implicit diagonal ----------------------------------------------
         float tau0 = 0.f, dextra = 1.f;
-        if (is_joint) joint_force(M, li, q, qd, effort, dt, tau0, dextra);
+        if (is_joint) joint_force(M, li, q, qd, effort, dt, A.targets != nullptr, target, tau0, dextra);
 
         // ---- pass 2: articulated inertia, bottom-up -------------------------------------------------
         V6 U = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
@@ -675,13 +690,14 @@ articulation_step_tpe_kernel(const DevModel* __restrict__ gmodel, const __grid_c
     float pu[MAXL][8];
     float slotI[kMaxSlots][27];
     float slotA[kMaxSlots][6];
-    float qv[MAXL], qdv[MAXL], eff[MAXL];
+    float qv[MAXL], qdv[MAXL], eff[MAXL], tgt[MAXL];
 
     for (int i = 1; i < L; ++i) {
         const int d = M.dof[i];
         qv[i] = A.q[env * D + d];
         qdv[i] = A.qd[env * D + d];
         eff[i] = A.actions[env * D + d] * P.joint_gears[d] * P.power_scale;  // locomotion.py:109
+        tgt[i] = A.targets != nullptr ? A.targets[env * D + d] : 0.f;
     }
     V3 rpos = {A.pos[env * 3], A.pos[env * 3 + 1], A.pos[env * 3 + 2]};
     Q4 rquat;
@@ -798,7 +814,7 @@ articulation_step_tpe_kernel(const DevModel* __restrict__ gmodel, const __grid_c
                 c = mk6(qd * ca, qd * cl);
             }
             float tau0, dextra;
-            joint_force(M, i, q, qd, eff[i], dt, tau0, dextra);
+            joint_force(M, i, q, qd, eff[i], dt, A.targets != nullptr, tgt[i], tau0, dextra);
             const V6 U = s6mul(IA, s);
             const float dinv = 1.f / (dot6(s, U) + dextra);
             const float u = tau0 - dot6(s, pA);
@@ -957,7 +973,7 @@ int k2_step(const OigeModel* model, const OigeTaskParams* P, const OigeState* st
         return fail(OIGE_E_SHAPE, "articulation_step: params.num_dof %d != model dofs %d", P->num_dof, model->num_dof);
     K2Args A;
     A.pos = st->root_pos; A.quat = st->root_quat; A.vel = st->root_vel; A.q = st->dof_pos; A.qd = st->dof_vel;
-    A.sens = st->sensors; A.actions = actions; A.n = n; A.substeps = substeps; A.dt = dt;
+    A.sens = st->sensors; A.targets = st->dof_pos_targets; A.actions = actions; A.n = n; A.substeps = substeps; A.dt = dt;
     if (!A.pos || !A.quat || !A.vel || !A.q || !A.qd) return fail(OIGE_E_NULL, "articulation_step: null state pointer");
     if (reinterpret_cast<uintptr_t>(A.quat) & 15u) return fail(OIGE_E_ALIGN, "articulation_step: root_quat not 16B aligned");
     if (model->num_sensors > 0 && P->num_sensors != model->num_sensors)
@@ -1074,6 +1090,7 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
         for (int k = 0; k < 6; ++k) h->inertia[k][i] = d->inertia[i][k];
         h->mass[i] = d->mass[i]; h->armature[i] = d->armature[i]; h->damping[i] = d->damping[i];
         h->stiffness[i] = d->stiffness[i]; h->sref[i] = d->spring_ref[i]; h->lo[i] = d->limit_lower[i]; h->hi[i] = d->limit_upper[i];
+        h->drive_kp[i] = d->drive_stiffness[i]; h->drive_kd[i] = d->drive_damping[i]; h->drive_fmax[i] = d->drive_max_force[i];
     }
     h->jquat[0][0] = 1.f;
     // spheres sorted by link (stable)

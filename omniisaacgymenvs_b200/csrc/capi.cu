@@ -216,6 +216,7 @@ int oige_env_step_host_f32(const OigeModel* model, const OigeTaskParams* params,
         st.root_pos += off * 3; st.root_quat += off * 4; st.root_vel += off * 6;
         st.dof_pos += off * D; st.dof_vel += off * D;
         if (st.sensors) st.sensors += off * 6 * S;
+        if (st.dof_pos_targets) st.dof_pos_targets += off * D;
         OigeTaskBuffers bf = *buf;
         bf.obs += off * OBS; bf.rew += off; bf.reset_buf += off; bf.progress_buf += off; bf.potentials += off;
         bf.prev_potentials += off; bf.up_vec += off * 3; bf.heading_vec += off * 3; bf.actions += off * D;

@@ -72,6 +72,9 @@ class ArticulationModel:
     spring_ref: np.ndarray
     limit_lower: np.ndarray       # [L] rad
     limit_upper: np.ndarray
+    drive_stiffness: np.ndarray   # [L] PD position-drive gains (0 = no drive)
+    drive_damping: np.ndarray
+    drive_max_force: np.ndarray   # <= 0: unlimited
     sphere_link: np.ndarray       # [K]
     sphere_pos: np.ndarray        # [K,3]
     sphere_radius: np.ndarray     # [K]
@@ -201,6 +204,7 @@ def build_model(name: str, **overrides) -> ArticulationModel:
         joint_axis=np.array(jaxis, np.float64), mass=mass, com=com, inertia=inertia,
         armature=np.array(arm), damping=np.array(damp), stiffness=np.array(stiff), spring_ref=np.zeros(L),
         limit_lower=np.array(lo), limit_upper=np.array(hi),
+        drive_stiffness=np.zeros(L), drive_damping=np.zeros(L), drive_max_force=np.zeros(L),
         sphere_link=np.array(sph_link, np.int32), sphere_pos=np.array(sph_pos, np.float64),
         sphere_radius=np.array(sph_r, np.float64),
         sensor_link=np.array([last_link[s] for s in table["sensor_bodies"]], np.int32),
@@ -236,6 +240,9 @@ def fill_desc(model: ArticulationModel, desc) -> None:
         desc.spring_ref[i] = float(model.spring_ref[i])
         desc.limit_lower[i] = float(model.limit_lower[i])
         desc.limit_upper[i] = float(model.limit_upper[i])
+        desc.drive_stiffness[i] = float(model.drive_stiffness[i])
+        desc.drive_damping[i] = float(model.drive_damping[i])
+        desc.drive_max_force[i] = float(model.drive_max_force[i])
     for s in range(K):
         desc.sphere_link[s] = int(model.sphere_link[s])
         desc.sphere_radius[s] = float(model.sphere_radius[s])

@@ -34,7 +34,7 @@ def _load():
     if _lib is None:
         lib = C.CDLL(build())
         dp = C.POINTER(C.c_double)
-        lib.oracle_articulation_step_f64.argtypes = [C.c_void_p, C.c_int64, dp, dp, dp, dp, dp, dp, dp, C.c_int,
+        lib.oracle_articulation_step_f64.argtypes = [C.c_void_p, C.c_int64, dp, dp, dp, dp, dp, dp, dp, dp, C.c_int,
                                                      C.c_double, C.c_int]
         lib.oracle_articulation_step_f64.restype = C.c_int
         lib.oracle_energy_f64.argtypes = [C.c_void_p, dp, dp, dp, dp, dp]
@@ -57,13 +57,14 @@ def make_desc(model):
     return desc
 
 
-def step(desc, pos, quat, vel, q, qd, efforts, sensors=None, substeps=1, dt=0.0083, num_threads=1) -> int:
+def step(desc, pos, quat, vel, q, qd, efforts, sensors=None, substeps=1, dt=0.0083, num_threads=1, targets=None) -> int:
     """In-place step of float64 C-contiguous arrays pos[N,3] quat[N,4] vel[N,6] q[N,D] qd[N,D]."""
     for a in (pos, quat, vel, q, qd, efforts):
         assert a.dtype == np.float64 and a.flags.c_contiguous
     n = pos.shape[0]
     return _load().oracle_articulation_step_f64(C.byref(desc), n, _p(pos), _p(quat), _p(vel), _p(q), _p(qd),
-                                                _p(efforts), _p(sensors), int(substeps), float(dt), int(num_threads))
+                                                _p(efforts), _p(targets), _p(sensors), int(substeps), float(dt),
+                                                int(num_threads))
 
 
 def energy(desc, pos, quat, vel, q, qd) -> float:

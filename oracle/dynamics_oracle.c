@@ -136,7 +136,7 @@ static contact contact_eval(const OigeModelDesc* M, int s, m3 R, v3 p, v3 vlin, 
 }
 
 static int step_one(const OigeModelDesc* M, double* pos, double* quat, double* vel, double* q, double* qd,
-                    const double* eff, double* sens, int last, double dt) {
+                    const double* eff, const double* tgt, double* sens, int last, double dt) {
     const int L = M->num_links, D = L - 1, nv = 6 + D;
     m3 R[OIGE_MAX_LINKS];
     v3 p[OIGE_MAX_LINKS], axw[OIGE_MAX_LINKS], w[OIGE_MAX_LINKS], vo[OIGE_MAX_LINKS], al0[OIGE_MAX_LINKS], ac0[OIGE_MAX_LINKS];
@@ -198,6 +198,12 @@ static int step_one(const OigeModelDesc* M, double* pos, double* quat, double* v
         double lo = M->limit_lower[i], hi = M->limit_upper[i];
         if (q[d] < lo) { tau += -(double)M->limit_stiffness * (qn - lo) - (double)M->limit_damping * qd[d]; Kimp += M->limit_stiffness; Dimp += M->limit_damping; }
         else if (q[d] > hi) { tau += -(double)M->limit_stiffness * (qn - hi) - (double)M->limit_damping * qd[d]; Kimp += M->limit_stiffness; Dimp += M->limit_damping; }
+        if (tgt) { /* PD position drive, implicit unless saturated at the force limit */
+            double kp = M->drive_stiffness[i], kd = M->drive_damping[i], fmax = M->drive_max_force[i];
+            double tpd = kp * (tgt[d] - qn) - kd * qd[d];
+            if (fmax > 0 && fabs(tpd) > fmax) tau += copysign(fmax, tpd);
+            else { tau += tpd; Kimp += kp; Dimp += kd; }
+        }
         rhs[c] += tau;
         A[c * NV_MAX + c] += (double)M->armature[i] + dt * (Dimp + dt * Kimp);
     }
@@ -270,8 +276,8 @@ static int step_one(const OigeModelDesc* M, double* pos, double* quat, double* v
  * efforts [N,D] are joint torques in DoF order (actions * gears * power_scale, formed by the caller).
  * Returns 0, or the number of envs whose system matrix was not positive definite. */
 int oracle_articulation_step_f64(const OigeModelDesc* M, int64_t n_envs, double* pos, double* quat, double* vel,
-                                 double* q, double* qd, const double* efforts, double* sensors, int substeps,
-                                 double dt, int num_threads) {
+                                 double* q, double* qd, const double* efforts, const double* targets,
+                                 double* sensors, int substeps, double dt, int num_threads) {
     const int D = M->num_links - 1, S = M->num_sensors;
     int bad = 0;
     (void)num_threads;
@@ -279,7 +285,7 @@ int oracle_articulation_step_f64(const OigeModelDesc* M, int64_t n_envs, double*
     for (int64_t e = 0; e < n_envs; ++e) {
         for (int s = 0; s < substeps; ++s) {
             int rc = step_one(M, pos + 3 * e, quat + 4 * e, vel + 6 * e, q + D * e, qd + D * e, efforts + D * e,
-                              sensors ? sensors + (int64_t)S * 6 * e : 0, s == substeps - 1, dt);
+                              targets ? targets + D * e : 0, sensors ? sensors + (int64_t)S * 6 * e : 0, s == substeps - 1, dt);
             if (rc != 0) { bad += 1; break; }
         }
     }

@@ -52,7 +52,7 @@ def run_gpu(cuda_lib, model, spec, st, substeps, dt, device="cuda:0", calls=1):
     n = st["pos"].shape[0]
     sens = torch.zeros((n, model.num_sensors, 6), device=dev)
     state = _lib.OigeState(t["pos"].data_ptr(), t["quat"].data_ptr(), t["vel"].data_ptr(), t["q"].data_ptr(),
-                           t["qd"].data_ptr(), sens.data_ptr())
+                           t["qd"].data_ptr(), sens.data_ptr(), t["targets"].data_ptr() if "targets" in t else None)
     p = unit_params(model, spec)
     for _ in range(calls):
         rc = cuda_lib.oige_articulation_step_f32(handle, C.byref(p), C.byref(state), t["actions"].data_ptr(), n,
@@ -60,7 +60,7 @@ def run_gpu(cuda_lib, model, spec, st, substeps, dt, device="cuda:0", calls=1):
         _lib.check(rc, "oige_articulation_step_f32")
     torch.cuda.synchronize(dev)
     cuda_lib.oige_model_destroy(handle)
-    out = {k: v.cpu().numpy().astype(np.float64) for k, v in t.items() if k != "actions"}
+    out = {k: v.cpu().numpy().astype(np.float64) for k, v in t.items() if k not in ("actions", "targets")}
     out["sensors"] = sens.cpu().numpy().astype(np.float64)
     return out
 
@@ -68,6 +68,7 @@ def run_gpu(cuda_lib, model, spec, st, substeps, dt, device="cuda:0", calls=1):
 def run_oracle(model, spec, st, substeps, dt, calls=1, threads=8):
     desc = dyn.make_desc(model)
     d = {k: np.ascontiguousarray(v.astype(np.float64)) for k, v in st.items()}
+    tg = d.get("targets")
     gears = model.joint_gears.astype(np.float32)
     # efforts formed in fp32 exactly as the kernel / reference do: (a * gear) * power_scale
     eff = ((st["actions"] * gears).astype(np.float32) * np.float32(spec.power_scale)).astype(np.float64)
@@ -75,7 +76,7 @@ def run_oracle(model, spec, st, substeps, dt, calls=1, threads=8):
     n = st["pos"].shape[0]
     sens = np.zeros((n, model.num_sensors, 6))
     for _ in range(calls):
-        bad = dyn.step(desc, d["pos"], d["quat"], d["vel"], d["q"], d["qd"], eff, sens, substeps, dt, threads)
+        bad = dyn.step(desc, d["pos"], d["quat"], d["vel"], d["q"], d["qd"], eff, sens, substeps, dt, threads, targets=tg)
         assert bad == 0, f"oracle: {bad} envs with a non-SPD system"
     out = {k: d[k] for k in ("pos", "quat", "vel", "q", "qd")}
     out["sensors"] = sens

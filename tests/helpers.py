@@ -82,7 +82,7 @@ class DeviceCase:
 
     def structs(self):
         st = _lib.OigeState(self.pos.data_ptr(), self.quat.data_ptr(), self.vel.data_ptr(), self.dof_pos.data_ptr(),
-                            self.dof_vel.data_ptr(), self.sensors.data_ptr())
+                            self.dof_vel.data_ptr(), self.sensors.data_ptr(), None)
         bf = _lib.OigeTaskBuffers(self.obs.data_ptr(), self.rew.data_ptr(), self.reset_buf.data_ptr(),
                                   self.progress_buf.data_ptr(), self.potentials.data_ptr(),
                                   self.prev_potentials.data_ptr(), self.up_vec.data_ptr(),

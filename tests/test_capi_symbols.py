@@ -37,11 +37,11 @@ def test_every_declared_symbol_is_exported():
 def test_struct_layouts_match_header_sizes():
     # sizes computed by hand from the header: catches ctypes / C drift without running a kernel
     assert ctypes.sizeof(_lib.OigeTaskParams) == 8 * 4 + 16 * 4 + 4 * 16 + 4 * 32 * 4
-    assert ctypes.sizeof(_lib.OigeState) == 6 * 8
+    assert ctypes.sizeof(_lib.OigeState) == 7 * 8
     assert ctypes.sizeof(_lib.OigeTaskBuffers) == 11 * 8
     assert ctypes.sizeof(_lib.OigeResetInit) == 3 * 8
     L, K, S = _lib.MAX_LINKS, _lib.MAX_SPHERES, _lib.MAX_SENSORS
-    expect = 16 + 2 * L * 4 + L * 4 * (3 + 4 + 3 + 1 + 3 + 6 + 6) + K * 4 * (1 + 3 + 1) + S * 4 + (3 + 8) * 4
+    expect = 16 + 2 * L * 4 + L * 4 * (3 + 4 + 3 + 1 + 3 + 6 + 6 + 3) + K * 4 * (1 + 3 + 1) + S * 4 + (3 + 8) * 4
     assert ctypes.sizeof(_lib.OigeModelDesc) == expect
 
 

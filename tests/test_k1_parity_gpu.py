@@ -104,7 +104,7 @@ def test_k1_unaligned_views_take_the_plain_path(cuda_lib, robot):
     dev = torch.device(DEV)
     big = helpers.DeviceCase(spec, s, DEV)
     st = _lib.OigeState(big.pos[1:].data_ptr(), big.quat[1:].data_ptr(), big.vel[1:].data_ptr(),
-                        big.dof_pos[1:].data_ptr(), big.dof_vel[1:].data_ptr(), big.sensors[1:].data_ptr())
+                        big.dof_pos[1:].data_ptr(), big.dof_vel[1:].data_ptr(), big.sensors[1:].data_ptr(), None)
     bf = _lib.OigeTaskBuffers(big.obs[1:].data_ptr(), big.rew[1:].data_ptr(), big.reset_buf[1:].data_ptr(),
                               big.progress_buf[1:].data_ptr(), big.potentials[1:].data_ptr(),
                               big.prev_potentials[1:].data_ptr(), big.up_vec[1:].data_ptr(),

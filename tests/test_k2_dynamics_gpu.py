@@ -89,6 +89,28 @@ def test_rollout_64_with_contacts_statistical(cuda_lib, robot):
     assert np.median(per_env) < 2e-3
 
 
+@pytest.mark.parametrize("robot", ["Humanoid", "Ant"])
+def test_pd_position_drive_matches_oracle(cuda_lib, robot):
+    """PD position-target actuation (set_joint_position_targets): implicit drive, saturating at max force."""
+    model, spec = dh.specs(robot)
+    model.drive_stiffness[1:] = 60.0
+    model.drive_damping[1:] = 3.0
+    model.drive_max_force[1:] = 40.0  # some joints saturate with the random targets below
+    st = dh.random_state(model, 512, 21, height=5.0)
+    rng = np.random.default_rng(3)
+    lim = model.dof_limits()
+    st["targets"] = np.ascontiguousarray((lim[:, 0] + rng.random((512, model.num_dof)) * (lim[:, 1] - lim[:, 0])).astype(np.float32))
+    st["actions"][:] *= 0.2
+    g = dh.run_gpu(cuda_lib, model, spec, st, 2, DT, calls=4)
+    o = dh.run_oracle(model, spec, st, 2, DT, calls=4)
+    assert _err(g["q"], o["q"]) < 1e-4 and _err(g["pos"], o["pos"]) < 1e-4
+    assert (np.abs(g["qd"] - o["qd"]) / np.maximum(1.0, np.abs(o["qd"]))).max() < 5e-3
+    # the drive does something: without targets the joints end elsewhere
+    st2 = {k: v for k, v in st.items() if k != "targets"}
+    g2 = dh.run_gpu(cuda_lib, model, spec, st2, 2, DT, calls=4)
+    assert _err(g["q"], g2["q"]) > 1e-2
+
+
 def test_both_kernels_agree_with_each_other(cuda_lib, monkeypatch):
     """warp-per-env vs thread-per-env on the same state: same model, different summation orders."""
     model, spec = dh.specs("Humanoid")
