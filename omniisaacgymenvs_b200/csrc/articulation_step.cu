@@ -938,23 +938,7 @@ articulation_step_tpe_kernel(const DevModel* __restrict__ gmodel, const __grid_c
     vv[3] = rvel.a[0]; vv[4] = rvel.a[1]; vv[5] = rvel.a[2];
 }
 
-__global__ void clamp_actions_kernel(const float* __restrict__ in, float* __restrict__ out, float clip, long long n) {
-    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) {
-        const float v = in[i];
-        out[i] = v < -clip ? -clip : (v > clip ? clip : v);  // torch.clamp (vec_env_rlgames.py:57)
-    }
-}
-
 }  // namespace
-
-int k2_clamp_actions(const float* in, float* out, float clip, int64_t count, cudaStream_t stream) {
-    if (!in || !out) return fail(OIGE_E_NULL, "clamp_actions: null pointer");
-    const unsigned blocks = (unsigned)((count + 255) / 256);
-    clamp_actions_kernel<<<blocks, 256, 0, stream>>>(in, out, clip, count);
-    count_launch();
-    return check_launch("clamp_actions_kernel");
-}
 
 // Kernel choice: OIGE_K2_MODE=warp|thread forces one; otherwise thread-per-env from kTpeMinEnvs envs on.
 static bool use_thread_per_env(int64_t n) {

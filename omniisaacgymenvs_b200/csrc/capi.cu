@@ -56,7 +56,6 @@ int k3_idx(const OigeTaskParams*, const OigeState*, const OigeTaskBuffers*, cons
            int64_t, const float*, const float*, uint64_t, uint64_t, int64_t, cudaStream_t);
 int k2_step(const OigeModel*, const OigeTaskParams*, const OigeState*, const float*, int64_t, int32_t, float,
             cudaStream_t, int64_t decision_n);
-int k2_clamp_actions(const float* in, float* out, float clip, int64_t count, cudaStream_t);
 OigeModel* k2_model_create(const OigeModelDesc*);
 void k2_model_destroy(OigeModel*);
 
