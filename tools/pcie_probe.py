@@ -1,14 +1,14 @@
-import torch, time
-n=16384
-obs_d=torch.empty(n,87,device='cuda'); obs_h=torch.empty(n,87).pin_memory()
-act_h=torch.empty(n,21).pin_memory(); act_d=torch.empty(n,21,device='cuda')
-for name,(dst,src) in {'D2H obs 5.7MB':(obs_h,obs_d),'H2D act 1.4MB':(act_d,act_h)}.items():
-    for _ in range(3): dst.copy_(src,non_blocking=True)
-    torch.cuda.synchronize(); a=torch.cuda.Event(enable_timing=True); b=torch.cuda.Event(enable_timing=True)
-    a.record()
-    for _ in range(20): dst.copy_(src,non_blocking=True)
-    b.record(); torch.cuda.synchronize(); ms=a.elapsed_time(b)/20
-    print(name, f"{ms*1e3:.1f} us", f"{src.numel()*4/ms/1e6:.1f} GB/s")
-big_d=torch.empty(256<<20,dtype=torch.uint8,device='cuda'); big_h=torch.empty(256<<20,dtype=torch.uint8).pin_memory()
-a=torch.cuda.Event(enable_timing=True); b=torch.cuda.Event(enable_timing=True)
-a.record(); big_h.copy_(big_d,non_blocking=True); b.record(); torch.cuda.synchronize(); print('D2H 256MB', 256/1024/(a.elapsed_time(b)/1e3), 'GB/s')
+"""PCIe copy characteristics of the GPU box (pinned host memory, CUDA events)."""
+import torch
+for size in (64 << 10, 344 << 10, 1376 << 10, 5898 << 10, 64 << 20):
+    h = torch.empty(size, dtype=torch.uint8).pin_memory(); d = torch.empty(size, dtype=torch.uint8, device="cuda")
+    for name, dst, src in (("H2D", d, h), ("D2H", h, d)):
+        for _ in range(3): dst.copy_(src, non_blocking=True)
+        torch.cuda.synchronize()
+        # latency of ONE copy (event around a single transfer) and throughput of 10 back-to-back
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); dst.copy_(src, non_blocking=True); b.record(); torch.cuda.synchronize(); one = a.elapsed_time(b)
+        a.record()
+        for _ in range(10): dst.copy_(src, non_blocking=True)
+        b.record(); torch.cuda.synchronize(); ten = a.elapsed_time(b) / 10
+        print(f"{name} {size/1024:9.0f} KiB: single {one*1e3:7.1f} us, pipelined {ten*1e3:7.1f} us = {size/ten/1e6:6.1f} GB/s")
