@@ -261,3 +261,45 @@ def test_cuda_graph_step_equals_eager_step(cuda_lib, robot, n):
     oa, ra, da, _ = env_a.step(a)
     ob, rb, db, _ = env_b.step(a)
     assert torch.equal(oa["obs"], ob["obs"]) and torch.equal(da, db)
+
+
+def test_rlgames_adapter_protocol(cuda_lib):
+    """RLGPUEnv / RLGPUAlgoObserver (reference utils/rlgames/rlgames_utils.py:38-118) driven the way rl_games'
+    a2c play_steps drives them: get_env_info, reset, step, process_infos, after_print_stats."""
+    from omniisaacgymenvs_b200.utils.rlgames.rlgames_utils import RLGPUAlgoObserver, RLGPUEnv
+
+    env, task = make_env("Ant", num_envs=128)
+    vec = RLGPUEnv("rlgpu", 128, env_creator=lambda **kw: env)
+    info = vec.get_env_info()
+    assert info["action_space"].shape == (8,) and info["observation_space"].shape == (60,) and "state_space" not in info
+    assert vec.get_number_of_agents() == 1
+    obs = vec.reset()
+    assert obs["obs"].shape == (128, 60)
+
+    class Writer:
+        def __init__(self):
+            self.rows = []
+
+        def add_scalar(self, k, v, step):
+            self.rows.append((k, float(v), step))
+
+    class Algo:
+        games_to_track, writer, device = 10, Writer(), task.device
+
+    ob = RLGPUAlgoObserver()
+    ob.after_init(Algo)
+    for _ in range(3):
+        o, r, d, infos = vec.step(torch.rand(128, 8, device=task.device) * 2 - 1)
+        infos = dict(infos, episode={"len": task.progress_buf.float().mean()}, lr=3e-4)
+        ob.process_infos(infos, d.nonzero())
+    ob.mean_scores.update(r)
+    ob.after_print_stats(frame=384, epoch_num=1, total_time=0.1)
+    keys = {k for k, _, _ in Algo.writer.rows}
+    assert {"Episode/len", "lr/frame", "scores/mean"} <= keys
+
+
+def test_random_policy_script_runs(cuda_lib, capsys):
+    from omniisaacgymenvs_b200.scripts import random_policy
+
+    assert random_policy.main(["task=Ant", "num_envs=64", "steps=5"]) == 0
+    assert "5 steps of 64 envs" in capsys.readouterr().out
