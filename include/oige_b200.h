@@ -44,6 +44,7 @@ extern "C" {
 #define OIGE_E_NODEVICE (-6)    /* no CUDA device / wrong architecture */
 
 enum { OIGE_LIMIT_COST_HUMANOID = 0, OIGE_LIMIT_COST_ANT = 1 };
+enum { OIGE_JOINT_HINGE = 0, OIGE_JOINT_PRISMATIC = 1 };
 
 /* Scalar constants of one locomotion task.
  * Replaces: LocomotionTask.__init__ scalars (tasks/shared/locomotion.py:53-67), the per-env
@@ -132,9 +133,10 @@ typedef struct OigeModelDesc {
     int32_t num_links;                       /* 1 + D */
     int32_t num_spheres;
     int32_t num_sensors;
-    int32_t reserved;
+    int32_t fixed_base;                      /* 1: link 0 is welded to the world (Cartpole rail), 0: floating root */
     int32_t parent[OIGE_MAX_LINKS];          /* parent[0] = -1 */
     int32_t dof_index[OIGE_MAX_LINKS];       /* link -> column of dof_pos (BFS dof order); -1 for root */
+    int32_t joint_type[OIGE_MAX_LINKS];      /* OIGE_JOINT_HINGE (rotation about joint_axis) or OIGE_JOINT_PRISMATIC (translation along it) */
     float joint_pos[OIGE_MAX_LINKS][3];      /* joint anchor in the parent link frame */
     float joint_quat[OIGE_MAX_LINKS][4];     /* fixed rotation parent link frame -> this link frame at q=0 (wxyz) */
     float joint_axis[OIGE_MAX_LINKS][3];     /* unit hinge axis in this link's frame */

@@ -58,8 +58,8 @@ class OigeResetInit(C.Structure):
 
 class OigeModelDesc(C.Structure):
     _fields_ = [
-        ("num_links", i32), ("num_spheres", i32), ("num_sensors", i32), ("reserved", i32),
-        ("parent", i32 * MAX_LINKS), ("dof_index", i32 * MAX_LINKS),
+        ("num_links", i32), ("num_spheres", i32), ("num_sensors", i32), ("fixed_base", i32),
+        ("parent", i32 * MAX_LINKS), ("dof_index", i32 * MAX_LINKS), ("joint_type", i32 * MAX_LINKS),
         ("joint_pos", (f32 * 3) * MAX_LINKS), ("joint_quat", (f32 * 4) * MAX_LINKS),
         ("joint_axis", (f32 * 3) * MAX_LINKS), ("mass", f32 * MAX_LINKS), ("com", (f32 * 3) * MAX_LINKS),
         ("inertia", (f32 * 6) * MAX_LINKS), ("armature", f32 * MAX_LINKS), ("damping", f32 * MAX_LINKS),

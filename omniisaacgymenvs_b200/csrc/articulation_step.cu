@@ -58,8 +58,10 @@ constexpr int kHasHeavy = 1, kIsHead = 2, kFirstLight = 4;
 struct DevModel {
     int num_links, num_spheres, num_sensors, max_depth;
     int max_sph_per_link, jump_rounds, pack, tpe_ok;
+    int fixed_base, pad_i[3];
     int parent[32];
     int dof[32];
+    int jtype[32];                   // OIGE_JOINT_HINGE / OIGE_JOINT_PRISMATIC
     int level[32];
     int child[kMaxChildren][32];
     int maxch_at_level[kMaxLevels];  // max #children over parents at this level
@@ -148,6 +150,20 @@ __device__ __forceinline__ float dot6(const V6& a, const V6& b) {
 __device__ __forceinline__ V3 ang(const V6& v) { return {v.a[0], v.a[1], v.a[2]}; }
 __device__ __forceinline__ V3 lin(const V6& v) { return {v.a[3], v.a[4], v.a[5]}; }
 __device__ __forceinline__ V6 mk6(V3 a, V3 l) { return {{a.x, a.y, a.z, l.x, l.y, l.z}}; }
+
+// Motion subspace of a joint whose axis is `aw` (world-aligned) and whose anchor is at p (rel. O):
+// hinge (aw, p x aw), prismatic (0, aw).
+__device__ __forceinline__ V6 joint_subspace(bool prismatic, V3 aw, V3 p) {
+    const V3 zero = {0.f, 0.f, 0.f};
+    return prismatic ? mk6(zero, aw) : mk6(aw, cross(p, aw));
+}
+// Velocity-product acceleration of a joint, c = qd * (v x s) (spatial motion cross product).
+__device__ __forceinline__ V6 velocity_product(const V6& v, const V6& s, float qd) {
+    const V3 w = ang(v), vl = lin(v), sa = ang(s);
+    const V3 ca = cross(w, sa);
+    const V3 cl = cross(w, lin(s)) + cross(vl, sa);
+    return mk6(qd * ca, qd * cl);
+}
 
 __device__ __forceinline__ float shfl(float v, int src) { return __shfl_sync(0xffffffffu, v, src); }
 
@@ -405,6 +421,8 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
     const int parent = active && li > 0 ? ebase + M.parent[li] : lane;
     const int dofi = active ? M.dof[li] : -1;
     const bool is_joint = active && li > 0;
+    const bool prismatic = is_joint && M.jtype[li] == OIGE_JOINT_PRISMATIC;
+    const bool fixed_base = M.fixed_base != 0;
     const float dt = A.dt;
     const int D = P.num_dof;
 
@@ -449,11 +467,12 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
             Q4 ql = {1.f, 0.f, 0.f, 0.f};
             if (is_joint) {
                 float sh, ch;
-                sincosf(0.5f * q, &sh, &ch);
+                sincosf(prismatic ? 0.f : 0.5f * q, &sh, &ch);
                 ql = qmul(jquat, Q4{ch, sh * axis.x, sh * axis.y, sh * axis.z});
                 p = jpos;
             }
             R = qmat(ql);
+            if (prismatic) p = p + q * mulv(R, axis);  // slide along the joint axis (fixed in the parent frame)
         }
         for (int k = 0; k < M.jump_rounds; ++k) {
             const int an = active ? ebase + M.anc[k][li] : lane;
@@ -489,8 +508,7 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
         V6 s = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
         V6 v = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
         if (is_joint) {
-            const V3 aw = mulv(R, axis);
-            s = mk6(aw, cross(p, aw));
+            s = joint_subspace(prismatic, mulv(R, axis), p);
 #pragma unroll
             for (int k = 0; k < 6; ++k) v.a[k] = s.a[k] * qd;
         }
@@ -510,12 +528,7 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
         }
         // velocity-product accelerations c_i and their path sums b_i (b_root = -(0, w0 x v0))
         V6 c = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
-        if (is_joint) {
-            const V3 w = ang(v), vl = lin(v), aw = ang(s);
-            const V3 ca = cross(w, aw);
-            const V3 cl = cross(w, lin(s)) + cross(vl, aw);
-            c = mk6(qd * ca, qd * cl);
-        }
+        if (is_joint) c = velocity_product(v, s, qd);
         V6 b = c;
         for (int k = 0; k < M.jump_rounds; ++k) {
             const int an = active ? ebase + M.anc[k][li] : lane;
@@ -582,7 +595,7 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
 
         // ---- root: solve I^A a = -p^A (6x6 Cholesky, root lane) -------------------------------------
         V6 a = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
-        if (is_root) chol6_solve(IA, pA, a);
+        if (is_root && !fixed_base) chol6_solve(IA, pA, a);  // a welded base does not accelerate
 
         // ---- pass 3: accelerations, top-down -----------------------------------------------------------
         float qdd = 0.f;
@@ -613,7 +626,7 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
             qd = fminf(fmaxf(qd, -M.max_qd), M.max_qd);
             q = fmaf(dt, qd, q);
         }
-        if (is_root) integrate_root(M, a, dt, rpos, rquat, rvel);
+        if (is_root && !fixed_base) integrate_root(M, a, dt, rpos, rquat, rvel);
     }
 
     // ---- non-finite guard: park the env below the termination height so K1 flags it for reset ----
@@ -629,9 +642,11 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
     const unsigned env_lanes = active ? (((L >= 32 ? 0u : (1u << L)) - 1u) << ebase) : 0u;
     if (bad_lanes & env_lanes) {  // any lane of THIS env
         q = 0.f; qd = 0.f;
-        rpos = {0.f, 0.f, -1.f};
-        rquat = {1.f, 0.f, 0.f, 0.f};
-        rvel = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
+        if (!fixed_base) {  // a welded base stays where it is; only the joints are zeroed
+            rpos = {0.f, 0.f, -1.f};
+            rquat = {1.f, 0.f, 0.f, 0.f};
+            rvel = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
+        }
         if (A.sens != nullptr)
             for (int k = li; k < M.num_sensors * 6; k += L) A.sens[env * M.num_sensors * 6 + k] = 0.f;
     }
@@ -737,21 +752,23 @@ articulation_step_tpe_kernel(const DevModel* __restrict__ gmodel, const __grid_c
             const M3 Rp = qmat(qp);
             const V3 axis = {M.axis[0][i], M.axis[1][i], M.axis[2][i]};
             float sh, ch;
-            sincosf(0.5f * qv[i], &sh, &ch);
+            const bool prismatic = M.jtype[i] == OIGE_JOINT_PRISMATIC;
+            sincosf(prismatic ? 0.f : 0.5f * qv[i], &sh, &ch);
             const Q4 ql = qmul(Q4{M.jquat[0][i], M.jquat[1][i], M.jquat[2][i], M.jquat[3][i]},
                                Q4{ch, sh * axis.x, sh * axis.y, sh * axis.z});
             const Q4 qi = qmul(qp, ql);
-            const V3 p = pp + mulv(Rp, V3{M.jpos[0][i], M.jpos[1][i], M.jpos[2][i]});
+            V3 p = pp + mulv(Rp, V3{M.jpos[0][i], M.jpos[1][i], M.jpos[2][i]});
             const M3 R = qmat(qi);
             const V3 aw = mulv(R, axis);
-            const V6 s = mk6(aw, cross(p, aw));
+            if (prismatic) p = p + qv[i] * aw;
+            const V6 s = joint_subspace(prismatic, aw, p);
             const float qd = qdv[i];
             V6 v;
 #pragma unroll
             for (int k = 0; k < 6; ++k) v.a[k] = fmaf(s.a[k], qd, pv.a[k]);
             const V3 w = ang(v), vl = lin(v);
-            const V3 ca = cross(w, aw);
-            const V3 cl = cross(w, lin(s)) + cross(vl, aw);
+            const V3 ca = cross(w, ang(s));
+            const V3 cl = cross(w, lin(s)) + cross(vl, ang(s));
             fk[i][0] = qi.w; fk[i][1] = qi.x; fk[i][2] = qi.y; fk[i][3] = qi.z;
             fk[i][4] = p.x; fk[i][5] = p.y; fk[i][6] = p.z;
 #pragma unroll
@@ -803,16 +820,9 @@ articulation_step_tpe_kernel(const DevModel* __restrict__ gmodel, const __grid_c
                 break;
             }
             const V3 axis = {M.axis[0][i], M.axis[1][i], M.axis[2][i]};
-            const V3 aw = mulv(R, axis);
-            const V6 s = mk6(aw, cross(p, aw));
+            const V6 s = joint_subspace(M.jtype[i] == OIGE_JOINT_PRISMATIC, mulv(R, axis), p);
             const float q = qv[i], qd = qdv[i];
-            V6 c;
-            {
-                const V3 w = ang(v), vl = lin(v);
-                const V3 ca = cross(w, aw);
-                const V3 cl = cross(w, lin(s)) + cross(vl, aw);
-                c = mk6(qd * ca, qd * cl);
-            }
+            const V6 c = velocity_product(v, s, qd);
             float tau0, dextra;
             joint_force(M, i, q, qd, eff[i], dt, A.targets != nullptr, tgt[i], tau0, dextra);
             const V6 U = s6mul(IA, s);
@@ -850,8 +860,8 @@ articulation_step_tpe_kernel(const DevModel* __restrict__ gmodel, const __grid_c
         }
 
         // ---- root: solve I^A a = -p^A (6x6 Cholesky) ----------------------------------------------
-        V6 a0;
-        chol6_solve(carryI, carryP, a0);
+        V6 a0 = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
+        if (!M.fixed_base) chol6_solve(carryI, carryP, a0);  // a welded base does not accelerate
         if (M.light_slot[0] >= 0) {
 #pragma unroll
             for (int k = 0; k < 6; ++k) slotA[M.light_slot[0]][k] = a0.a[k];
@@ -876,8 +886,8 @@ articulation_step_tpe_kernel(const DevModel* __restrict__ gmodel, const __grid_c
             V6 v;
 #pragma unroll
             for (int k = 0; k < 6; ++k) v.a[k] = fk[i][7 + k];
-            const V3 aw = mulv(R, V3{M.axis[0][i], M.axis[1][i], M.axis[2][i]});
-            const V6 s = mk6(aw, cross(p, aw));
+            const V6 s = joint_subspace(M.jtype[i] == OIGE_JOINT_PRISMATIC,
+                                        mulv(R, V3{M.axis[0][i], M.axis[1][i], M.axis[2][i]}), p);
             const float qd0 = qdv[i];
             V6 U;
 #pragma unroll
@@ -885,10 +895,7 @@ articulation_step_tpe_kernel(const DevModel* __restrict__ gmodel, const __grid_c
             const float qdd = (pu[i][7] - dot6(U, ap)) * pu[i][6];
             V6 a;
             {
-                const V3 w = ang(v), vl = lin(v);
-                const V3 ca = cross(w, aw);
-                const V3 cl = cross(w, lin(s)) + cross(vl, aw);
-                const V6 c = mk6(qd0 * ca, qd0 * cl);
+                const V6 c = velocity_product(v, s, qd0);
 #pragma unroll
                 for (int k = 0; k < 6; ++k) a.a[k] = fmaf(s.a[k], qdd, ap.a[k] + c.a[k]);
             }
@@ -910,7 +917,7 @@ articulation_step_tpe_kernel(const DevModel* __restrict__ gmodel, const __grid_c
             qv[i] = fmaf(dt, qd, qv[i]);
             acarry = a;
         }
-        integrate_root(M, a0, dt, rpos, rquat, rvel);
+        if (!M.fixed_base) integrate_root(M, a0, dt, rpos, rquat, rvel);
     }
 
     // ---- non-finite guard + store ---------------------------------------------------------------
@@ -919,10 +926,12 @@ articulation_step_tpe_kernel(const DevModel* __restrict__ gmodel, const __grid_c
 #pragma unroll
     for (int k = 0; k < 6; ++k) bad = bad || !isfinite(rvel.a[k]);
     for (int i = 1; i < L; ++i) bad = bad || !(isfinite(qv[i]) && isfinite(qdv[i]));
-    if (bad) {
+    if (bad && !M.fixed_base) {
         rpos = {0.f, 0.f, -1.f};
         rquat = {1.f, 0.f, 0.f, 0.f};
         rvel = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
+    }
+    if (bad) {
         if (A.sens != nullptr)
             for (int k = 0; k < M.num_sensors * 6; ++k) A.sens[env * M.num_sensors * 6 + k] = 0.f;
     }
@@ -996,6 +1005,7 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
     DevModel* h = new DevModel();
     memset(h, 0, sizeof(DevModel));
     h->num_links = L; h->num_spheres = d->num_spheres; h->num_sensors = d->num_sensors;
+    h->fixed_base = d->fixed_base != 0;
     for (int k = 0; k < kMaxChildren; ++k)
         for (int i = 0; i < 32; ++i) h->child[k][i] = -1;
     int nchild[32] = {0};
@@ -1003,11 +1013,13 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
     for (int i = 0; i < L && ok; ++i) {
         h->parent[i] = d->parent[i];
         h->dof[i] = d->dof_index[i];
+        h->jtype[i] = d->joint_type[i];
         h->sensor_of_link[i] = -1;
         if (i == 0) { h->level[0] = 0; continue; }
         const int p = d->parent[i];
         if (p < 0 || p >= i) { ok = false; break; }
         if (d->dof_index[i] < 0 || d->dof_index[i] >= L - 1) { ok = false; break; }
+        if (d->joint_type[i] != OIGE_JOINT_HINGE && d->joint_type[i] != OIGE_JOINT_PRISMATIC) { ok = false; break; }
         h->level[i] = h->level[p] + 1;
         if (h->level[i] >= kMaxLevels || nchild[p] >= kMaxChildren) { ok = false; break; }
         h->child[nchild[p]++][p] = i;

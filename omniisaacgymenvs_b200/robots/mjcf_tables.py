@@ -173,4 +173,38 @@ ANT = dict(
     gears={"hip": 15.0, "ankle": 15.0},   # tasks/ant.py:80
 )
 
-ROBOTS = {"Humanoid": HUMANOID, "Ant": ANT}
+def cartpole_bodies():
+    """The Cartpole of ``/Isaac/Robots/Cartpole/cartpole.usd`` (robots/articulations/cartpole.py:52), a USD
+    conversion of the public IsaacGymEnvs ``cartpole.urdf``, restated as recalled (PROVENANCE: unpinned;
+    the reference pins only the joint names, tasks/cartpole.py:133-134, and the spawn height 2.0,
+    tasks/cartpole.py:57): an 8 m rail welded to the world, a 1 kg cart sliding along y within +-4 m
+    and a 1 kg, 1 m pole on a continuous hinge about x, its box centred 0.47 m above the hinge."""
+    rail = dict(name="rail", parent=None, pos=(0, 0, 0), quat=(1, 0, 0, 0), joints=[],
+                geoms=[("box", (0, 0, 0), (0.03, 8.0, 0.03))], mass=1.0)
+    cart = dict(
+        name="cart", parent="rail", pos=(0, 0, 0), quat=(1, 0, 0, 0), mass=1.0,
+        joints=[dict(name="cartJoint", type="slide", anchor=(0, 0, 0), axis=(0, 1, 0), range=(-4.0, 4.0),
+                     stiffness=0.0, damping=0.0, armature=0.0)],
+        geoms=[("box", (0, 0, 0), (0.2, 0.25, 0.2))],
+    )
+    pole = dict(
+        name="pole", parent="cart", pos=(0.12, 0, 0), quat=(1, 0, 0, 0), mass=1.0,
+        joints=[dict(name="poleJoint", type="hinge", anchor=(0, 0, 0), axis=(1, 0, 0), range=None,
+                     stiffness=0.0, damping=0.0, armature=0.0)],
+        geoms=[("box", (0, 0, 0.47), (0.04, 0.06, 1.0))],
+    )
+    return [rail, cart, pole]
+
+
+CARTPOLE = dict(
+    name="Cartpole",
+    bodies=cartpole_bodies,
+    density=1000.0,                       # overridden per body by the explicit masses
+    spawn_height=2.0,                     # tasks/cartpole.py:57
+    fixed_base=True,                      # the rail is jointed to the world in the USD
+    sensor_bodies=[],
+    dof_order_in_body={},
+    gears={"cartJoint": 1.0, "poleJoint": 1.0},  # efforts are formed by the task (tasks/cartpole.py:104-105)
+)
+
+ROBOTS = {"Humanoid": HUMANOID, "Ant": ANT, "Cartpole": CARTPOLE}

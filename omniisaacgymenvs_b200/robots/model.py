@@ -32,7 +32,13 @@ def _quat_to_mat(q):
 
 
 def _geom_inertial(geom, density):
-    """(mass, com[3], inertia-about-com 3x3) of a capsule / sphere of uniform density."""
+    """(mass, com[3], inertia-about-com 3x3) of a capsule / sphere / box of uniform density."""
+    if geom[0] == "box":  # ("box", centre, full sizes), axis-aligned in the body frame
+        _, pos, size = geom
+        sx, sy, sz = (float(v) for v in size)
+        m = density * sx * sy * sz
+        return m, np.array(pos, float), np.diag([m * (sy * sy + sz * sz) / 12.0, m * (sx * sx + sz * sz) / 12.0,
+                                                 m * (sx * sx + sy * sy) / 12.0])
     if geom[0] == "sphere":
         _, pos, r = geom
         m = density * 4.0 / 3.0 * math.pi * r ** 3
@@ -60,6 +66,7 @@ class ArticulationModel:
     num_dof: int
     parent: np.ndarray            # [L] int
     dof_index: np.ndarray         # [L] int (-1 root)
+    joint_type: np.ndarray        # [L] int: 0 hinge, 1 prismatic
     joint_pos: np.ndarray         # [L,3]
     joint_quat: np.ndarray        # [L,4] wxyz
     joint_axis: np.ndarray        # [L,3]
@@ -94,6 +101,7 @@ class ArticulationModel:
     limit_damping: float = 2.0e1
     max_joint_velocity: float = 100.0
     angular_damping: float = 0.0
+    fixed_base: bool = False      # link 0 welded to the world
 
     @property
     def num_sensors(self) -> int:
@@ -137,7 +145,7 @@ def build_model(name: str, **overrides) -> ArticulationModel:
             dof_names.append(jn)
             dof_body_names.append(b["name"])
 
-    parent, dof_index, jpos, jquat, jaxis = [-1], [-1], [(0, 0, 0)], [(1, 0, 0, 0)], [(0, 0, 1)]
+    parent, dof_index, jpos, jquat, jaxis, jtype = [-1], [-1], [(0, 0, 0)], [(1, 0, 0, 0)], [(0, 0, 1)], [0]
     arm, damp, stiff, lo, hi, link_names = [0.0], [0.0], [0.0], [0.0], [0.0], [bodies[0]["name"]]
     last_link: Dict[str, int] = {bodies[0]["name"]: 0}
     last_anchor: Dict[str, np.ndarray] = {bodies[0]["name"]: np.zeros(3)}
@@ -166,7 +174,15 @@ def build_model(name: str, **overrides) -> ArticulationModel:
             jquat.append(jq)
             jaxis.append(tuple(ax))
             arm.append(j["armature"]); damp.append(j["damping"]); stiff.append(j["stiffness"])
-            lo.append(math.radians(j["range"][0])); hi.append(math.radians(j["range"][1]))
+            slide = j.get("type", "hinge") == "slide"
+            jtype.append(1 if slide else 0)
+            # hinge ranges are in degrees, slide ranges in metres; None = unlimited (URDF "continuous")
+            if j["range"] is None:
+                lo.append(-1.0e30); hi.append(1.0e30)
+            elif slide:
+                lo.append(float(j["range"][0])); hi.append(float(j["range"][1]))
+            else:
+                lo.append(math.radians(j["range"][0])); hi.append(math.radians(j["range"][1]))
             link_names.append(j["name"])
             prev_anchor = anchor
         last_link[b["name"]] = len(parent) - 1
@@ -179,6 +195,9 @@ def build_model(name: str, **overrides) -> ArticulationModel:
         link = last_link[b["name"]]
         off = last_anchor[b["name"]]
         parts = [_geom_inertial(g, table["density"]) for g in b["geoms"]]
+        if b.get("mass") is not None:  # URDF-style explicit body mass: rescale the uniform-density parts
+            k = float(b["mass"]) / sum(p[0] for p in parts)
+            parts = [(p[0] * k, p[1], p[2] * k) for p in parts]
         m = sum(p[0] for p in parts)
         c = sum(p[0] * p[1] for p in parts) / m
         I = np.zeros((3, 3))
@@ -189,6 +208,8 @@ def build_model(name: str, **overrides) -> ArticulationModel:
         com[link] = c - off
         inertia[link] = [I[0, 0], I[1, 1], I[2, 2], I[0, 1], I[0, 2], I[1, 2]]
         for g in b["geoms"]:
+            if g[0] == "box":
+                continue  # boxes carry mass only (the Cartpole never touches the ground)
             if g[0] == "sphere":
                 sph_link.append(link); sph_pos.append(np.array(g[1], float) - off); sph_r.append(g[2])
             else:
@@ -200,12 +221,13 @@ def build_model(name: str, **overrides) -> ArticulationModel:
     model = ArticulationModel(
         name=name, num_links=L, num_dof=L - 1,
         parent=np.array(parent, np.int32), dof_index=np.array(dof_index, np.int32),
+        joint_type=np.array(jtype, np.int32), fixed_base=bool(table.get("fixed_base", False)),
         joint_pos=np.array(jpos, np.float64), joint_quat=np.array(jquat, np.float64),
         joint_axis=np.array(jaxis, np.float64), mass=mass, com=com, inertia=inertia,
         armature=np.array(arm), damping=np.array(damp), stiffness=np.array(stiff), spring_ref=np.zeros(L),
         limit_lower=np.array(lo), limit_upper=np.array(hi),
         drive_stiffness=np.zeros(L), drive_damping=np.zeros(L), drive_max_force=np.zeros(L),
-        sphere_link=np.array(sph_link, np.int32), sphere_pos=np.array(sph_pos, np.float64),
+        sphere_link=np.array(sph_link, np.int32), sphere_pos=np.array(sph_pos, np.float64).reshape(-1, 3),
         sphere_radius=np.array(sph_r, np.float64),
         sensor_link=np.array([last_link[s] for s in table["sensor_bodies"]], np.int32),
         dof_names=dof_names, dof_body_names=dof_body_names, joint_gears=gears,
@@ -222,9 +244,11 @@ def fill_desc(model: ArticulationModel, desc) -> None:
     """Fills a ctypes ``OigeModelDesc`` (or the oracle's identical struct) from the model."""
     L, K, S = model.num_links, len(model.sphere_link), model.num_sensors
     desc.num_links, desc.num_spheres, desc.num_sensors = L, K, S
+    desc.fixed_base = 1 if model.fixed_base else 0
     for i in range(L):
         desc.parent[i] = int(model.parent[i])
         desc.dof_index[i] = int(model.dof_index[i])
+        desc.joint_type[i] = int(model.joint_type[i])
         for k in range(3):
             desc.joint_pos[i][k] = float(model.joint_pos[i, k])
             desc.joint_axis[i][k] = float(model.joint_axis[i, k])

@@ -81,8 +81,12 @@ static void point_jacobian(const OigeModelDesc* M, int link, v3 point, const v3*
         J->jv[3 + k] = crs(e, sub(point, p[0]));
     }
     for (int j = link; j > 0; j = M->parent[j]) {
-        J->jw[6 + j - 1] = axw[j];
-        J->jv[6 + j - 1] = crs(axw[j], sub(point, p[j]));
+        if (M->joint_type[j] == OIGE_JOINT_PRISMATIC) { /* pure translation of everything downstream */
+            J->jv[6 + j - 1] = axw[j];
+        } else {
+            J->jw[6 + j - 1] = axw[j];
+            J->jv[6 + j - 1] = crs(axw[j], sub(point, p[j]));
+        }
     }
 }
 
@@ -156,6 +160,20 @@ static int step_one(const OigeModelDesc* M, double* pos, double* quat, double* v
         v3 ax = V(M->joint_axis[i][0], M->joint_axis[i][1], M->joint_axis[i][2]);
         double jq[4] = {M->joint_quat[i][0], M->joint_quat[i][1], M->joint_quat[i][2], M->joint_quat[i][3]};
         v3 r = mv(R[pa], V(M->joint_pos[i][0], M->joint_pos[i][1], M->joint_pos[i][2]));
+        if (M->joint_type[i] == OIGE_JOINT_PRISMATIC) {
+            /* the link slides along the axis (fixed in the parent): origin offset r + axw q, relative
+             * velocity axw qd, hence the Coriolis term 2 w x (axw qd) in the origin's acceleration */
+            R[i] = mmul(R[pa], quat_mat(jq));
+            axw[i] = mv(R[i], ax);
+            r = add(r, scl(q[d], axw[i]));
+            p[i] = add(p[pa], r);
+            w[i] = w[pa];
+            vo[i] = add(vo[pa], add(crs(w[pa], r), scl(qd[d], axw[i])));
+            al0[i] = al0[pa];
+            ac0[i] = add(ac0[pa], add(add(crs(al0[pa], r), crs(w[pa], crs(w[pa], r))),
+                                      scl(2.0 * qd[d], crs(w[pa], axw[i]))));
+            continue;
+        }
         p[i] = add(p[pa], r);
         R[i] = mmul(mmul(R[pa], quat_mat(jq)), axis_angle(ax, q[d]));
         axw[i] = mv(R[i], ax);
@@ -221,7 +239,14 @@ static int step_one(const OigeModelDesc* M, double* pos, double* quat, double* v
                                      cons[s].C.z * J.jv[a].z * J.jv[b].z;
         }
     }
-    /* 5. solve */
+    /* 5. solve (a welded base: its six rows/columns become the identity with zero right-hand side) */
+    if (M->fixed_base) {
+        for (int a = 0; a < 6; ++a) {
+            for (int b = 0; b <= a; ++b) A[a * NV_MAX + b] = (a == b) ? 1.0 : 0.0;
+            for (int c = 6; c < nv; ++c) A[c * NV_MAX + a] = 0.0;
+            rhs[a] = 0.0;
+        }
+    }
     if (cholesky_solve(A, rhs, nv, NV_MAX) != 0) return -1;
     const double* x = rhs;
     /* 6. sensors: net ground wrench on each sensor link, in the link frame, torque about the link origin */
@@ -252,6 +277,7 @@ static int step_one(const OigeModelDesc* M, double* pos, double* quat, double* v
         qd[d] = v;
         q[d] += dt * v;
     }
+    if (M->fixed_base) return 0;
     double damp = 1.0 - dt * (double)M->angular_damping;
     if (damp < 0) damp = 0;
     v3 w1 = scl(damp, add(w[0], scl(dt, V(x[3], x[4], x[5]))));
@@ -306,10 +332,19 @@ double oracle_energy_f64(const OigeModelDesc* M, const double* pos, const double
             v3 ax = V(M->joint_axis[i][0], M->joint_axis[i][1], M->joint_axis[i][2]);
             double jq[4] = {M->joint_quat[i][0], M->joint_quat[i][1], M->joint_quat[i][2], M->joint_quat[i][3]};
             v3 r = mv(R[pa], V(M->joint_pos[i][0], M->joint_pos[i][1], M->joint_pos[i][2]));
-            p[i] = add(p[pa], r);
-            R[i] = mmul(mmul(R[pa], quat_mat(jq)), axis_angle(ax, q[d]));
-            w[i] = add(w[pa], scl(qd[d], mv(R[i], ax)));
-            vo[i] = add(vo[pa], crs(w[pa], r));
+            if (M->joint_type[i] == OIGE_JOINT_PRISMATIC) {
+                R[i] = mmul(R[pa], quat_mat(jq));
+                v3 a = mv(R[i], ax);
+                r = add(r, scl(q[d], a));
+                p[i] = add(p[pa], r);
+                w[i] = w[pa];
+                vo[i] = add(vo[pa], add(crs(w[pa], r), scl(qd[d], a)));
+            } else {
+                p[i] = add(p[pa], r);
+                R[i] = mmul(mmul(R[pa], quat_mat(jq)), axis_angle(ax, q[d]));
+                w[i] = add(w[pa], scl(qd[d], mv(R[i], ax)));
+                vo[i] = add(vo[pa], crs(w[pa], r));
+            }
             E += 0.5 * (double)M->armature[i] * qd[d] * qd[d];
             double dq = q[d] - (double)M->spring_ref[i];
             E += 0.5 * (double)M->stiffness[i] * dq * dq;

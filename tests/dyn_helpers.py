@@ -85,3 +85,29 @@ def run_oracle(model, spec, st, substeps, dt, calls=1, threads=8):
 
 def specs(robot):
     return build_model(robot), lo.SPECS[robot]
+
+
+def link_coms(model, s):
+    """Mass-weighted centre of mass of env 0 (float64 numpy forward kinematics, hinge + prismatic)."""
+    def qmat(q):
+        w, x, y, z = q
+        return np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y)],
+                         [2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x)],
+                         [2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)]])
+
+    L = model.num_links
+    R, p = [None] * L, [None] * L
+    R[0], p[0] = qmat(s["quat"][0]), np.array(s["pos"][0], float)
+    for i in range(1, L):
+        pa, d = int(model.parent[i]), int(model.dof_index[i])
+        ax = model.joint_axis[i]
+        Rj = R[pa] @ qmat(model.joint_quat[i])
+        if model.joint_type[i] == 1:
+            R[i] = Rj
+            p[i] = p[pa] + R[pa] @ model.joint_pos[i] + (Rj @ ax) * s["q"][0, d]
+        else:
+            th = s["q"][0, d]
+            R[i] = Rj @ qmat(np.concatenate([[np.cos(th / 2)], np.sin(th / 2) * ax]))
+            p[i] = p[pa] + R[pa] @ model.joint_pos[i]
+    tot = sum(model.mass)
+    return sum(model.mass[i] * (p[i] + R[i] @ model.com[i]) for i in range(L)) / tot

@@ -75,3 +75,82 @@ def test_openmp_threads_do_not_change_results():
     dyn.step(desc, b["pos"], b["quat"], b["vel"], b["q"], b["qd"], eff, None, 8, 0.0083, num_threads=4)
     for k in a:
         assert np.array_equal(a[k], b[k])
+
+
+# ---- prismatic joints and a welded base (Cartpole) ---------------------------------
+def _cartpole_accel(m, x, th, xd, thd, force):
+    """Textbook cart-pole equations (Lagrange), cart along +y, pole hinge about +x, theta = 0 upright."""
+    M, mp = m.mass[1], m.mass[2]
+    l = m.com[2, 2]
+    I = m.inertia[2, 0]  # about the hinge axis (x), at the centre of mass
+    g = float(np.float32(9.81))
+    # (M+m) xdd - m l cos(th) thdd + m l sin(th) thd^2 = F ;  (I + m l^2) thdd - m l cos(th) xdd - m g l sin(th) = 0
+    A = np.array([[M + mp, -mp * l * np.cos(th)], [-mp * l * np.cos(th), I + mp * l * l]])
+    b = np.array([force - mp * l * np.sin(th) * thd * thd, mp * g * l * np.sin(th)])
+    return np.linalg.solve(A, b)
+
+
+def test_cartpole_accelerations_match_the_textbook_equations():
+    m = build_model("Cartpole")
+    assert m.fixed_base and list(m.joint_type) == [0, 1, 0] and m.dof_names == ["cartJoint", "poleJoint"]
+    desc = dyn.make_desc(m)
+    rng = np.random.default_rng(3)
+    dt = 1e-3
+    for _ in range(20):
+        x, th = rng.uniform(-2, 2), rng.uniform(-3, 3)
+        xd, thd = rng.normal(), 2 * rng.normal()
+        f = rng.uniform(-400, 400)
+        s = dict(pos=np.array([[1.0, -2.0, 2.0]]), quat=np.array([[1.0, 0, 0, 0]]), vel=np.zeros((1, 6)),
+                 q=np.array([[x, th]]), qd=np.array([[xd, thd]]))
+        assert dyn.step(desc, s["pos"], s["quat"], s["vel"], s["q"], s["qd"], np.array([[f, 0.0]]), None, 1, dt) == 0
+        acc = (s["qd"][0] - np.array([xd, thd])) / dt
+        np.testing.assert_allclose(acc, _cartpole_accel(m, x, th, xd, thd, f), rtol=1e-9, atol=1e-9)
+        # the welded rail did not move
+        assert np.array_equal(s["pos"], [[1.0, -2.0, 2.0]]) and np.array_equal(s["vel"], np.zeros((1, 6)))
+
+
+def test_cartpole_energy_is_conserved_without_actuation():
+    m = build_model("Cartpole")
+    desc = dyn.make_desc(m)
+    base = dict(pos=np.array([[0, 0, 2.0]]), quat=np.array([[1.0, 0, 0, 0]]), vel=np.zeros((1, 6)),
+                q=np.array([[0.3, 0.4]]), qd=np.array([[-0.5, 1.0]]))
+    e0 = dyn.energy(desc, *[base[k] for k in ("pos", "quat", "vel", "q", "qd")])
+    drift = []
+    for dt in (1e-3, 1e-4):
+        s = {k: v.copy() for k, v in base.items()}
+        assert dyn.step(desc, s["pos"], s["quat"], s["vel"], s["q"], s["qd"], np.zeros((1, 2)), None,
+                        int(round(1.0 / dt)), dt) == 0
+        drift.append(abs(dyn.energy(desc, *[s[k] for k in ("pos", "quat", "vel", "q", "qd")]) - e0) / abs(e0))
+    assert drift[0] < 5e-3 and drift[1] < drift[0] / 5
+
+
+def test_prismatic_joint_on_a_floating_base_conserves_momentum():
+    """A tumbling, free-floating cart-pole (no gravity): linear momentum is exactly conserved by the
+    integrator, and the energy drift shrinks with dt -- exercises the Coriolis terms of the slider."""
+    m = build_model("Cartpole", fixed_base=False, gravity=(0.0, 0.0, 0.0))
+    desc = dyn.make_desc(m)
+    rng = np.random.default_rng(5)
+    base = dict(pos=np.array([[0, 0, 50.0]]), quat=np.array([[1.0, 0, 0, 0]]), vel=rng.normal(size=(1, 6)),
+                q=np.array([[0.5, 0.7]]), qd=np.array([[1.5, -2.0]]))
+
+    def momentum(s):
+        # finite-difference the centre of mass: total mass x com velocity, from two energy-free evaluations
+        from dyn_helpers import link_coms
+        return link_coms(m, s)
+
+    e0 = dyn.energy(desc, *[base[k] for k in ("pos", "quat", "vel", "q", "qd")])
+    drift = []
+    for dt in (1e-3, 1e-4):
+        s = {k: v.copy() for k, v in base.items()}
+        c0 = momentum(s)
+        n = int(round(0.5 / dt))
+        assert dyn.step(desc, s["pos"], s["quat"], s["vel"], s["q"], s["qd"], np.zeros((1, 2)), None, 1, dt) == 0
+        c1 = momentum(s)
+        assert dyn.step(desc, s["pos"], s["quat"], s["vel"], s["q"], s["qd"], np.zeros((1, 2)), None, n, dt) == 0
+        c2 = momentum(s)
+        assert dyn.step(desc, s["pos"], s["quat"], s["vel"], s["q"], s["qd"], np.zeros((1, 2)), None, 1, dt) == 0
+        c3 = momentum(s)
+        v_start, v_end = (c1 - c0) / dt, (c3 - c2) / dt
+        np.testing.assert_allclose(v_end, v_start, atol=5e-3 * max(1.0, np.abs(v_start).max()) * (dt / 1e-3))
+        drift.append(abs(dyn.energy(desc, *[s[k] for k in ("pos", "quat", "vel", "q", "qd")]) - e0) / abs(e0))
+    assert drift[1] < drift[0] / 5

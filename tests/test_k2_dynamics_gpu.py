@@ -221,3 +221,88 @@ def test_model_create_rejects_malformed_trees(cuda_lib):
     fill_desc(model, desc)
     desc.num_links = 40
     assert not cuda_lib.oige_model_create(C.byref(desc))
+
+
+# ---- prismatic joint + welded base: the Cartpole tree ---------------------------------
+class _UnitSpec:
+    power_scale = 1.0
+
+
+def _cartpole_state(n, seed, floating=False):
+    rng = np.random.default_rng(seed)
+    f32 = lambda a: np.ascontiguousarray(np.asarray(a, np.float64).astype(np.float32))
+    pos = np.zeros((n, 3))
+    pos[:, :2] = rng.normal(size=(n, 2)) * 3.0
+    pos[:, 2] = 50.0 if floating else 2.0
+    quat = np.zeros((n, 4))
+    quat[:, 0] = 1.0
+    vel = np.zeros((n, 6))
+    if floating:
+        axis = rng.normal(size=(n, 3))
+        axis /= np.linalg.norm(axis, axis=1, keepdims=True)
+        ang = 0.5 * rng.normal(size=(n, 1))
+        quat = np.concatenate([np.cos(ang / 2), np.sin(ang / 2) * axis], axis=1)
+        vel = 0.5 * rng.normal(size=(n, 6))
+    q = np.stack([rng.uniform(-2.5, 2.5, n), rng.uniform(-3.0, 3.0, n)], axis=1)
+    qd = np.stack([rng.normal(size=n), 2.0 * rng.normal(size=n)], axis=1)
+    act = np.stack([rng.uniform(-400, 400, n), np.zeros(n)], axis=1)  # efforts: tasks/cartpole.py:104-105
+    return {"pos": f32(pos), "quat": f32(quat), "vel": f32(vel), "q": f32(q), "qd": f32(qd), "actions": f32(act)}
+
+
+@pytest.mark.parametrize("floating", [False, True])
+def test_cartpole_single_substep(cuda_lib, floating):
+    from omniisaacgymenvs_b200.robots.model import build_model
+
+    model = build_model("Cartpole", fixed_base=not floating)
+    st = _cartpole_state(500, 40, floating)
+    g = dh.run_gpu(cuda_lib, model, _UnitSpec, st, 1, DT)
+    o = dh.run_oracle(model, _UnitSpec, st, 1, DT)
+    assert _err(g["q"], o["q"]) < 2e-5
+    assert (np.abs(g["qd"] - o["qd"]) / np.maximum(1.0, np.abs(o["qd"]))).max() < 1e-4
+    assert _err(g["pos"], o["pos"]) < 2e-5 and _quat_err(g["quat"], o["quat"]) < 2e-5
+    assert (np.abs(g["vel"] - o["vel"]) / np.maximum(1.0, np.abs(o["vel"]))).max() < 2e-3
+    if not floating:  # the welded rail is untouched, bit for bit
+        assert np.array_equal(g["pos"], st["pos"].astype(np.float64)) and np.abs(g["vel"]).max() == 0.0
+
+
+@pytest.mark.parametrize("floating", [False, True])
+def test_cartpole_rollout_120_substeps(cuda_lib, floating):
+    from omniisaacgymenvs_b200.robots.model import build_model
+
+    model = build_model("Cartpole", fixed_base=not floating)
+    st = _cartpole_state(500, 41, floating)
+    st["actions"][:] *= 0.02  # keep the cart inside the rail limits for a second of simulated time
+    g = dh.run_gpu(cuda_lib, model, _UnitSpec, st, 2, DT, calls=60)
+    o = dh.run_oracle(model, _UnitSpec, st, 2, DT, calls=60)
+    assert np.abs(o["q"][:, 1] - st["q"][:, 1]).max() > 1.0, "the poles must actually swing"
+    per_env = np.abs(g["q"] - o["q"]).max(axis=1)
+    assert np.median(per_env) < 2e-4 and (per_env < 1e-2).mean() >= 0.99  # near-upright poles amplify rounding
+    assert _err(g["pos"], o["pos"]) < 5e-3
+
+
+def test_cartpole_rail_limits_hold_the_cart(cuda_lib):
+    """A cart pushed hard against the +-4 m rail limit is stopped by the (implicit) limit spring, as in the oracle."""
+    from omniisaacgymenvs_b200.robots.model import build_model
+
+    model = build_model("Cartpole")
+    st = _cartpole_state(64, 42)
+    st["q"][:, 0] = 3.9
+    st["qd"][:, 0] = 3.0
+    st["actions"][:, 0] = 50.0
+    g = dh.run_gpu(cuda_lib, model, _UnitSpec, st, 2, DT, calls=30)
+    o = dh.run_oracle(model, _UnitSpec, st, 2, DT, calls=30)
+    assert o["q"][:, 0].max() < 4.3 and g["q"][:, 0].max() < 4.3
+    assert (np.abs(g["q"] - o["q"]).max(axis=1) < 2e-2).mean() >= 0.95
+
+
+def test_model_create_rejects_unknown_joint_type(cuda_lib):
+    import ctypes as C
+
+    from omniisaacgymenvs_b200 import _lib
+    from omniisaacgymenvs_b200.robots.model import build_model, fill_desc
+
+    desc = _lib.OigeModelDesc()
+    fill_desc(build_model("Cartpole"), desc)
+    desc.joint_type[1] = 7
+    assert not cuda_lib.oige_model_create(C.byref(desc))
+    assert b"malformed" in cuda_lib.oige_last_error()
