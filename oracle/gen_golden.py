@@ -128,6 +128,10 @@ def main() -> None:
         ep = ref_task_driver.run_episode(robot, n, steps=5, seed=0, dof_limits=torch.from_numpy(model.dof_limits()),
                                          spawn_pos=spawn)
         np.savez_compressed(os.path.join(GOLDEN_DIR, f"episode_{robot.lower()}.npz"), **ep)
+    # Cartpole: the verbatim CartpoleTask methods on a fake view (tasks/cartpole.py:80-162)
+    from oracle import ref_cartpole_driver
+
+    np.savez_compressed(os.path.join(GOLDEN_DIR, "episode_cartpole.npz"), **ref_cartpole_driver.run_episode(96, steps=6, seed=0))
     print("wrote", len(os.listdir(GOLDEN_DIR)), "fixtures to", GOLDEN_DIR)
 
 
