@@ -235,6 +235,56 @@ int oige_env_step_host_f32(const OigeModel* model, const OigeTaskParams* params,
                            float clip_actions, uint64_t seed, uint64_t counter, int64_t env_id_offset,
                            int64_t n_envs, int32_t substeps, float dt, void* stream);
 
+/* ================= Cartpole (tasks/cartpole.py) =================
+ * Same three-kernel step as the locomotion tasks with the task-specific passes swapped:
+ *   reset + efforts (pre_physics_step, cartpole.py:101-130)  ->  K2 on the 3-link welded-base tree
+ *   ->  observations + reward + done (cartpole.py:80-99,143-162; rl_task.py:242).
+ * dof_pos / dof_vel / efforts are [N,2] in DoF order (cartJoint, poleJoint by default). */
+typedef struct OigeCartpoleParams {
+    int32_t cart_dof;           /* get_dof_index("cartJoint") (cartpole.py:133) */
+    int32_t pole_dof;           /* get_dof_index("poleJoint") (cartpole.py:134) */
+    int32_t progress_increment; /* 1: fuse `progress_buf += 1` (rl_task.py:242) into the pass; 0: leave it */
+    int32_t reserved_i;
+    float reset_dist;           /* cfg resetDist, 3.0 (cartpole.py:59) */
+    float max_push_effort;      /* cfg maxEffort, 400 (cartpole.py:60) */
+    float max_episode_length;   /* 500 (cartpole.py:61); done when progress >= it (cartpole.py:161) */
+    float clip_obs;             /* 5.0 (Cartpole.yaml:13); the STORED observations are clamped, reward and
+                                   done are evaluated on the unclamped values like the reference */
+} OigeCartpoleParams;
+
+typedef struct OigeCartpoleBuffers {
+    float* obs;              /* [N,4] cart_pos, cart_vel, pole_pos, pole_vel (cartpole.py:89-92) */
+    float* rew;              /* [N] */
+    int64_t* reset_buf;      /* [N] */
+    int64_t* progress_buf;   /* [N] */
+    float* efforts;          /* [N,2] what set_joint_efforts receives (cartpole.py:104-108) */
+    double* episode_stats;   /* [OIGE_STATS_SLOTS,4] or NULL, as in OigeTaskBuffers */
+    uint64_t* reset_counter; /* NULL or device scalar, as in OigeTaskBuffers */
+} OigeCartpoleBuffers;
+
+/* get_observations + calculate_metrics + is_done (+ progress += 1) in one pass (cartpole.py:80-99,143-162).
+ * Only state->dof_pos / dof_vel are read. */
+int oige_cartpole_obs_reward_reset_f32(const OigeCartpoleParams* params, const OigeState* state,
+                                       const OigeCartpoleBuffers* buf, int64_t n_envs, void* stream);
+/* pre_physics_step (cartpole.py:101-108): resets every env whose reset_buf != 0 on the device (no nonzero()
+ * host sync) and, if actions_in ([N,1]) is not NULL, writes efforts = maxEffort * clamp(actions, +-clip_actions)
+ * on the cart DoF and 0 on the pole.  rand: raw U[0,1) draws [N,4] in the reference's draw order (cart position,
+ * pole angle, cart velocity, pole velocity; cartpole.py:115-121) or NULL for Philox keyed by
+ * (seed, env_id_offset + env, counter). */
+int oige_cartpole_reset_masked_f32(const OigeCartpoleParams* params, const OigeState* state,
+                                   const OigeCartpoleBuffers* buf, const float* actions_in, float clip_actions,
+                                   const float* rand, uint64_t seed, uint64_t counter, int64_t env_id_offset,
+                                   int64_t n_envs, void* stream);
+/* reset_idx(env_ids) (cartpole.py:110-130), the reference's calling form; rand is [k,4] or NULL. */
+int oige_cartpole_reset_idx_f32(const OigeCartpoleParams* params, const OigeState* state,
+                                const OigeCartpoleBuffers* buf, const int64_t* env_ids, int64_t k, const float* rand,
+                                uint64_t seed, uint64_t counter, int64_t env_id_offset, void* stream);
+/* Whole VecEnvRLGames.step (envs/vec_env_rlgames.py:56-78) for Cartpole on device buffers: three launches. */
+int oige_cartpole_env_step_f32(const OigeModel* model, const OigeCartpoleParams* params, const OigeState* state,
+                               const OigeCartpoleBuffers* buf, const float* actions_in, float clip_actions,
+                               uint64_t seed, uint64_t counter, int64_t env_id_offset, int64_t n_envs,
+                               int32_t substeps, float dt, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -74,6 +74,16 @@ class OigeModelDesc(C.Structure):
     ]
 
 
+class OigeCartpoleParams(C.Structure):
+    _fields_ = [("cart_dof", i32), ("pole_dof", i32), ("progress_increment", i32), ("reserved_i", i32),
+                ("reset_dist", f32), ("max_push_effort", f32), ("max_episode_length", f32), ("clip_obs", f32)]
+
+
+class OigeCartpoleBuffers(C.Structure):
+    _fields_ = [("obs", vp), ("rew", vp), ("reset_buf", vp), ("progress_buf", vp), ("efforts", vp),
+                ("episode_stats", vp), ("reset_counter", vp)]
+
+
 # every symbol include/oige_b200.h declares (tests/test_capi_symbols.py checks the .so exports them)
 EXPORTED_SYMBOLS = [
     "oige_abi_version", "oige_last_error", "oige_kernel_launch_count",
@@ -81,6 +91,8 @@ EXPORTED_SYMBOLS = [
     "oige_reset_masked_f32", "oige_reset_idx_f32",
     "oige_model_create", "oige_model_destroy", "oige_articulation_step_f32",
     "oige_env_step_f32", "oige_env_step_host_f32",
+    "oige_cartpole_obs_reward_reset_f32", "oige_cartpole_reset_masked_f32", "oige_cartpole_reset_idx_f32",
+    "oige_cartpole_env_step_f32",
 ]
 
 _lib: Optional[C.CDLL] = None
@@ -117,8 +129,15 @@ def load() -> C.CDLL:
     lib.oige_env_step_host_f32.argtypes = [vp, P(OigeTaskParams), P(OigeState), P(OigeTaskBuffers),
                                            P(OigeResetInit), vp, vp, vp, vp, vp, f32, u64, u64, i64, i64, i32,
                                            f32, vp]
+    CP, CB = P(OigeCartpoleParams), P(OigeCartpoleBuffers)
+    lib.oige_cartpole_obs_reward_reset_f32.argtypes = [CP, P(OigeState), CB, i64, vp]
+    lib.oige_cartpole_reset_masked_f32.argtypes = [CP, P(OigeState), CB, vp, f32, vp, u64, u64, i64, i64, vp]
+    lib.oige_cartpole_reset_idx_f32.argtypes = [CP, P(OigeState), CB, vp, i64, vp, u64, u64, i64, vp]
+    lib.oige_cartpole_env_step_f32.argtypes = [vp, CP, P(OigeState), CB, vp, f32, u64, u64, i64, i64, i32, f32, vp]
     for name in ("oige_obs_reward_reset_f32", "oige_obs_reward_reset_tile_f32", "oige_reset_masked_f32",
-                 "oige_reset_idx_f32", "oige_articulation_step_f32", "oige_env_step_f32", "oige_env_step_host_f32"):
+                 "oige_reset_idx_f32", "oige_articulation_step_f32", "oige_env_step_f32", "oige_env_step_host_f32",
+                 "oige_cartpole_obs_reward_reset_f32", "oige_cartpole_reset_masked_f32",
+                 "oige_cartpole_reset_idx_f32", "oige_cartpole_env_step_f32"):
         getattr(lib, name).restype = C.c_int
     if lib.oige_abi_version() != 1:
         raise RuntimeError(f"liboige_b200.so ABI version {lib.oige_abi_version()} != 1: rebuild the library")

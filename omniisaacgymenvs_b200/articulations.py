@@ -124,6 +124,10 @@ class ArticulationView:
             return x[indices]
         return x.clone() if clone else x
 
+    def get_dof_index(self, dof_name: str) -> int:
+        """Column of a named joint in the [N,D] tensors (tasks/cartpole.py:133-134)."""
+        return self.model.dof_names.index(dof_name)
+
     def get_dof_limits(self) -> torch.Tensor:
         return self._dof_limits.unsqueeze(0).expand(self.count, -1, -1)
 

@@ -26,6 +26,7 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-I", INCLUDE
 SOURCES = [
     ("obs_reward_reset.cu", ["-fmad=false"]),
     ("reset_idx.cu", ["-fmad=false"]),
+    ("cartpole.cu", ["-fmad=false"]),
     ("articulation_step.cu", []),
     ("capi.cu", []),
 ]

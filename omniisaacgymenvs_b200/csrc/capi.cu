@@ -57,6 +57,11 @@ int k3_idx(const OigeTaskParams*, const OigeState*, const OigeTaskBuffers*, cons
 int k2_step(const OigeModel*, const OigeTaskParams*, const OigeState*, const float*, int64_t, int32_t, float,
             cudaStream_t, int64_t decision_n);
 OigeModel* k2_model_create(const OigeModelDesc*);
+int cartpole_post(const OigeCartpoleParams*, const OigeState*, const OigeCartpoleBuffers*, int64_t, cudaStream_t, bool);
+int cartpole_pre(const OigeCartpoleParams*, const OigeState*, const OigeCartpoleBuffers*, const float*, float,
+                 const float*, uint64_t, uint64_t, int64_t, int64_t, cudaStream_t, bool);
+int cartpole_reset_idx(const OigeCartpoleParams*, const OigeState*, const OigeCartpoleBuffers*, const int64_t*, int64_t,
+                       const float*, uint64_t, uint64_t, int64_t, cudaStream_t);
 void k2_model_destroy(OigeModel*);
 
 static int check_common(const char* who, const OigeTaskParams* p, const OigeState* s, const OigeTaskBuffers* b,
@@ -238,5 +243,61 @@ int oige_env_step_host_f32(const OigeModel* model, const OigeTaskParams* params,
     }
     return OIGE_OK;
 }
+
+// ---- Cartpole (tasks/cartpole.py) ------------------------------------------------------------------------
+static int cartpole_range(const char* who, int64_t n) {
+    if (n < 0 || n > (int64_t)1 << 31) return fail(OIGE_E_RANGE, "%s: n_envs %lld out of range", who, (long long)n);
+    return OIGE_OK;
+}
+
+int oige_cartpole_obs_reward_reset_f32(const OigeCartpoleParams* params, const OigeState* state,
+                                       const OigeCartpoleBuffers* buf, int64_t n_envs, void* stream) {
+    if (int rc = cartpole_range("oige_cartpole_obs_reward_reset_f32", n_envs)) return rc;
+    if (n_envs == 0) return (params && state && buf) ? OIGE_OK : fail(OIGE_E_NULL, "oige_cartpole_obs_reward_reset_f32: null struct pointer");
+    return cartpole_post(params, state, buf, n_envs, (cudaStream_t)stream, false);
+}
+
+int oige_cartpole_reset_masked_f32(const OigeCartpoleParams* params, const OigeState* state,
+                                   const OigeCartpoleBuffers* buf, const float* actions_in, float clip_actions,
+                                   const float* rand, uint64_t seed, uint64_t counter, int64_t env_id_offset,
+                                   int64_t n_envs, void* stream) {
+    if (int rc = cartpole_range("oige_cartpole_reset_masked_f32", n_envs)) return rc;
+    if (n_envs == 0) return (params && state && buf) ? OIGE_OK : fail(OIGE_E_NULL, "oige_cartpole_reset_masked_f32: null struct pointer");
+    return cartpole_pre(params, state, buf, actions_in, clip_actions, rand, seed, counter, env_id_offset, n_envs,
+                        (cudaStream_t)stream, false);
+}
+
+int oige_cartpole_reset_idx_f32(const OigeCartpoleParams* params, const OigeState* state,
+                                const OigeCartpoleBuffers* buf, const int64_t* env_ids, int64_t k, const float* rand,
+                                uint64_t seed, uint64_t counter, int64_t env_id_offset, void* stream) {
+    if (int rc = cartpole_range("oige_cartpole_reset_idx_f32", k)) return rc;
+    if (k == 0) return (params && state && buf) ? OIGE_OK : fail(OIGE_E_NULL, "oige_cartpole_reset_idx_f32: null struct pointer");
+    return cartpole_reset_idx(params, state, buf, env_ids, k, rand, seed, counter, env_id_offset, (cudaStream_t)stream);
+}
+
+int oige_cartpole_env_step_f32(const OigeModel* model, const OigeCartpoleParams* params, const OigeState* state,
+                               const OigeCartpoleBuffers* buf, const float* actions_in, float clip_actions,
+                               uint64_t seed, uint64_t counter, int64_t env_id_offset, int64_t n_envs,
+                               int32_t substeps, float dt, void* stream) {
+    if (int rc = cartpole_range("oige_cartpole_env_step_f32", n_envs)) return rc;
+    if (!model || !params || !state || !buf || !actions_in)
+        return fail(OIGE_E_NULL, "oige_cartpole_env_step_f32: null argument");
+    if (substeps < 1 || substeps > 64) return fail(OIGE_E_RANGE, "substeps %d not in [1,64]", substeps);
+    if (n_envs == 0) return OIGE_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    // VecEnvRLGames.step: clamp -> pre_physics_step (reset flagged envs, efforts) -> substeps x world.step
+    //                     -> post_physics_step
+    if (int rc = cartpole_pre(params, state, buf, actions_in, clip_actions, nullptr, seed, counter, env_id_offset,
+                              n_envs, s, buf->reset_counter != nullptr))
+        return rc;
+    OigeTaskParams unit;  // K2 reads num_dof, joint_gears and power_scale: the efforts are already formed
+    memset(&unit, 0, sizeof(unit));
+    unit.num_dof = 2;
+    unit.joint_gears[0] = unit.joint_gears[1] = 1.0f;
+    unit.power_scale = 1.0f;
+    if (int rc = k2_step(model, &unit, state, buf->efforts, n_envs, substeps, dt, s, 0)) return rc;
+    return cartpole_post(params, state, buf, n_envs, s, true);
+}
+
 
 }  // extern "C"
