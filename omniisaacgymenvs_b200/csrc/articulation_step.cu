@@ -297,16 +297,15 @@ __device__ __forceinline__ void joint_force(const DevModel& M, int li, float q, 
         Kimp += M.k_lim; Dimp += M.d_lim;
     }
     if (has_target) {
-        // PD position drive (ArticulationView.set_joint_position_targets): implicit like the passive spring,
-        // unless it saturates at the drive's force limit, where it acts as a constant torque
+        // PD position drive (ArticulationView.set_joint_position_targets): implicit like the passive spring.
+        // Force limit: when the drive torque at the current state exceeds it, both gains are scaled by
+        // fmax / |torque| -- the torque is then exactly +-fmax and the drive stays implicit (and passive), so a
+        // saturated stiff drive cannot chatter the way a constant explicit torque would.
         const float kp = M.drive_kp[li], kd = M.drive_kd[li], fmax = M.drive_fmax[li];
         const float tpd = kp * (target - qn) - kd * qd;
-        if (fmax > 0.f && fabsf(tpd) > fmax) {
-            tau0 += copysignf(fmax, tpd);
-        } else {
-            tau0 += tpd;
-            Kimp += kp; Dimp += kd;
-        }
+        const float alpha = (fmax > 0.f && fabsf(tpd) > fmax) ? fmax / fabsf(tpd) : 1.f;
+        tau0 += alpha * tpd;
+        Kimp += alpha * kp; Dimp += alpha * kd;
     }
     dextra = M.armature[li] + dt * (Dimp + dt * Kimp);
 }

@@ -207,4 +207,59 @@ CARTPOLE = dict(
     gears={"cartJoint": 1.0, "poleJoint": 1.0},  # efforts are formed by the task (tasks/cartpole.py:104-105)
 )
 
-ROBOTS = {"Humanoid": HUMANOID, "Ant": ANT, "Cartpole": CARTPOLE}
+def anymal_bodies():
+    """ANYmal C (``/Isaac/Robots/ANYbotics/anymal_instanceable.usd``, robots/articulations/anymal.py:58), restated
+    from the public ``anymal_c`` URDF as recalled (PROVENANCE: unpinned; the reference pins the 12 DoF names and
+    their order, robots/articulations/anymal.py:72-83, the spawn height 0.62, tasks/anymal.py:100, the fall
+    threshold 0.51 m, tasks/anymal.py:284, and the link names ``base`` / ``*_SHANK``, views/anymal_view.py:49-50).
+    Per leg: HAA about x at (+-0.2999, +-0.104, 0) on the base, HFE about y at (+-0.0599, +-0.08381, 0), KFE about
+    y at (0, +-0.1003, -0.285), foot (sphere r = 0.03) at (+-0.08795, +-0.01305, -0.33797) in the shank frame.
+    Masses: base + attached boxes 25.2, hip 2.781, thigh 3.071, shank + foot 0.838 kg (52 kg in total).  Shapes
+    only distribute those masses and place collision spheres (feet, knees, base corners)."""
+    import math
+
+    base = dict(
+        name="base", parent=None, pos=(0, 0, 0), quat=(1, 0, 0, 0), joints=[], mass=25.2,
+        geoms=[("box", (0, 0, 0.02), (0.65, 0.28, 0.2))]
+              + [("csphere", (sx * 0.3, sy * 0.12, sz * 0.08 + 0.02), 0.04) for sx in (-1, 1) for sy in (-1, 1) for sz in (-1, 1)],
+    )
+    legs = [("LF", 1.0, 1.0), ("LH", -1.0, 1.0), ("RF", 1.0, -1.0), ("RH", -1.0, -1.0)]
+    jd = dict(stiffness=0.0, damping=0.0, armature=0.0)
+    haa, free = math.degrees(0.72), math.degrees(9.42)
+    hips, thighs, shanks = [], [], []
+    for nm, sx, sy in legs:
+        hips.append(dict(
+            name=f"{nm}_HIP", parent="base", pos=(sx * 0.2999, sy * 0.104, 0.0), quat=(1, 0, 0, 0), mass=2.781,
+            joints=[dict(name=f"{nm}_HAA", anchor=(0, 0, 0), axis=(1, 0, 0), range=(-haa, haa), **jd)],
+            geoms=[("sphere", (sx * 0.0599, sy * 0.04, 0.0), 0.08)],
+        ))
+        thighs.append(dict(
+            name=f"{nm}_THIGH", parent=f"{nm}_HIP", pos=(sx * 0.0599, sy * 0.08381, 0.0), quat=(1, 0, 0, 0), mass=3.071,
+            joints=[dict(name=f"{nm}_HFE", anchor=(0, 0, 0), axis=(0, 1, 0), range=(-free, free), **jd)],
+            geoms=[("capsule", (0, sy * 0.05, 0), (0, sy * 0.09, -0.285), 0.04)],
+        ))
+        shanks.append(dict(
+            name=f"{nm}_SHANK", parent=f"{nm}_THIGH", pos=(0.0, sy * 0.1003, -0.285), quat=(1, 0, 0, 0), mass=0.838,
+            joints=[dict(name=f"{nm}_KFE", anchor=(0, 0, 0), axis=(0, 1, 0), range=(-free, free), **jd)],
+            geoms=[("capsule", (0, 0, 0), (sx * 0.08795, sy * 0.01305, -0.33797), 0.02),
+                   ("sphere", (sx * 0.08795, sy * 0.01305, -0.33797), 0.03)],
+        ))
+    # document order = breadth-first: the four hips, then thighs, then shanks (the reference's DoF order)
+    return [base] + hips + thighs + shanks
+
+
+ANYMAL = dict(
+    name="Anymal",
+    bodies=anymal_bodies,
+    density=1000.0,                       # overridden per body by the explicit masses
+    spawn_height=0.62,                    # tasks/anymal.py:100
+    sensor_bodies=[],
+    dof_order_in_body={},
+    gears={"HAA": 0.0, "HFE": 0.0, "KFE": 0.0},  # no effort actuation: PD position targets only (anymal.py:190)
+    # set_drive(..., "angular", "position", 0, 400, 40, 1000) (tasks/anymal.py:128, tasks/utils/usd_utils.py:71-82).
+    # UsdPhysics angular drives are specified PER DEGREE (stiffness in N*m/deg, damping in N*m*s/deg); the joint
+    # state and targets of the tensor API are in radians, hence the 180/pi factors.  The max force is 1000 N*m.
+    drive=dict(stiffness=400.0 * 57.29577951308232, damping=40.0 * 57.29577951308232, max_force=1000.0),
+)
+
+ROBOTS = {"Humanoid": HUMANOID, "Ant": ANT, "Cartpole": CARTPOLE, "Anymal": ANYMAL}

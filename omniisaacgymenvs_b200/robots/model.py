@@ -194,7 +194,7 @@ def build_model(name: str, **overrides) -> ArticulationModel:
     for b in bodies:
         link = last_link[b["name"]]
         off = last_anchor[b["name"]]
-        parts = [_geom_inertial(g, table["density"]) for g in b["geoms"]]
+        parts = [_geom_inertial(g, table["density"]) for g in b["geoms"] if g[0] != "csphere"]
         if b.get("mass") is not None:  # URDF-style explicit body mass: rescale the uniform-density parts
             k = float(b["mass"]) / sum(p[0] for p in parts)
             parts = [(p[0] * k, p[1], p[2] * k) for p in parts]
@@ -209,7 +209,10 @@ def build_model(name: str, **overrides) -> ArticulationModel:
         inertia[link] = [I[0, 0], I[1, 1], I[2, 2], I[0, 1], I[0, 2], I[1, 2]]
         for g in b["geoms"]:
             if g[0] == "box":
-                continue  # boxes carry mass only (the Cartpole never touches the ground)
+                continue  # boxes carry mass only
+            if g[0] == "csphere":  # collision-only sphere (no mass)
+                sph_link.append(link); sph_pos.append(np.array(g[1], float) - off); sph_r.append(g[2])
+                continue
             if g[0] == "sphere":
                 sph_link.append(link); sph_pos.append(np.array(g[1], float) - off); sph_r.append(g[2])
             else:
@@ -233,6 +236,11 @@ def build_model(name: str, **overrides) -> ArticulationModel:
         dof_names=dof_names, dof_body_names=dof_body_names, joint_gears=gears,
         spawn_height=table["spawn_height"], link_names=link_names,
     )
+    drive = table.get("drive")
+    if drive:  # PD position drive on every joint (tasks/anymal.py:128)
+        model.drive_stiffness[1:] = drive["stiffness"]
+        model.drive_damping[1:] = drive["damping"]
+        model.drive_max_force[1:] = drive["max_force"]
     for k, v in overrides.items():
         if not hasattr(model, k):
             raise AttributeError(k)

@@ -216,11 +216,11 @@ static int step_one(const OigeModelDesc* M, double* pos, double* quat, double* v
         double lo = M->limit_lower[i], hi = M->limit_upper[i];
         if (q[d] < lo) { tau += -(double)M->limit_stiffness * (qn - lo) - (double)M->limit_damping * qd[d]; Kimp += M->limit_stiffness; Dimp += M->limit_damping; }
         else if (q[d] > hi) { tau += -(double)M->limit_stiffness * (qn - hi) - (double)M->limit_damping * qd[d]; Kimp += M->limit_stiffness; Dimp += M->limit_damping; }
-        if (tgt) { /* PD position drive, implicit unless saturated at the force limit */
+        if (tgt) { /* PD position drive, implicit; past the force limit both gains are scaled by fmax/|torque| */
             double kp = M->drive_stiffness[i], kd = M->drive_damping[i], fmax = M->drive_max_force[i];
             double tpd = kp * (tgt[d] - qn) - kd * qd[d];
-            if (fmax > 0 && fabs(tpd) > fmax) tau += copysign(fmax, tpd);
-            else { tau += tpd; Kimp += kp; Dimp += kd; }
+            double alpha = (fmax > 0 && fabs(tpd) > fmax) ? fmax / fabs(tpd) : 1.0;
+            tau += alpha * tpd; Kimp += alpha * kp; Dimp += alpha * kd;
         }
         rhs[c] += tau;
         A[c * NV_MAX + c] += (double)M->armature[i] + dt * (Dimp + dt * Kimp);

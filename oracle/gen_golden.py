@@ -132,6 +132,14 @@ def main() -> None:
     from oracle import ref_cartpole_driver
 
     np.savez_compressed(os.path.join(GOLDEN_DIR, "episode_cartpole.npz"), **ref_cartpole_driver.run_episode(96, steps=6, seed=0))
+    # Anymal: the verbatim AnymalTask / AnymalView methods on a fake view (tasks/anymal.py:137-293)
+    from oracle import ref_anymal_driver
+
+    model = build_model("Anymal")
+    spawn = torch.from_numpy(grid_env_origins(96, 4.0))
+    spawn[:, 2] += model.spawn_height
+    ep = ref_anymal_driver.run_episode(96, steps=5, seed=0, spawn_pos=spawn, dof_limits=torch.from_numpy(model.dof_limits()))
+    np.savez_compressed(os.path.join(GOLDEN_DIR, "episode_anymal.npz"), **ep)
     print("wrote", len(os.listdir(GOLDEN_DIR)), "fixtures to", GOLDEN_DIR)
 
 
