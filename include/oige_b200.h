@@ -285,6 +285,72 @@ int oige_cartpole_env_step_f32(const OigeModel* model, const OigeCartpoleParams*
                                uint64_t seed, uint64_t counter, int64_t env_id_offset, int64_t n_envs,
                                int32_t substeps, float dt, void* stream);
 
+/* ================= Anymal, flat terrain (tasks/anymal.py) =================
+ * PD position-target actuation: pre_physics_step integrates and clamps the joint targets, K2 drives the joints
+ * toward them with the model's drive gains (set_drive, anymal.py:128), post_physics_step forms 48 observations,
+ * the velocity-tracking reward and the fall / time-out flags.  D = 12; all [N,12] tensors in the reference's
+ * breadth-first DoF order (robots/articulations/anymal.py:72-83). */
+#define OIGE_ANYMAL_DOF 12
+#define OIGE_ANYMAL_OBS 48
+
+typedef struct OigeAnymalParams {
+    int32_t progress_increment;  /* 1: fuse `progress_buf += 1` (rl_task.py:242) into the pass */
+    int32_t reserved_i[3];
+    float lin_vel_scale, ang_vel_scale, dof_pos_scale, dof_vel_scale; /* anymal.py:57-60 */
+    float action_scale;          /* 13.5 (anymal.py:61) */
+    float dt;                    /* task dt, 1/60 (anymal.py:88) */
+    /* reward scales ALREADY multiplied by dt in double precision (anymal.py:94-95) */
+    float rew_lin_vel_xy, rew_ang_vel_z, rew_lin_vel_z, rew_joint_acc, rew_action_rate, rew_cosmetic;
+    float command_x[2], command_y[2], command_yaw[2]; /* (min, max) of the resampled commands (anymal.py:72-74) */
+    float fallen_threshold;      /* base height below which the env is reset with reward -1, 0.51 (anymal.py:284) */
+    float max_episode_length;    /* int(episodeLength_s / dt + 0.5) = 3000; done when progress >= it - 1 */
+    float clip_obs;              /* 5.0; the STORED observations are clamped */
+    float reserved_f;
+    float default_dof_pos[OIGE_ANYMAL_DOF];   /* defaultJointAngles in DoF order (anymal.py:130-135) */
+    float dof_limits_lower[OIGE_ANYMAL_DOF];  /* anymal.py:234-235 */
+    float dof_limits_upper[OIGE_ANYMAL_DOF];
+} OigeAnymalParams;
+
+typedef struct OigeAnymalBuffers {
+    float* obs;              /* [N,48] lin vel 3, ang vel 3, projected gravity 3, commands 3, dof pos 12, dof vel 12,
+                                actions 12 (anymal.py:158-169) */
+    float* rew;              /* [N] */
+    int64_t* reset_buf;      /* [N] */
+    int64_t* progress_buf;   /* [N] */
+    float* actions;          /* [N,12] the task's stored (clamped) actions */
+    float* last_actions;     /* [N,12] in/out (anymal.py:280) */
+    float* last_dof_vel;     /* [N,12] in/out (anymal.py:281) */
+    float* commands;         /* [N,3] x, y, yaw velocity commands (anymal.py:237-240) */
+    float* current_targets;  /* [N,12] joint position targets; the caller passes the same tensor as
+                                OigeState.dof_pos_targets (what set_joint_position_targets receives) */
+    double* episode_stats;   /* [OIGE_STATS_SLOTS,4] or NULL, as in OigeTaskBuffers */
+    uint64_t* reset_counter; /* NULL or device scalar, as in OigeTaskBuffers */
+} OigeAnymalBuffers;
+
+/* get_observations + calculate_metrics + is_done (+ progress += 1) in one pass (anymal.py:137-179,252-293). */
+int oige_anymal_obs_reward_reset_f32(const OigeAnymalParams* params, const OigeState* state,
+                                     const OigeAnymalBuffers* buf, int64_t n_envs, void* stream);
+/* pre_physics_step (anymal.py:181-190): device-side masked reset_idx (no nonzero() host sync), then -- if
+ * actions_in ([N,12]) is not NULL -- actions = clamp(actions_in, +-clip_actions) and
+ * current_targets = clamp(current_targets + action_scale * actions * dt, lower, upper).
+ * rand_vel [N,12] / rand_cmd [N,3]: raw U[0,1) draws in the reference's draw order (joint velocities; command
+ * x, y, yaw; anymal.py:195,211-219) or NULL for Philox keyed by (seed, env_id_offset + env, counter).
+ * init: initial_root_pos / initial_root_rot (anymal.py:230); initial_dof_pos is not read. */
+int oige_anymal_reset_masked_f32(const OigeAnymalParams* params, const OigeState* state, const OigeAnymalBuffers* buf,
+                                 const OigeResetInit* init, const float* actions_in, float clip_actions,
+                                 const float* rand_vel, const float* rand_cmd, uint64_t seed, uint64_t counter,
+                                 int64_t env_id_offset, int64_t n_envs, void* stream);
+/* reset_idx(env_ids) (anymal.py:192-227); rand_vel [k,12], rand_cmd [k,3] or NULL. */
+int oige_anymal_reset_idx_f32(const OigeAnymalParams* params, const OigeState* state, const OigeAnymalBuffers* buf,
+                              const OigeResetInit* init, const int64_t* env_ids, int64_t k, const float* rand_vel,
+                              const float* rand_cmd, uint64_t seed, uint64_t counter, int64_t env_id_offset,
+                              void* stream);
+/* Whole VecEnvRLGames.step (envs/vec_env_rlgames.py:56-78) for Anymal on device buffers: three launches. */
+int oige_anymal_env_step_f32(const OigeModel* model, const OigeAnymalParams* params, const OigeState* state,
+                             const OigeAnymalBuffers* buf, const OigeResetInit* init, const float* actions_in,
+                             float clip_actions, uint64_t seed, uint64_t counter, int64_t env_id_offset,
+                             int64_t n_envs, int32_t substeps, float dt, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

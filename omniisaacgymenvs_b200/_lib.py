@@ -84,6 +84,28 @@ class OigeCartpoleBuffers(C.Structure):
                 ("episode_stats", vp), ("reset_counter", vp)]
 
 
+ANYMAL_DOF = 12
+ANYMAL_OBS = 48
+
+
+class OigeAnymalParams(C.Structure):
+    _fields_ = [("progress_increment", i32), ("reserved_i", i32 * 3),
+                ("lin_vel_scale", f32), ("ang_vel_scale", f32), ("dof_pos_scale", f32), ("dof_vel_scale", f32),
+                ("action_scale", f32), ("dt", f32),
+                ("rew_lin_vel_xy", f32), ("rew_ang_vel_z", f32), ("rew_lin_vel_z", f32), ("rew_joint_acc", f32),
+                ("rew_action_rate", f32), ("rew_cosmetic", f32),
+                ("command_x", f32 * 2), ("command_y", f32 * 2), ("command_yaw", f32 * 2),
+                ("fallen_threshold", f32), ("max_episode_length", f32), ("clip_obs", f32), ("reserved_f", f32),
+                ("default_dof_pos", f32 * ANYMAL_DOF), ("dof_limits_lower", f32 * ANYMAL_DOF),
+                ("dof_limits_upper", f32 * ANYMAL_DOF)]
+
+
+class OigeAnymalBuffers(C.Structure):
+    _fields_ = [("obs", vp), ("rew", vp), ("reset_buf", vp), ("progress_buf", vp), ("actions", vp),
+                ("last_actions", vp), ("last_dof_vel", vp), ("commands", vp), ("current_targets", vp),
+                ("episode_stats", vp), ("reset_counter", vp)]
+
+
 # every symbol include/oige_b200.h declares (tests/test_capi_symbols.py checks the .so exports them)
 EXPORTED_SYMBOLS = [
     "oige_abi_version", "oige_last_error", "oige_kernel_launch_count",
@@ -93,6 +115,8 @@ EXPORTED_SYMBOLS = [
     "oige_env_step_f32", "oige_env_step_host_f32",
     "oige_cartpole_obs_reward_reset_f32", "oige_cartpole_reset_masked_f32", "oige_cartpole_reset_idx_f32",
     "oige_cartpole_env_step_f32",
+    "oige_anymal_obs_reward_reset_f32", "oige_anymal_reset_masked_f32", "oige_anymal_reset_idx_f32",
+    "oige_anymal_env_step_f32",
 ]
 
 _lib: Optional[C.CDLL] = None
@@ -134,6 +158,16 @@ def load() -> C.CDLL:
     lib.oige_cartpole_reset_masked_f32.argtypes = [CP, P(OigeState), CB, vp, f32, vp, u64, u64, i64, i64, vp]
     lib.oige_cartpole_reset_idx_f32.argtypes = [CP, P(OigeState), CB, vp, i64, vp, u64, u64, i64, vp]
     lib.oige_cartpole_env_step_f32.argtypes = [vp, CP, P(OigeState), CB, vp, f32, u64, u64, i64, i64, i32, f32, vp]
+    AP, AB = P(OigeAnymalParams), P(OigeAnymalBuffers)
+    lib.oige_anymal_obs_reward_reset_f32.argtypes = [AP, P(OigeState), AB, i64, vp]
+    lib.oige_anymal_reset_masked_f32.argtypes = [AP, P(OigeState), AB, P(OigeResetInit), vp, f32, vp, vp, u64, u64, i64,
+                                                 i64, vp]
+    lib.oige_anymal_reset_idx_f32.argtypes = [AP, P(OigeState), AB, P(OigeResetInit), vp, i64, vp, vp, u64, u64, i64, vp]
+    lib.oige_anymal_env_step_f32.argtypes = [vp, AP, P(OigeState), AB, P(OigeResetInit), vp, f32, u64, u64, i64, i64,
+                                             i32, f32, vp]
+    for name in ("oige_anymal_obs_reward_reset_f32", "oige_anymal_reset_masked_f32", "oige_anymal_reset_idx_f32",
+                 "oige_anymal_env_step_f32"):
+        getattr(lib, name).restype = C.c_int
     for name in ("oige_obs_reward_reset_f32", "oige_obs_reward_reset_tile_f32", "oige_reset_masked_f32",
                  "oige_reset_idx_f32", "oige_articulation_step_f32", "oige_env_step_f32", "oige_env_step_host_f32",
                  "oige_cartpole_obs_reward_reset_f32", "oige_cartpole_reset_masked_f32",

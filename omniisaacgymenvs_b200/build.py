@@ -27,6 +27,7 @@ SOURCES = [
     ("obs_reward_reset.cu", ["-fmad=false"]),
     ("reset_idx.cu", ["-fmad=false"]),
     ("cartpole.cu", ["-fmad=false"]),
+    ("anymal.cu", ["-fmad=false"]),
     ("articulation_step.cu", []),
     ("capi.cu", []),
 ]

@@ -57,6 +57,11 @@ int k3_idx(const OigeTaskParams*, const OigeState*, const OigeTaskBuffers*, cons
 int k2_step(const OigeModel*, const OigeTaskParams*, const OigeState*, const float*, int64_t, int32_t, float,
             cudaStream_t, int64_t decision_n);
 OigeModel* k2_model_create(const OigeModelDesc*);
+int anymal_post(const OigeAnymalParams*, const OigeState*, const OigeAnymalBuffers*, int64_t, cudaStream_t, bool);
+int anymal_pre(const OigeAnymalParams*, const OigeState*, const OigeAnymalBuffers*, const OigeResetInit*, const float*,
+               float, const float*, const float*, uint64_t, uint64_t, int64_t, int64_t, cudaStream_t, bool);
+int anymal_reset_idx(const OigeAnymalParams*, const OigeState*, const OigeAnymalBuffers*, const OigeResetInit*,
+                     const int64_t*, int64_t, const float*, const float*, uint64_t, uint64_t, int64_t, cudaStream_t);
 int cartpole_post(const OigeCartpoleParams*, const OigeState*, const OigeCartpoleBuffers*, int64_t, cudaStream_t, bool);
 int cartpole_pre(const OigeCartpoleParams*, const OigeState*, const OigeCartpoleBuffers*, const float*, float,
                  const float*, uint64_t, uint64_t, int64_t, int64_t, cudaStream_t, bool);
@@ -299,5 +304,56 @@ int oige_cartpole_env_step_f32(const OigeModel* model, const OigeCartpoleParams*
     return cartpole_post(params, state, buf, n_envs, s, true);
 }
 
+
+// ---- Anymal (tasks/anymal.py) ------------------------------------------------------------------------------
+int oige_anymal_obs_reward_reset_f32(const OigeAnymalParams* params, const OigeState* state,
+                                     const OigeAnymalBuffers* buf, int64_t n_envs, void* stream) {
+    if (int rc = cartpole_range("oige_anymal_obs_reward_reset_f32", n_envs)) return rc;
+    if (n_envs == 0) return (params && state && buf) ? OIGE_OK : fail(OIGE_E_NULL, "oige_anymal_obs_reward_reset_f32: null struct pointer");
+    return anymal_post(params, state, buf, n_envs, (cudaStream_t)stream, false);
+}
+
+int oige_anymal_reset_masked_f32(const OigeAnymalParams* params, const OigeState* state, const OigeAnymalBuffers* buf,
+                                 const OigeResetInit* init, const float* actions_in, float clip_actions,
+                                 const float* rand_vel, const float* rand_cmd, uint64_t seed, uint64_t counter,
+                                 int64_t env_id_offset, int64_t n_envs, void* stream) {
+    if (int rc = cartpole_range("oige_anymal_reset_masked_f32", n_envs)) return rc;
+    if (n_envs == 0) return (params && state && buf) ? OIGE_OK : fail(OIGE_E_NULL, "oige_anymal_reset_masked_f32: null struct pointer");
+    return anymal_pre(params, state, buf, init, actions_in, clip_actions, rand_vel, rand_cmd, seed, counter,
+                      env_id_offset, n_envs, (cudaStream_t)stream, false);
+}
+
+int oige_anymal_reset_idx_f32(const OigeAnymalParams* params, const OigeState* state, const OigeAnymalBuffers* buf,
+                              const OigeResetInit* init, const int64_t* env_ids, int64_t k, const float* rand_vel,
+                              const float* rand_cmd, uint64_t seed, uint64_t counter, int64_t env_id_offset,
+                              void* stream) {
+    if (int rc = cartpole_range("oige_anymal_reset_idx_f32", k)) return rc;
+    if (k == 0) return (params && state && buf) ? OIGE_OK : fail(OIGE_E_NULL, "oige_anymal_reset_idx_f32: null struct pointer");
+    return anymal_reset_idx(params, state, buf, init, env_ids, k, rand_vel, rand_cmd, seed, counter, env_id_offset,
+                            (cudaStream_t)stream);
+}
+
+int oige_anymal_env_step_f32(const OigeModel* model, const OigeAnymalParams* params, const OigeState* state,
+                             const OigeAnymalBuffers* buf, const OigeResetInit* init, const float* actions_in,
+                             float clip_actions, uint64_t seed, uint64_t counter, int64_t env_id_offset,
+                             int64_t n_envs, int32_t substeps, float dt, void* stream) {
+    if (int rc = cartpole_range("oige_anymal_env_step_f32", n_envs)) return rc;
+    if (!model || !params || !state || !buf || !init || !actions_in)
+        return fail(OIGE_E_NULL, "oige_anymal_env_step_f32: null argument");
+    if (substeps < 1 || substeps > 64) return fail(OIGE_E_RANGE, "substeps %d not in [1,64]", substeps);
+    if (state->dof_pos_targets == nullptr || state->dof_pos_targets != buf->current_targets)
+        return fail(OIGE_E_NULL, "oige_anymal_env_step_f32: state.dof_pos_targets must be buf.current_targets");
+    if (n_envs == 0) return OIGE_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (int rc = anymal_pre(params, state, buf, init, actions_in, clip_actions, nullptr, nullptr, seed, counter,
+                            env_id_offset, n_envs, s, buf->reset_counter != nullptr))
+        return rc;
+    OigeTaskParams unit;  // K2 reads num_dof, joint_gears and power_scale; zero gears = no effort actuation,
+    memset(&unit, 0, sizeof(unit));  // the joints are driven by the PD position drive toward current_targets
+    unit.num_dof = OIGE_ANYMAL_DOF;
+    unit.power_scale = 1.0f;
+    if (int rc = k2_step(model, &unit, state, buf->actions, n_envs, substeps, dt, s, 0)) return rc;
+    return anymal_post(params, state, buf, n_envs, s, true);
+}
 
 }  // extern "C"

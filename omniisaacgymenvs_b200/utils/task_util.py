@@ -1,14 +1,16 @@
 """Task registry and construction (reference: utils/task_util.py:30-71).  Built here: the locomotion hot path
-(Ant, Humanoid) and Cartpole; the reference's other tasks are out of scope."""
+(Ant, Humanoid), Cartpole and flat-terrain Anymal (N2); the reference's other tasks are out of scope."""
 from omniisaacgymenvs_b200.utils.config import SimConfig
 
 
 def task_map() -> dict:
     from omniisaacgymenvs_b200.tasks.ant import AntLocomotionTask
+    from omniisaacgymenvs_b200.tasks.anymal import AnymalTask
     from omniisaacgymenvs_b200.tasks.cartpole import CartpoleTask
     from omniisaacgymenvs_b200.tasks.humanoid import HumanoidLocomotionTask
 
-    return {"Ant": AntLocomotionTask, "Humanoid": HumanoidLocomotionTask, "Cartpole": CartpoleTask}
+    return {"Ant": AntLocomotionTask, "Humanoid": HumanoidLocomotionTask, "Cartpole": CartpoleTask,
+            "Anymal": AnymalTask}
 
 
 def initialize_task(config, env, init_sim=True):

@@ -42,6 +42,8 @@ def test_struct_layouts_match_header_sizes():
     assert ctypes.sizeof(_lib.OigeResetInit) == 3 * 8
     assert ctypes.sizeof(_lib.OigeCartpoleParams) == 8 * 4
     assert ctypes.sizeof(_lib.OigeCartpoleBuffers) == 7 * 8
+    assert ctypes.sizeof(_lib.OigeAnymalParams) == 4 * 4 + 22 * 4 + 3 * 12 * 4
+    assert ctypes.sizeof(_lib.OigeAnymalBuffers) == 11 * 8
     L, K, S = _lib.MAX_LINKS, _lib.MAX_SPHERES, _lib.MAX_SENSORS
     expect = 16 + 3 * L * 4 + L * 4 * (3 + 4 + 3 + 1 + 3 + 6 + 6 + 3) + K * 4 * (1 + 3 + 1) + S * 4 + (3 + 8) * 4
     assert ctypes.sizeof(_lib.OigeModelDesc) == expect
