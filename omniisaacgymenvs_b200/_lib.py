@@ -16,7 +16,7 @@ MAX_DOF = 32
 MAX_LINKS = 32
 MAX_SPHERES = 48
 MAX_SENSORS = 4
-STATS_SLOTS = 32
+STATS_SLOTS = 2048
 LIMIT_COST_HUMANOID = 0
 LIMIT_COST_ANT = 1
 
