@@ -12,6 +12,7 @@ outputs.  The fixtures travel to the GPU box where /root/reference does not exis
 """
 import math
 import os
+import sys
 
 import numpy as np
 import torch
@@ -106,7 +107,17 @@ def save_case(name: str, spec: lo.TaskSpec, s: dict) -> None:
     np.savez_compressed(os.path.join(GOLDEN_DIR, name + ".npz"), **blob)
 
 
+def write_dr() -> None:
+    """Observation / action noise: the verbatim Randomizer methods
+    (utils/domain_randomization/randomize.py:212-305); `python -m oracle.gen_golden dr` writes this fixture only."""
+    from oracle import ref_dr_driver
+
+    np.savez_compressed(os.path.join(GOLDEN_DIR, "episode_dr.npz"), **ref_dr_driver.run_all())
+
+
 def main() -> None:
+    if sys.argv[1:] == ["dr"]:
+        return write_dr()
     if not ref_loader.reference_available():
         raise SystemExit("reference tree not found: golden vectors can only be generated in the build container")
     torch.set_num_threads(1)
@@ -140,6 +151,7 @@ def main() -> None:
     spawn[:, 2] += model.spawn_height
     ep = ref_anymal_driver.run_episode(96, steps=5, seed=0, spawn_pos=spawn, dof_limits=torch.from_numpy(model.dof_limits()))
     np.savez_compressed(os.path.join(GOLDEN_DIR, "episode_anymal.npz"), **ep)
+    write_dr()
     print("wrote", len(os.listdir(GOLDEN_DIR)), "fixtures to", GOLDEN_DIR)
 
 
