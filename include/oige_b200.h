@@ -351,6 +351,38 @@ int oige_anymal_env_step_f32(const OigeModel* model, const OigeAnymalParams* par
                              float clip_actions, uint64_t seed, uint64_t counter, int64_t env_id_offset,
                              int64_t n_envs, int32_t substeps, float dt, void* stream);
 
+/* ---- observation / action noise (utils/domain_randomization/randomize.py:212-305) -------------------------------
+ * Replaces Randomizer.apply_actions_randomization / apply_observations_randomization, the two hooks of
+ * VecEnvRLGames.step (envs/vec_env_rlgames.py:59-60,70-71), with one launch per buffer and no nonzero() host sync. */
+enum { OIGE_DR_GAUSSIAN = 0, OIGE_DR_UNIFORM = 1, OIGE_DR_LOGUNIFORM = 2 };
+enum { OIGE_DR_ADDITIVE = 0, OIGE_DR_SCALING = 1 };
+enum { OIGE_DR_STREAM_ACTIONS = 0, OIGE_DR_STREAM_OBSERVATIONS = 2 }; /* + 0 on_reset, + 1 on_interval */
+
+typedef struct OigeNoiseSpec {   /* one on_reset / on_interval block of the task YAML */
+    int32_t enabled;             /* 0: block absent */
+    int32_t operation;           /* OIGE_DR_ADDITIVE | OIGE_DR_SCALING */
+    int32_t distribution;        /* OIGE_DR_* */
+    int32_t frequency_interval;  /* on_interval only */
+    float p0, p1;                /* (mean, std) or (low, high) */
+} OigeNoiseSpec;
+
+typedef struct OigeNoiseState {  /* randomize.py:192-193 / :209-210 */
+    int32_t* counter;            /* [N] steps since the last interval noise (int32, as the reference's torch.int) */
+    float* correlated;           /* [N,dim] on-reset noise kept until the env's next reset; may be NULL if !on_reset.enabled */
+} OigeNoiseState;
+
+/* out[N,dim] = clamp(noise(clamp(in[N,dim], +-clip_in)), +-clip_out); `out` may alias `in`; INFINITY skips a clamp.
+ * clip_in folds the wrapper's action clamp (vec_env_rlgames.py:57, before the noise) and clip_out its observation
+ * clamp (vec_env_rlgames.py:42, after the noise) into the launch.  reset_buf [N] int64 is only read.
+ * noise_reset / noise_interval: [N,dim] ready-made noise values, read at the flagged envs only (parity mode: the
+ * caller made the reference's torch.normal / torch.rand draws), or NULL for in-kernel Philox4x32-10 keyed by
+ * (seed, env_id_offset + env, counter, stream + {0,1}) -- sharding-invariant.  If counter_dev is not NULL the
+ * counter is read from that device scalar instead (CUDA-graph replays; the task's reset counter serves). */
+int oige_dr_apply_f32(const OigeNoiseSpec* on_reset, const OigeNoiseSpec* on_interval, const OigeNoiseState* state,
+                      const float* in, float* out, const int64_t* reset_buf, int64_t n_envs, int32_t dim, float clip_in,
+                      float clip_out, const float* noise_reset, const float* noise_interval, uint64_t seed, uint64_t counter,
+                      const uint64_t* counter_dev, int32_t stream_id, int64_t env_id_offset, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -106,6 +106,20 @@ class OigeAnymalBuffers(C.Structure):
                 ("episode_stats", vp), ("reset_counter", vp)]
 
 
+DR_GAUSSIAN, DR_UNIFORM, DR_LOGUNIFORM = 0, 1, 2
+DR_ADDITIVE, DR_SCALING = 0, 1
+DR_STREAM_ACTIONS, DR_STREAM_OBSERVATIONS = 0, 2
+
+
+class OigeNoiseSpec(C.Structure):
+    _fields_ = [("enabled", i32), ("operation", i32), ("distribution", i32), ("frequency_interval", i32),
+                ("p0", f32), ("p1", f32)]
+
+
+class OigeNoiseState(C.Structure):
+    _fields_ = [("counter", vp), ("correlated", vp)]
+
+
 # every symbol include/oige_b200.h declares (tests/test_capi_symbols.py checks the .so exports them)
 EXPORTED_SYMBOLS = [
     "oige_abi_version", "oige_last_error", "oige_kernel_launch_count",
@@ -117,6 +131,7 @@ EXPORTED_SYMBOLS = [
     "oige_cartpole_env_step_f32",
     "oige_anymal_obs_reward_reset_f32", "oige_anymal_reset_masked_f32", "oige_anymal_reset_idx_f32",
     "oige_anymal_env_step_f32",
+    "oige_dr_apply_f32",
 ]
 
 _lib: Optional[C.CDLL] = None
@@ -165,6 +180,9 @@ def load() -> C.CDLL:
     lib.oige_anymal_reset_idx_f32.argtypes = [AP, P(OigeState), AB, P(OigeResetInit), vp, i64, vp, vp, u64, u64, i64, vp]
     lib.oige_anymal_env_step_f32.argtypes = [vp, AP, P(OigeState), AB, P(OigeResetInit), vp, f32, u64, u64, i64, i64,
                                              i32, f32, vp]
+    lib.oige_dr_apply_f32.argtypes = [P(OigeNoiseSpec), P(OigeNoiseSpec), P(OigeNoiseState), vp, vp, vp, i64, i32, f32,
+                                      f32, vp, vp, u64, u64, vp, i32, i64, vp]
+    lib.oige_dr_apply_f32.restype = C.c_int
     for name in ("oige_anymal_obs_reward_reset_f32", "oige_anymal_reset_masked_f32", "oige_anymal_reset_idx_f32",
                  "oige_anymal_env_step_f32"):
         getattr(lib, name).restype = C.c_int

@@ -28,6 +28,7 @@ SOURCES = [
     ("reset_idx.cu", ["-fmad=false"]),
     ("cartpole.cu", ["-fmad=false"]),
     ("anymal.cu", ["-fmad=false"]),
+    ("domain_randomization.cu", ["-fmad=false"]),
     ("articulation_step.cu", []),
     ("capi.cu", []),
 ]

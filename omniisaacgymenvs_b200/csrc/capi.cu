@@ -57,6 +57,9 @@ int k3_idx(const OigeTaskParams*, const OigeState*, const OigeTaskBuffers*, cons
 int k2_step(const OigeModel*, const OigeTaskParams*, const OigeState*, const float*, int64_t, int32_t, float,
             cudaStream_t, int64_t decision_n);
 OigeModel* k2_model_create(const OigeModelDesc*);
+int dr_apply(const OigeNoiseSpec*, const OigeNoiseSpec*, const OigeNoiseState*, const float*, float*, const int64_t*,
+             int64_t, int32_t, float, float, const float*, const float*, uint64_t, uint64_t, const uint64_t*, int32_t,
+             int64_t, cudaStream_t);
 int anymal_post(const OigeAnymalParams*, const OigeState*, const OigeAnymalBuffers*, int64_t, cudaStream_t, bool);
 int anymal_pre(const OigeAnymalParams*, const OigeState*, const OigeAnymalBuffers*, const OigeResetInit*, const float*,
                float, const float*, const float*, uint64_t, uint64_t, int64_t, int64_t, cudaStream_t, bool);
@@ -354,6 +357,39 @@ int oige_anymal_env_step_f32(const OigeModel* model, const OigeAnymalParams* par
     unit.power_scale = 1.0f;
     if (int rc = k2_step(model, &unit, state, buf->actions, n_envs, substeps, dt, s, 0)) return rc;
     return anymal_post(params, state, buf, n_envs, s, true);
+}
+
+// ---- observation / action noise (utils/domain_randomization/randomize.py:212-305) -------------------------------
+static int noise_spec_ok(const char* who, const OigeNoiseSpec* sp, bool interval) {
+    if (!sp || !sp->enabled) return OIGE_OK;
+    if (sp->operation != OIGE_DR_ADDITIVE && sp->operation != OIGE_DR_SCALING)
+        return fail(OIGE_E_RANGE, "%s: operation %d is not additive/scaling", who, sp->operation);
+    if (sp->distribution < OIGE_DR_GAUSSIAN || sp->distribution > OIGE_DR_LOGUNIFORM)
+        return fail(OIGE_E_RANGE, "%s: distribution %d is not gaussian/uniform/loguniform", who, sp->distribution);
+    if (sp->distribution == OIGE_DR_LOGUNIFORM && !(sp->p0 > 0.f && sp->p1 > 0.f))
+        return fail(OIGE_E_RANGE, "%s: loguniform bounds must be positive", who);
+    if (interval && sp->frequency_interval < 0) return fail(OIGE_E_RANGE, "%s: negative frequency_interval", who);
+    return OIGE_OK;
+}
+
+int oige_dr_apply_f32(const OigeNoiseSpec* on_reset, const OigeNoiseSpec* on_interval, const OigeNoiseState* state,
+                      const float* in, float* out, const int64_t* reset_buf, int64_t n_envs, int32_t dim, float clip_in,
+                      float clip_out, const float* noise_reset, const float* noise_interval, uint64_t seed, uint64_t counter,
+                      const uint64_t* counter_dev, int32_t stream_id, int64_t env_id_offset, void* stream) {
+    const char* who = "oige_dr_apply_f32";
+    if (n_envs < 0 || n_envs > (int64_t)1 << 31) return fail(OIGE_E_RANGE, "%s: n_envs %lld out of range", who, (long long)n_envs);
+    if (dim < 1 || dim > 4096) return fail(OIGE_E_RANGE, "%s: dim %d not in [1,4096]", who, dim);
+    if (!state || !state->counter || !in || !out || !reset_buf) return fail(OIGE_E_NULL, "%s: null argument", who);
+    if (int rc = noise_spec_ok(who, on_reset, false)) return rc;
+    if (int rc = noise_spec_ok(who, on_interval, true)) return rc;
+    if (on_reset && on_reset->enabled && !state->correlated)
+        return fail(OIGE_E_NULL, "%s: on_reset noise needs state.correlated", who);
+    if (!(clip_in >= 0.f) || !(clip_out >= 0.f)) return fail(OIGE_E_RANGE, "%s: clip_in / clip_out must be >= 0 (INFINITY = no clamp)", who);
+    if (stream_id != OIGE_DR_STREAM_ACTIONS && stream_id != OIGE_DR_STREAM_OBSERVATIONS)
+        return fail(OIGE_E_RANGE, "%s: stream_id %d", who, stream_id);
+    if (n_envs == 0) return OIGE_OK;
+    return dr_apply(on_reset, on_interval, state, in, out, reset_buf, n_envs, dim, clip_in, clip_out, noise_reset, noise_interval, seed,
+                    counter, counter_dev, stream_id, env_id_offset, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -77,6 +77,8 @@ class World:
         if not soft or getattr(self._task, "_robots", None) is None:
             self._task.set_up_scene(self.scene)
         self._task.post_reset()
+        if hasattr(self._task, "set_up_domain_randomization"):
+            self._task.set_up_domain_randomization()
         self.current_time_step_index = 0
 
     def step(self, render: bool = False) -> None:

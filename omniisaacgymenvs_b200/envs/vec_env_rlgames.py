@@ -53,8 +53,11 @@ class VecEnvRLGames(VecEnvBase):
         self.graph_replays = 0
         launches0 = _lib.launch_count()
         saved = task._reset_counter
+        if task.randomize_actions or task.randomize_observations:
+            task._dr_randomizer.use_device_counter(task._reset_counter_dev)  # replays draw fresh noise
+            self._dr_actions_buffer()
         with torch.cuda.graph(self._graph, stream=side):
-            task.fused_step(self._g_actions, dt, graph_mode=True)
+            self._fused_step_with_noise(self._g_actions, dt, graph_mode=True)
             self._obs, self._rew, self._resets = task.obs_buf, task.rew_buf, task.reset_buf
             self._states = task.get_states()
             self._extras = task.extras
@@ -66,11 +69,34 @@ class VecEnvRLGames(VecEnvBase):
 
     def disable_cuda_graph(self) -> None:
         self._graph = None
+        if self._task.randomize_actions or self._task.randomize_observations:
+            self._task._dr_randomizer.use_device_counter(None)
+
+    # ---- observation / action noise around the fused step (vec_env_rlgames.py:59-60,70-71) -----------
+    def _dr_actions_buffer(self):
+        if getattr(self, "_dr_actions", None) is None:
+            self._dr_actions = torch.empty((self.num_envs, self._task.num_actions), device=self._task.device)
+        return self._dr_actions
+
+    def _fused_step_with_noise(self, actions, dt, graph_mode=False) -> None:
+        """clamp -> action noise -> [K3 K2 K1] -> observation noise -> clamp; each noise hook is one launch that also
+        performs the wrapper's clamp, so K3 / K1 run with their own clamps disabled.  The Philox step counter is
+        the task's reset counter (host value in eager mode, device scalar in graph mode: identical sequences)."""
+        task = self._task
+        dr = task._dr_randomizer
+        if task.randomize_actions:
+            a = actions if actions.dtype == torch.float32 and actions.is_contiguous() else actions.float().contiguous()
+            noisy = dr.apply_actions_randomization(actions=a, reset_buf=task.reset_buf, clip=task.clip_actions,
+                                                   out=self._dr_actions_buffer(), counter=task._reset_counter + 1)
+            task.fused_step(noisy, dt, graph_mode=graph_mode, clip_actions=float("inf"))
+        else:
+            task.fused_step(actions, dt, graph_mode=graph_mode)
+        if task.randomize_observations:
+            dr.apply_observations_randomization(observations=task.obs_buf, reset_buf=task.reset_buf,
+                                                clip=task.clip_obs, counter=task._reset_counter + 1)
 
     def step(self, actions):
         task = self._task
-        if task.randomize_actions or task.randomize_observations:
-            raise RuntimeError("domain randomisation is not part of this build (SURVEY.md section 8(f) N3)")
         if getattr(self, "_graph", None) is not None:
             self._g_actions.copy_(actions, non_blocking=True)
             self._graph.replay()
@@ -81,17 +107,22 @@ class VecEnvRLGames(VecEnvBase):
             return self._g_out[0], self._g_out[1], self._g_out[2], task.extras.copy()
         if getattr(task, "supports_fused_step", False) and task.fused_step_enabled():
             actions = actions.to(task.device)
-            task.fused_step(actions, self._world.get_physics_dt())
+            self._fused_step_with_noise(actions, self._world.get_physics_dt())
             self.sim_frame_count += task.control_frequency_inv
             self._world.current_time_step_index += task.control_frequency_inv
             self._obs, self._rew, self._resets, self._extras = task.obs_buf, task.rew_buf, task.reset_buf, task.extras
         else:
             actions = torch.clamp(actions, -task.clip_actions, task.clip_actions).to(task.device).clone()
+            if task.randomize_actions:
+                actions = task._dr_randomizer.apply_actions_randomization(actions=actions, reset_buf=task.reset_buf)
             task.pre_physics_step(actions)
             for _ in range(task.control_frequency_inv):
                 self._world.step(render=self._render)
                 self.sim_frame_count += 1
             self._obs, self._rew, self._resets, self._extras = task.post_physics_step()
+            if task.randomize_observations:
+                self._obs = task._dr_randomizer.apply_observations_randomization(
+                    observations=self._obs, reset_buf=task.reset_buf, clip=task.clip_obs)
         self._states = task.get_states()
         self._process_data()
         obs_dict = {"obs": self._obs, "states": self._states}
@@ -111,5 +142,7 @@ class VecEnvRLGames(VecEnvBase):
                   reset_host: torch.Tensor) -> None:
         """Whole step with HOST (ideally pinned) buffers through `oige_env_step_host_f32`:
         H2D actions, K3+K2+K1, D2H obs/rew/resets, all asynchronous on the current stream."""
+        if self._task.randomize_actions or self._task.randomize_observations:
+            raise RuntimeError("step_host does not apply observation / action noise; use step()")
         self._task.fused_step_host(actions_host, obs_host, rew_host, reset_host, self._world.get_physics_dt())
         self.sim_frame_count += self._task.control_frequency_inv

@@ -278,7 +278,8 @@ class AnymalTask(RLTask):
                 and cls.reset_idx is AnymalTask.reset_idx
                 and self._env._world.is_playing())
 
-    def fused_step(self, actions: torch.Tensor, physics_dt: float, graph_mode: bool = False) -> None:
+    def fused_step(self, actions: torch.Tensor, physics_dt: float, graph_mode: bool = False,
+                   clip_actions=None) -> None:
         """VecEnvRLGames.step (envs/vec_env_rlgames.py:56-78) as one C-ABI call."""
         self._check_bound()
         a = actions
@@ -288,7 +289,7 @@ class AnymalTask(RLTask):
         rc = _lib.load().oige_anymal_env_step_f32(
             self._anymals.model_handle, C.byref(self._params), C.byref(self._anymals.state_struct),
             C.byref(self._buffers_graph if graph_mode else self._buffers), C.byref(self._reset_init),
-            _lib.dptr(a, torch.float32, "actions"), float(self.clip_actions), self._reset_seed, self._reset_counter,
+            _lib.dptr(a, torch.float32, "actions"), float(self.clip_actions if clip_actions is None else clip_actions), self._reset_seed, self._reset_counter,
             self.env_id_offset, self._num_envs, int(self.control_frequency_inv), float(physics_dt), self._stream())
         _lib.check(rc, "oige_anymal_env_step_f32")
 

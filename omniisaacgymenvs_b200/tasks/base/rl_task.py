@@ -11,6 +11,7 @@ import torch
 
 from omniisaacgymenvs_b200.articulations import grid_env_origins
 from omniisaacgymenvs_b200.envs.vec_env_base import Box
+from omniisaacgymenvs_b200.utils.domain_randomization.randomize import Randomizer
 
 
 class BaseTask:
@@ -44,7 +45,7 @@ class RLTask(BaseTask):
         super().__init__(name=name, offset=offset)
         self.test = self._cfg.get("test", False)
         self._device = self._cfg["sim_device"]
-        self._dr_randomizer = None  # domain randomisation: out of scope
+        self._dr_randomizer = Randomizer(self._sim_config)  # observation / action noise
         print("Task Device:", self._device)
 
         self.randomize_actions = False
@@ -74,6 +75,14 @@ class RLTask(BaseTask):
         if not hasattr(self, "state_space"):
             self.state_space = Box(np.ones(self.num_states) * -np.inf, np.ones(self.num_states) * np.inf)
         self.cleanup()
+
+    def set_up_domain_randomization(self) -> None:
+        """Called by ``World.reset`` after ``post_reset``, where the reference's tasks that use the Randomizer call
+        it (tasks/shared/in_hand_manipulation.py:206-207).  The reference's locomotion / Anymal / Cartpole tasks never
+        do, so a ``domain_randomization`` block in their YAML is inert there; here it is honoured."""
+        if self._dr_randomizer.randomize and not getattr(self, "_dr_is_set_up", False):
+            self._dr_randomizer.set_up_domain_randomization(self)
+            self._dr_is_set_up = True
 
     def cleanup(self) -> None:
         """Allocates the RL buffers (rl_task.py:98-107)."""

@@ -190,7 +190,8 @@ class CartpoleTask(RLTask):
                 and cls.reset_idx is CartpoleTask.reset_idx
                 and self._env._world.is_playing())
 
-    def fused_step(self, actions: torch.Tensor, physics_dt: float, graph_mode: bool = False) -> None:
+    def fused_step(self, actions: torch.Tensor, physics_dt: float, graph_mode: bool = False,
+                   clip_actions=None) -> None:
         """VecEnvRLGames.step (envs/vec_env_rlgames.py:56-78) as one C-ABI call; ``graph_mode`` takes the reset
         counter from device memory so the call can be captured in a CUDA graph."""
         self._check_bound()
@@ -201,7 +202,7 @@ class CartpoleTask(RLTask):
         rc = _lib.load().oige_cartpole_env_step_f32(
             self._cartpoles.model_handle, C.byref(self._params), C.byref(self._cartpoles.state_struct),
             C.byref(self._buffers_graph if graph_mode else self._buffers), _lib.dptr(a, torch.float32, "actions"),
-            float(self.clip_actions), self._reset_seed, self._reset_counter, self.env_id_offset, self._num_envs,
+            float(self.clip_actions if clip_actions is None else clip_actions), self._reset_seed, self._reset_counter, self.env_id_offset, self._num_envs,
             int(self.control_frequency_inv), float(physics_dt), self._stream())
         _lib.check(rc, "oige_cartpole_env_step_f32")
 
