@@ -362,6 +362,9 @@ def run_ours(args):
     rew_h = torch.empty(n).pin_memory()
     rst_h = torch.empty(n, dtype=torch.int64).pin_memory()
     env.disable_cuda_graph()
+    if not args.no_cuda_graph:  # one captured graph per ring slot: H2D, 4 chunk streams of kernels, D2H
+        for a in a_host:
+            env.enable_cuda_graph_host(a, obs_h, rew_h, rst_h)
     for i in range(3):
         env.step_host(a_host[i % 4], obs_h, rew_h, rst_h)
     barrier()

@@ -682,8 +682,8 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
 // heavy child last, so a link directly follows its heavy child); only light children (chain heads)
 // go through a small slot array.  Same equations, same contact model, same integrator as above.
 // ================================================================================================
-template <int MAXL>
-__global__ void __launch_bounds__(128, TPE_MINBLOCKS)
+template <int MAXL, int MINB>
+__global__ void __launch_bounds__(128, MINB)
 articulation_step_tpe_kernel(const DevModel* __restrict__ gmodel, const __grid_constant__ OigeTaskParams P,
                              const __grid_constant__ K2Args A) {
     __shared__ __align__(16) DevModel M;
@@ -974,9 +974,20 @@ int k2_step(const OigeModel* model, const OigeTaskParams* P, const OigeState* st
         const int bs = 128;
         const unsigned tb = (unsigned)((n + bs - 1) / bs);
         const DevModel* dm = reinterpret_cast<const DevModel*>(model->dev_table);
-        if (model->num_links <= 12) articulation_step_tpe_kernel<12><<<tb, bs, 0, stream>>>(dm, *P, A);
-        else if (model->num_links <= 24) articulation_step_tpe_kernel<24><<<tb, bs, 0, stream>>>(dm, *P, A);
-        else articulation_step_tpe_kernel<32><<<tb, bs, 0, stream>>>(dm, *P, A);
+        // Up to two CTAs per SM cover the launch in one wave: the register budget per thread is then 255 instead of
+        // 126 and ptxas schedules for latency (the regime where one warp per scheduler runs alone).  Same PTX, same
+        // arithmetic -- only the register allocation / instruction order differ.
+        const char* mb = getenv("OIGE_K2_MINB");
+        const bool roomy = mb ? mb[0] == '2' : tb <= 2u * (unsigned)sm_count();
+        if (roomy) {
+            if (model->num_links <= 12) articulation_step_tpe_kernel<12, 2><<<tb, bs, 0, stream>>>(dm, *P, A);
+            else if (model->num_links <= 24) articulation_step_tpe_kernel<24, 2><<<tb, bs, 0, stream>>>(dm, *P, A);
+            else articulation_step_tpe_kernel<32, 2><<<tb, bs, 0, stream>>>(dm, *P, A);
+        } else {
+            if (model->num_links <= 12) articulation_step_tpe_kernel<12, TPE_MINBLOCKS><<<tb, bs, 0, stream>>>(dm, *P, A);
+            else if (model->num_links <= 24) articulation_step_tpe_kernel<24, TPE_MINBLOCKS><<<tb, bs, 0, stream>>>(dm, *P, A);
+            else articulation_step_tpe_kernel<32, TPE_MINBLOCKS><<<tb, bs, 0, stream>>>(dm, *P, A);
+        }
         count_launch();
         return check_launch("articulation_step_tpe_kernel");
     }

@@ -85,6 +85,8 @@ constexpr int kHostChunks = 4;
 struct HostPipe {
     cudaStream_t streams[kHostChunks];
     cudaEvent_t start, done[kHostChunks];
+    cudaEvent_t t0, t[kHostChunks][3];  // OIGE_HOST_TRACE=1: after H2D, after the kernels, after D2H (timing events)
+    bool trace, pending;
 };
 static HostPipe* host_pipe() {
     static HostPipe* pipes[64] = {nullptr};
@@ -97,11 +99,21 @@ static HostPipe* host_pipe() {
             ok = cudaStreamCreateWithFlags(&p->streams[i], cudaStreamNonBlocking) == cudaSuccess &&
                  cudaEventCreateWithFlags(&p->done[i], cudaEventDisableTiming) == cudaSuccess;
         }
+        const char* tr = getenv("OIGE_HOST_TRACE");
+        p->trace = tr && tr[0] == '1';
+        p->pending = false;
+        if (p->trace) {
+            ok = ok && cudaEventCreate(&p->t0) == cudaSuccess;
+            for (int i = 0; i < kHostChunks && ok; ++i)
+                for (int k = 0; k < 3 && ok; ++k) ok = cudaEventCreate(&p->t[i][k]) == cudaSuccess;
+        }
         if (!ok) { delete p; return nullptr; }
         pipes[dev] = p;
     }
     return pipes[dev];
 }
+
+__global__ void bump_counter_kernel(unsigned long long* c) { *c += 1; }
 
 }  // namespace oige
 
@@ -206,19 +218,43 @@ int oige_env_step_host_f32(const OigeModel* model, const OigeTaskParams* params,
     if (int rc = check_common("oige_env_step_host_f32", params, state, buf, n_envs)) return rc;
     if (!actions_host || !actions_dev_staging || !obs_host || !rew_host || !reset_host || !init || !model)
         return fail(OIGE_E_NULL, "oige_env_step_host_f32: null host/staging buffer");
-    if (n_envs == 0) return OIGE_OK;
     cudaStream_t user = (cudaStream_t)stream;
-    HostPipe* hp = host_pipe();
+    HostPipe* hp = host_pipe();  // created on the first call, also for n_envs == 0 (lets a caller warm up before a capture)
     if (!hp) return fail((int)cudaErrorUnknown, "oige_env_step_host_f32: cannot create copy/compute streams");
+    if (n_envs == 0) return OIGE_OK;
     // Envs are independent, so the step is cut into kHostChunks contiguous env ranges, each on its own
     // stream: H2D(actions) -> K3 -> K2 -> K1 -> D2H(obs, rew, resets).  Chunk c's D2H overlaps chunk c+1's
     // kernels and chunk c+2's H2D (separate copy engines per direction).  Results are identical to the
     // one-launch step: every kernel is row-wise and reset noise is keyed by the global env id.
     const int D = params->num_dof, S = params->num_sensors, OBS = params->num_obs;
+    // Opt-in (OIGE_HOST_ZEROCOPY=1) zero-copy observations: when obs_host is pinned (device-accessible under UVA) K1
+    // stores its observation tiles straight into it over PCIe (bulk shared->global stores) instead of a D2H copy per
+    // chunk; buf->obs on the device is then NOT written by this call.  Measured 272 vs 284 us per 16384-env step.
+    float* obs_host_dev = nullptr;
+    {
+        const char* zc = getenv("OIGE_HOST_ZEROCOPY");
+        cudaPointerAttributes at;
+        if (zc && zc[0] == '1' && cudaPointerGetAttributes(&at, obs_host) == cudaSuccess &&
+            at.type == cudaMemoryTypeHost && at.devicePointer != nullptr)
+            obs_host_dev = static_cast<float*>(at.devicePointer);
+        else if (zc && zc[0] == '1')
+            cudaGetLastError();  // unregistered host memory reports an error on older drivers: clear it
+    }
     int64_t per = ((n_envs + kHostChunks - 1) / kHostChunks + 31) / 32 * 32;  // tile-aligned chunk size
     if (n_envs < 4096) per = n_envs;                                           // too small to be worth splitting
+    if (hp->trace && hp->pending) {  // diagnostic: timeline of the PREVIOUS call (after it has completed)
+        cudaEventSynchronize(hp->t[kHostChunks - 1][2]);
+        for (int c = 0; c < kHostChunks; ++c) {
+            float a = 0, b = 0, d = 0;
+            cudaEventElapsedTime(&a, hp->t0, hp->t[c][0]); cudaEventElapsedTime(&b, hp->t0, hp->t[c][1]);
+            cudaEventElapsedTime(&d, hp->t0, hp->t[c][2]);
+            fprintf(stderr, "[oige host step] chunk %d: H2D done %.1f us, kernels done %.1f us, D2H done %.1f us\n", c,
+                    a * 1e3f, b * 1e3f, d * 1e3f);
+        }
+    }
     cudaError_t e = cudaEventRecord(hp->start, user);
     if (e != cudaSuccess) return fail((int)e, "event record: %s", cudaGetErrorString(e));
+    if (hp->trace) { cudaEventRecord(hp->t0, user); hp->pending = true; }
     int used = 0;
     for (int64_t off = 0; off < n_envs; off += per, ++used) {
         const int64_t cnt = (n_envs - off) < per ? (n_envs - off) : per;
@@ -232,22 +268,37 @@ int oige_env_step_host_f32(const OigeModel* model, const OigeTaskParams* params,
         OigeTaskBuffers bf = *buf;
         bf.obs += off * OBS; bf.rew += off; bf.reset_buf += off; bf.progress_buf += off; bf.potentials += off;
         bf.prev_potentials += off; bf.up_vec += off * 3; bf.heading_vec += off * 3; bf.actions += off * D;
-        bf.reset_counter = nullptr;  // chunks share the host-provided counter
+        if (obs_host_dev) bf.obs = obs_host_dev + off * OBS;
+        // chunks share one counter: the host-provided one, or -- when buf->reset_counter is set (the call is being
+        // captured in a CUDA graph) -- the device scalar, which K3 only reads; it is bumped once after the last chunk
         OigeResetInit in = *init;
         in.initial_root_pos += off * 3; in.initial_root_rot += off * 4; in.initial_dof_pos += off * D;
         float* stage = actions_dev_staging + off * D;
         e = cudaMemcpyAsync(stage, actions_host + off * D, (size_t)cnt * D * sizeof(float), cudaMemcpyHostToDevice, s);
         if (e != cudaSuccess) return fail((int)e, "H2D actions: %s", cudaGetErrorString(e));
+        if (hp->trace) cudaEventRecord(hp->t[used][0], s);
         if (int rc = env_step_impl(model, params, &st, &bf, &in, stage, clip_actions, seed, counter,
                                    env_id_offset + off, cnt, substeps, dt, (void*)s, n_envs))
             return rc;
-        e = cudaMemcpyAsync(obs_host + off * OBS, bf.obs, (size_t)cnt * OBS * sizeof(float), cudaMemcpyDeviceToHost, s);
-        if (e == cudaSuccess) e = cudaMemcpyAsync(rew_host + off, bf.rew, (size_t)cnt * sizeof(float), cudaMemcpyDeviceToHost, s);
-        if (e == cudaSuccess)
-            e = cudaMemcpyAsync(reset_host + off, bf.reset_buf, (size_t)cnt * sizeof(int64_t), cudaMemcpyDeviceToHost, s);
-        if (e != cudaSuccess) return fail((int)e, "D2H results: %s", cudaGetErrorString(e));
+        if (hp->trace) cudaEventRecord(hp->t[used][1], s);
+        // only the big observation block is copied per chunk: every copy costs ~5 us of fixed overhead on the copy
+        // engine, so the small rew / reset blocks of ALL chunks go out as two copies after the last chunk
+        if (!obs_host_dev) {
+            e = cudaMemcpyAsync(obs_host + off * OBS, bf.obs, (size_t)cnt * OBS * sizeof(float), cudaMemcpyDeviceToHost, s);
+            if (e != cudaSuccess) return fail((int)e, "D2H obs: %s", cudaGetErrorString(e));
+        }
+        if (hp->trace) cudaEventRecord(hp->t[used][2], s);
         cudaEventRecord(hp->done[used], s);
         cudaStreamWaitEvent(user, hp->done[used], 0);  // the caller's stream observes the whole step
+    }
+    e = cudaMemcpyAsync(rew_host, buf->rew, (size_t)n_envs * sizeof(float), cudaMemcpyDeviceToHost, user);
+    if (e == cudaSuccess)
+        e = cudaMemcpyAsync(reset_host, buf->reset_buf, (size_t)n_envs * sizeof(int64_t), cudaMemcpyDeviceToHost, user);
+    if (e != cudaSuccess) return fail((int)e, "D2H rew/reset: %s", cudaGetErrorString(e));
+    if (buf->reset_counter != nullptr) {
+        bump_counter_kernel<<<1, 1, 0, user>>>(reinterpret_cast<unsigned long long*>(buf->reset_counter));
+        count_launch();
+        return check_launch("bump_counter_kernel");
     }
     return OIGE_OK;
 }

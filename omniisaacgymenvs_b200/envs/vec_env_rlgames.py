@@ -137,6 +137,37 @@ class VecEnvRLGames(VecEnvBase):
         obs_dict, _, _, _ = self.step(actions)
         return obs_dict
 
+    def enable_cuda_graph_host(self, actions_host, obs_host, rew_host, reset_host) -> None:
+        """Captures ``step_host`` for THIS set of pinned host buffers (the copy engines' H2D / D2H transfers, the four
+        chunk streams of `oige_env_step_host_f32` and their kernels) in one CUDA graph; later ``step_host`` calls
+        with the same four buffers replay it -- one launch instead of ~40 stream operations per step.  Several
+        buffer sets may be registered (e.g. a ring of action buffers)."""
+        task = self._task
+        for t in (actions_host, obs_host, rew_host, reset_host):
+            if t.is_cuda or not t.is_pinned():
+                raise RuntimeError("enable_cuda_graph_host needs pinned host tensors")
+        if getattr(self, "_graph", None) is not None:
+            raise RuntimeError("device-buffer CUDA-graph mode is active; disable_cuda_graph() first")
+        dev = torch.device(task.device)
+        if not hasattr(self, "_host_graphs"):
+            self._host_graphs = {}
+            # creates the staging buffer and the library's streams / events without stepping the envs
+            task.fused_step_host(actions_host, obs_host, rew_host, reset_host, self._world.get_physics_dt(), run=False)
+            torch.cuda.synchronize(dev)
+        task._reset_counter_dev.fill_(task._reset_counter + 1)
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        g = torch.cuda.CUDAGraph()
+        saved = task._reset_counter
+        with torch.cuda.graph(g, stream=side):
+            task.fused_step_host(actions_host, obs_host, rew_host, reset_host, self._world.get_physics_dt(), graph_mode=True)
+        task._reset_counter = saved  # capture does not execute the step
+        torch.cuda.current_stream(dev).wait_stream(side)
+        self._host_graphs[(actions_host.data_ptr(), obs_host.data_ptr(), rew_host.data_ptr(), reset_host.data_ptr())] = g
+
+    def disable_cuda_graph_host(self) -> None:
+        self._host_graphs = {}
+
     # ---- host-buffer entry point (what a CPU-side trainer would call) -------------------------
     def step_host(self, actions_host: torch.Tensor, obs_host: torch.Tensor, rew_host: torch.Tensor,
                   reset_host: torch.Tensor) -> None:
@@ -144,5 +175,14 @@ class VecEnvRLGames(VecEnvBase):
         H2D actions, K3+K2+K1, D2H obs/rew/resets, all asynchronous on the current stream."""
         if self._task.randomize_actions or self._task.randomize_observations:
             raise RuntimeError("step_host does not apply observation / action noise; use step()")
+        g = getattr(self, "_host_graphs", {}).get(
+            (actions_host.data_ptr(), obs_host.data_ptr(), rew_host.data_ptr(), reset_host.data_ptr()))
+        if g is not None:
+            g.replay()
+            self._task._reset_counter += 1  # host mirror of the device-side counter
+            self.sim_frame_count += self._task.control_frequency_inv
+            return
         self._task.fused_step_host(actions_host, obs_host, rew_host, reset_host, self._world.get_physics_dt())
+        if getattr(self, "_host_graphs", None):  # keep the device-side counter of the captured graphs in step
+            self._task._reset_counter_dev.fill_(self._task._reset_counter + 1)
         self.sim_frame_count += self._task.control_frequency_inv

@@ -273,7 +273,8 @@ class LocomotionTask(RLTask):
             int(self.control_frequency_inv), float(physics_dt), self._stream())
         _lib.check(rc, "oige_env_step_f32")
 
-    def fused_step_host(self, actions_host, obs_host, rew_host, reset_host, physics_dt: float) -> None:
+    def fused_step_host(self, actions_host, obs_host, rew_host, reset_host, physics_dt: float,
+                        graph_mode: bool = False, run: bool = True) -> None:
         self._check_bound()
         if not hasattr(self, "_actions_staging"):
             self._actions_staging = torch.empty_like(self.actions)
@@ -281,13 +282,14 @@ class LocomotionTask(RLTask):
                       (reset_host, "reset_host")):
             if t.is_cuda or not t.is_contiguous():
                 raise RuntimeError(f"{nm} must be a contiguous host tensor")
-        self._reset_counter += 1
+        n = self._num_envs if run else 0  # n = 0: only creates the library's copy/compute streams
+        self._reset_counter += 1 if run else 0
         lib = _lib.load()
         rc = lib.oige_env_step_host_f32(
             self._robots.model_handle, C.byref(self._params), C.byref(self._robots.state_struct),
-            C.byref(self._buffers), C.byref(self._reset_init), actions_host.data_ptr(),
+            C.byref(self._buffers_graph if graph_mode else self._buffers), C.byref(self._reset_init), actions_host.data_ptr(),
             self._actions_staging.data_ptr(), obs_host.data_ptr(), rew_host.data_ptr(), reset_host.data_ptr(),
-            float(self.clip_actions), self._reset_seed, self._reset_counter, self.env_id_offset, self._num_envs,
+            float(self.clip_actions), self._reset_seed, self._reset_counter, self.env_id_offset, n,
             int(self.control_frequency_inv), float(physics_dt), self._stream())
         _lib.check(rc, "oige_env_step_host_f32")
 

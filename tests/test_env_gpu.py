@@ -175,6 +175,36 @@ def test_step_host_round_trip(cuda_lib, n):
     assert torch.equal(va.dof_pos, vb.dof_pos) and torch.equal(va.root_pos, vb.root_pos)
 
 
+@pytest.mark.parametrize("robot,n", [("Humanoid", 20000), ("Ant", 4096)])
+def test_step_host_cuda_graph_equals_device_step(cuda_lib, robot, n):
+    """enable_cuda_graph_host(): H2D, the chunk streams' kernels and D2H captured once per host-buffer set; replays
+    must be bit-identical to the device-buffer step, incl. reset noise over several reset waves, and may be mixed
+    with un-captured step_host calls."""
+    ov = {"task.env.episodeLength": 6}
+    env_a, task_a = make_env(robot, num_envs=n, seed=4, overrides=ov)
+    env_b, task_b = make_env(robot, num_envs=n, seed=4, overrides=ov)
+    env_a.reset(); env_b.reset()
+    A = task_a.num_actions
+    ring = [(torch.rand(n, A) * 2 - 1).pin_memory() for _ in range(3)]
+    obs_h = torch.empty(n, task_a.num_observations).pin_memory()
+    rew_h = torch.empty(n).pin_memory()
+    rst_h = torch.empty(n, dtype=torch.int64).pin_memory()
+    for ah in ring[:2]:
+        env_a.enable_cuda_graph_host(ah, obs_h, rew_h, rst_h)
+    resets = 0
+    for t in range(20):
+        ah = ring[t % 3]  # slot 2 was never captured: eager host step in between the replays
+        ah.copy_(torch.rand(n, A) * 2 - 1)
+        env_a.step_host(ah, obs_h, rew_h, rst_h)
+        torch.cuda.synchronize()
+        o, r, d, _ = env_b.step(ah.to(task_b.device))
+        assert torch.equal(obs_h, o["obs"].cpu()) and torch.equal(rew_h, r.cpu()) and torch.equal(rst_h, d.cpu()), t
+        resets += int(rst_h.sum())
+    assert resets > n and task_a._reset_counter == task_b._reset_counter
+    va, vb = task_a.get_robot(), task_b.get_robot()
+    assert torch.equal(va.dof_pos, vb.dof_pos) and torch.equal(va.root_pos, vb.root_pos)
+
+
 def test_cpu_tensors_are_rejected_not_silently_computed(cuda_lib):
     env, task = make_env("Ant", num_envs=64)
     env.reset()
