@@ -438,6 +438,12 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-cuda-graph", action="store_true")
     args = ap.parse_args()
+    # stdout carries exactly ONE JSON line: libraries that write to the C-level stdout (NCCL prints its version
+    # banner there) are sent to stderr by pointing fd 1 at fd 2 and giving Python's sys.stdout the original fd
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    sys.stdout = real_stdout
     if args.impl == "reference":
         return run_reference_arm(args)
     return run_ours(args)
