@@ -975,10 +975,13 @@ int k2_step(const OigeModel* model, const OigeTaskParams* P, const OigeState* st
         const unsigned tb = (unsigned)((n + bs - 1) / bs);
         const DevModel* dm = reinterpret_cast<const DevModel*>(model->dev_table);
         // Up to two CTAs per SM cover the launch in one wave: the register budget per thread is then 255 instead of
-        // 126 and ptxas schedules for latency (the regime where one warp per scheduler runs alone).  Same PTX, same
-        // arithmetic -- only the register allocation / instruction order differ.
+        // 126 and ptxas schedules for latency (the regime where one warp per scheduler runs alone).  Same PTX; ptxas
+        // schedules (and may fuse mul+add) differently, so the two variants agree to rounding, not bit for bit.
         const char* mb = getenv("OIGE_K2_MINB");
-        const bool roomy = mb ? mb[0] == '2' : tb <= 2u * (unsigned)sm_count();
+        // (decided on the WHOLE step's env count, like the kernel choice: ptxas may contract mul+add differently in
+        // the two instantiations, and chunked and one-shot steps must stay bit-identical)
+        const long long dn = decision_n > 0 ? decision_n : n;
+        const bool roomy = mb ? mb[0] == '2' : (dn + bs - 1) / bs <= 2ll * sm_count();
         if (roomy) {
             if (model->num_links <= 12) articulation_step_tpe_kernel<12, 2><<<tb, bs, 0, stream>>>(dm, *P, A);
             else if (model->num_links <= 24) articulation_step_tpe_kernel<24, 2><<<tb, bs, 0, stream>>>(dm, *P, A);
