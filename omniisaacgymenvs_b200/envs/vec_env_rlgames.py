@@ -61,7 +61,15 @@ class VecEnvRLGames(VecEnvBase):
             self._obs, self._rew, self._resets = task.obs_buf, task.rew_buf, task.reset_buf
             self._states = task.get_states()
             self._extras = task.extras
-            self._process_data()
+            if torch.device(task.rl_device) == dev:
+                # SURVEY.md 8(f) N1, "rl_device hand-off fused": the returned tensors are static buffers in this mode
+                # anyway, and obs_buf / rew_buf are written whole (already clamped) by the step and never read by the
+                # next one, so they ARE the hand-off buffers -- no clone kernels.  reset_buf is read by the next
+                # step's reset pass, so the caller still gets its own copy of it.
+                self._resets = self._resets.clone()
+                self._states = torch.clamp(self._states, -task.clip_obs, task.clip_obs).clone()
+            else:
+                self._process_data()
         task._reset_counter = saved  # capture does not execute the step
         self.graph_kernels = _lib.launch_count() - launches0  # kernels of liboige_b200.so inside one replay
         self._g_out = ({"obs": self._obs, "states": self._states}, self._rew, self._resets)
