@@ -95,38 +95,36 @@ class BufferNoise:
 def philox_noise(spec: NoiseSpec, seed: int, counter: int, env_gids, dim: int, stream: int) -> np.ndarray:
     """[len(env_gids), dim] float32 noise values the kernel generates for (seed, counter, global env id, stream).
 
-    One Philox4x32-10 call per (env, block of 4 columns): counter words (gid_lo, gid_hi, counter_lo,
-    counter_hi << 8 ^ block), key (seed_lo, seed_hi ^ 0x44520000 ^ stream).  Uniform / log-uniform use the four
-    24-bit uniforms; gaussian uses Box-Muller on the pairs (r0, r1) -> columns 0, 1 and (r2, r3) -> columns 2, 3 with
-    the radius uniform shifted to (0, 1]."""
+    Element (env, col) has the GLOBAL flat index ``gid * dim + col``; one Philox4x32-10 call serves the group of 4
+    consecutive flat indices: counter words (group_lo, group_hi, counter_lo, counter_hi), key (seed_lo,
+    seed_hi ^ 0x44520000 ^ stream); the element takes component ``flat & 3``.  Uniform / log-uniform use the four
+    24-bit uniforms; gaussian uses Box-Muller on the pairs (r0, r1) -> components 0, 1 and (r2, r3) -> components 2, 3
+    with the radius uniform shifted to (0, 1]."""
     gid = np.asarray(env_gids, dtype=np.uint64)
-    k = len(gid)
-    out = np.zeros((k, dim), np.float32)
-    c0 = (gid & np.uint64(0xFFFFFFFF)).astype(np.uint32)
-    c1 = (gid >> np.uint64(32)).astype(np.uint32)
+    flat = (gid[:, None] * np.uint64(dim) + np.arange(dim, dtype=np.uint64)[None, :]).ravel()
+    group, comp = flat >> np.uint64(2), (flat & np.uint64(3)).astype(np.int64)
+    k = len(flat)
+    c0 = (group & np.uint64(0xFFFFFFFF)).astype(np.uint32)
+    c1 = (group >> np.uint64(32)).astype(np.uint32)
     c2 = np.full(k, counter & 0xFFFFFFFF, np.uint32)
+    c3 = np.full(k, (counter >> 32) & 0xFFFFFFFF, np.uint32)
     k0 = np.full(k, seed & 0xFFFFFFFF, np.uint32)
     k1 = np.full(k, ((seed >> 32) & 0xFFFFFFFF) ^ 0x44520000 ^ stream, np.uint32)
-    hi = (((counter >> 32) & 0xFFFFFFFF) << 8) & 0xFFFFFFFF
     p0, p1 = (np.float32(p) for p in spec.distribution_parameters)
-    for blk in range((dim + 3) // 4):
-        r = philox.philox4x32_10(c0, c1, c2, np.full(k, hi ^ blk, np.uint32), k0, k1)
-        if spec.dist_code == GAUSSIAN:
-            vals = []
-            for a, b in ((r[0], r[1]), (r[2], r[3])):
-                u1 = ((a >> np.uint32(8)).astype(np.float32) + np.float32(1.0)) * np.float32(1.0 / 16777216.0)
-                u2 = philox.u01(b)
-                rad = np.sqrt(np.float32(-2.0) * np.log(u1)).astype(np.float32)
-                ang = (np.float32(6.2831853071795864) * u2).astype(np.float32)
-                vals += [rad * np.cos(ang).astype(np.float32), rad * np.sin(ang).astype(np.float32)]
-            vals = [(p0 + p1 * v).astype(np.float32) for v in vals]
-        elif spec.dist_code == UNIFORM:
-            vals = [((p1 - p0) * philox.u01(x) + p0).astype(np.float32) for x in r]
-        else:
-            l0, l1 = np.float32(np.log(p0)), np.float32(np.log(p1))
-            vals = [np.exp(((l1 - l0) * philox.u01(x) + l0).astype(np.float32)).astype(np.float32) for x in r]
-        for j in range(4):
-            col = blk * 4 + j
-            if col < dim:
-                out[:, col] = vals[j]
-    return out
+    r = philox.philox4x32_10(c0, c1, c2, c3, k0, k1)
+    if spec.dist_code == GAUSSIAN:
+        vals = []
+        for a, b in ((r[0], r[1]), (r[2], r[3])):
+            u1 = ((a >> np.uint32(8)).astype(np.float32) + np.float32(1.0)) * np.float32(1.0 / 16777216.0)
+            u2 = philox.u01(b)
+            rad = np.sqrt(np.float32(-2.0) * np.log(u1)).astype(np.float32)
+            ang = (np.float32(6.2831853071795864) * u2).astype(np.float32)
+            vals += [rad * np.cos(ang).astype(np.float32), rad * np.sin(ang).astype(np.float32)]
+        vals = [(p0 + p1 * v).astype(np.float32) for v in vals]
+    elif spec.dist_code == UNIFORM:
+        vals = [((p1 - p0) * philox.u01(x) + p0).astype(np.float32) for x in r]
+    else:
+        l0, l1 = np.float32(np.log(p0)), np.float32(np.log(p1))
+        vals = [np.exp(((l1 - l0) * philox.u01(x) + l0).astype(np.float32)).astype(np.float32) for x in r]
+    out = np.stack(vals, axis=1)[np.arange(k), comp]
+    return out.reshape(len(gid), dim).astype(np.float32)

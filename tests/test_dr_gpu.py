@@ -81,12 +81,14 @@ def test_kernel_reproduces_reference_episode_bit_exact(cuda_lib, name):
 
 @pytest.mark.parametrize("dist,params,op", [("gaussian", (0.1, 0.5), "additive"), ("uniform", (0.9, 1.1), "scaling"),
                                             ("loguniform", (0.5, 2.0), "scaling"), ("normal", (0.0, 0.02), "additive")])
-@pytest.mark.parametrize("n,dim", [(1, 8), (77, 87), (4096, 60), (1000, 21)])
-def test_philox_mode_matches_numpy_restatement(cuda_lib, dist, params, op, n, dim):
-    """In-kernel Philox noise == oracle/dr_oracle.philox_noise fed through the oracle's apply."""
+@pytest.mark.parametrize("n,dim,off", [(1, 8, 100_000), (77, 87, 100_000), (4096, 60, 100_000), (1000, 21, 100_000),
+                                       (333, 87, 3), (130, 21, 1)])
+def test_philox_mode_matches_numpy_restatement(cuda_lib, dist, params, op, n, dim, off):
+    """In-kernel Philox noise == oracle/dr_oracle.philox_noise fed through the oracle's apply.  Offsets 3 and 1 with an
+    odd row length put the shard on a global flat index that is not a multiple of 4: the element-wise path."""
     r_spec = dro.NoiseSpec(op, dist, params)
     i_spec = dro.NoiseSpec(op, dist, params, 2)
-    seed, off = 0x1234_5678_9ABC, 100_000
+    seed = 0x1234_5678_9ABC
     kern = KernelNoise(n, dim, r_spec, i_spec, _lib.DR_STREAM_OBSERVATIONS, seed, off)
     orc = dro.BufferNoise(n, dim, r_spec, i_spec)
     gen = torch.Generator().manual_seed(n * 131 + dim)
@@ -121,6 +123,23 @@ def test_clamps_sit_before_and_after_the_noise(cuda_lib):
     assert torch.equal(out, buf.clamp(-1, 1) + 0.5) and not torch.equal(out, buf)
     kern.apply(cuda_lib, buf, rb, clip_out=1.0, out=out)
     assert torch.equal(out, (buf + 0.5).clamp(-1, 1))
+
+
+def test_unaligned_views_take_the_elementwise_path(cuda_lib):
+    """A buffer view whose base is only 4-byte aligned gives the same result as the aligned tensor."""
+    n, dim = 200, 87
+    spec = dro.NoiseSpec("additive", "gaussian", (0.0, 0.1), 1)
+    a = KernelNoise(n, dim, spec, spec, _lib.DR_STREAM_OBSERVATIONS, seed=5)
+    b = KernelNoise(n, dim, spec, spec, _lib.DR_STREAM_OBSERVATIONS, seed=5)
+    x = torch.randn(n, dim, device=DEV)
+    pad = torch.zeros(n * dim + 1, device=DEV)
+    y = pad[1:].view(n, dim)
+    y.copy_(x)
+    assert y.data_ptr() % 16 != 0
+    rb = (torch.rand(n, device=DEV) < 0.5).long()
+    a.apply(cuda_lib, x, rb, counter=4)
+    b.apply(cuda_lib, y, rb, counter=4)
+    assert torch.equal(x, y) and torch.equal(a.correlated, b.correlated)
 
 
 def test_noise_is_keyed_by_global_env_id(cuda_lib):
