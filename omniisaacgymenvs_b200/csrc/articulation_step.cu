@@ -39,6 +39,9 @@ struct OigeModel {
     int num_dof;
     int num_sensors;
     int tpe_ok;
+    int role_ok;      // K2-R tables valid (>= 2 roles)
+    int nroles;
+    int role_smem;    // dynamic shared memory of the role-split kernel
 };
 
 namespace oige {
@@ -52,8 +55,11 @@ constexpr int kMaxLevels = 16;
 constexpr int kMaxChildren = 4;
 constexpr int kMaxJump = 4;  // 2^4 = 16 >= kMaxLevels
 constexpr int kMaxSlots = 8;
+constexpr long long kRoleMinEnvs = 4096, kRoleMinEnvsSmall = 1024, kRoleMaxEnvs = 32768;  // measured, profiles/r1_k2_modes.txt
 constexpr long long kTpeMinEnvs = 8192;  // measured crossover, see profiles/
 constexpr int kHasHeavy = 1, kIsHead = 2, kFirstLight = 4;
+constexpr int kMaxRoles = 4, kMaxTrunk = 8, kMaxHeads = 8;
+constexpr int kRTip = 1, kRHead = 2, kRTrunk = 4;
 
 struct DevModel {
     int num_links, num_spheres, num_sensors, max_depth;
@@ -73,6 +79,18 @@ struct DevModel {
     int sph_start[32];
     int sph_count[32];
     int sensor_of_link[32];
+    // role-split kernel (K2-R): trunk = root + every link with a branching descendant-or-self; what hangs off the
+    // trunk are plain chains, dealt to `nroles` warps; role 0 also owns the trunk
+    int nroles, ntrunk, nheads, role_ok;
+    int rflags[32];                  // kRTip | kRHead | kRTrunk
+    int trunk_idx[32];               // index among the trunk links (root = 0), else -1
+    int head_slot[32];               // hand-over slot of a chain head, else -1
+    int trunk_link[kMaxTrunk];       // trunk links in increasing index order
+    int th_begin[kMaxTrunk + 4];     // heads attached to trunk link t: th_heads[th_begin[t] .. th_begin[t+1])
+    int th_heads[kMaxHeads];
+    int n1[kMaxRoles], n2[kMaxRoles], sync2[kMaxRoles], sync3[kMaxRoles];
+    int list1[kMaxRoles][32];        // kinematics order: trunk (non-root) + own links, increasing index
+    int list2[kMaxRoles][32];        // inertia order: own chains tip->head, then (role 0) trunk downwards, root last
     float jpos[3][32];
     float jquat[4][32];
     float axis[3][32];
@@ -946,6 +964,8 @@ articulation_step_tpe_kernel(const DevModel* __restrict__ gmodel, const __grid_c
     vv[3] = rvel.a[0]; vv[4] = rvel.a[1]; vv[5] = rvel.a[2];
 }
 
+#include "articulation_role.cuh"  // K2-R: role-split kernel (same device functions)
+
 }  // namespace
 
 // Kernel choice: OIGE_K2_MODE=warp|thread forces one; otherwise thread-per-env from kTpeMinEnvs envs on.
@@ -954,6 +974,15 @@ static bool use_thread_per_env(int64_t n) {
     if (e && e[0] == 'w') return false;
     if (e && e[0] == 't') return true;
     return n >= kTpeMinEnvs;
+}
+
+// Role-split kernel (K2-R): between the warp-per-env kernel's range and the point where one thread per env fills the
+// machine by itself.  OIGE_K2_MODE=role forces it; warp|thread exclude it.
+static bool use_role_split(int64_t n, int num_links) {
+    const char* e = getenv("OIGE_K2_MODE");
+    if (e && e[0] == 'r') return true;
+    if (e && (e[0] == 'w' || e[0] == 't')) return false;
+    return n >= (num_links <= 12 ? kRoleMinEnvsSmall : kRoleMinEnvs) && n <= kRoleMaxEnvs;
 }
 
 // `decision_n`: env count the kernel choice is based on (the whole step's count when the caller
@@ -970,6 +999,29 @@ int k2_step(const OigeModel* model, const OigeTaskParams* P, const OigeState* st
     if (reinterpret_cast<uintptr_t>(A.quat) & 15u) return fail(OIGE_E_ALIGN, "articulation_step: root_quat not 16B aligned");
     if (model->num_sensors > 0 && P->num_sensors != model->num_sensors)
         return fail(OIGE_E_SHAPE, "articulation_step: params.num_sensors %d != model %d", P->num_sensors, model->num_sensors);
+    if (model->role_ok && use_role_split(decision_n > 0 ? decision_n : n, model->num_links)) {
+        const unsigned tb = (unsigned)((n + 31) / 32);
+        const DevModel* dm = reinterpret_cast<const DevModel*>(model->dev_table);
+        const int bs = model->nroles * 32;
+        // One wave with up to two CTAs per SM: 255-register budget (latency schedule); up to four: a budget sized for
+        // the model's warp count.  Decided on the WHOLE step's env count (chunked == one-shot stays bit-identical).
+        const long long dn = decision_n > 0 ? decision_n : n;
+        const char* mb = getenv("OIGE_K2_MINB");
+        const bool roomy = mb ? mb[0] == '2' : (dn + 31) / 32 <= 2ll * sm_count();
+        const int sm = model->role_smem;
+#define OIGE_ROLE_LAUNCH(MAXL)                                                                                  \
+    do {                                                                                                        \
+        if (roomy) articulation_step_role_kernel<MAXL, kMaxRoles, 2><<<tb, bs, sm, stream>>>(dm, *P, A);        \
+        else if (model->nroles == 2) articulation_step_role_kernel<MAXL, 2, 4><<<tb, bs, sm, stream>>>(dm, *P, A); \
+        else if (model->nroles == 3) articulation_step_role_kernel<MAXL, 3, 4><<<tb, bs, sm, stream>>>(dm, *P, A); \
+        else articulation_step_role_kernel<MAXL, 4, 4><<<tb, bs, sm, stream>>>(dm, *P, A);                      \
+    } while (0)
+        if (model->num_links <= 12) OIGE_ROLE_LAUNCH(12);
+        else OIGE_ROLE_LAUNCH(24);
+#undef OIGE_ROLE_LAUNCH
+        count_launch();
+        return check_launch("articulation_step_role_kernel");
+    }
     if (model->tpe_ok && use_thread_per_env(decision_n > 0 ? decision_n : n)) {
         const int bs = 128;
         const unsigned tb = (unsigned)((n + bs - 1) / bs);
@@ -1091,6 +1143,91 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
         }
         if (heavy[0] >= 0) h->tflags[0] |= kHasHeavy;
     }
+    {   // role split (K2-R): trunk = root + ancestors-or-self of every branching link; the rest are chains
+        bool trunk[32] = {false};
+        trunk[0] = true;
+        for (int i = 0; i < L; ++i)
+            if (nchild[i] >= 2)
+                for (int a = i; a > 0 && !trunk[a]; a = h->parent[a]) trunk[a] = true;
+        for (int i = 0; i < 32; ++i) { h->trunk_idx[i] = -1; h->head_slot[i] = -1; h->rflags[i] = 0; }
+        int nt = 0, nh = 0, heads[32], hlen[32], tip[32];
+        bool fits = true;
+        for (int i = 0; i < L; ++i) {
+            if (trunk[i]) {
+                if (nt >= kMaxTrunk) { fits = false; break; }
+                h->trunk_idx[i] = nt; h->trunk_link[nt++] = i; h->rflags[i] |= kRTrunk;
+            } else if (trunk[h->parent[i]]) {
+                if (nh >= kMaxHeads) { fits = false; break; }
+                heads[nh++] = i;
+            }
+        }
+        for (int c = 0; c < nh && fits; ++c) {  // chain below each head (no branching by construction)
+            int len = 1, cur = heads[c];
+            while (nchild[cur] == 1) { cur = h->child[0][cur]; ++len; }
+            hlen[c] = len; tip[c] = cur;
+            h->head_slot[heads[c]] = c; h->rflags[heads[c]] |= kRHead; h->rflags[cur] |= kRTip;
+        }
+        // smallest number of roles that reaches the best critical path (longest-processing-time dealing)
+        int best_r = 1, best_load = 1 << 30, owner[32];
+        int order[32];
+        for (int c = 0; c < nh; ++c) order[c] = c;
+        for (int a = 0; a < nh; ++a)
+            for (int b = a + 1; b < nh; ++b)
+                if (hlen[order[b]] > hlen[order[a]]) { int t = order[a]; order[a] = order[b]; order[b] = t; }
+        for (int r = 1; r <= kMaxRoles && fits; ++r) {
+            int load[kMaxRoles] = {0}, mx = 0;
+            for (int a = 0; a < nh; ++a) {
+                int w = 0;
+                for (int q = 1; q < r; ++q) if (load[q] < load[w]) w = q;
+                load[w] += hlen[order[a]];
+            }
+            for (int q = 0; q < r; ++q) if (load[q] > mx) mx = load[q];
+            if (mx < best_load) { best_load = mx; best_r = r; }
+        }
+        {
+            int load[kMaxRoles] = {0};
+            for (int a = 0; a < nh; ++a) {
+                int w = 0;
+                for (int q = 1; q < best_r; ++q) if (load[q] < load[w]) w = q;
+                load[w] += hlen[order[a]];
+                owner[order[a]] = w;
+            }
+        }
+        h->nroles = best_r; h->ntrunk = nt; h->nheads = nh;
+        h->role_ok = (fits && best_r >= 2 && h->tpe_ok && L <= 24) ? 1 : 0;
+        if (h->role_ok) {
+            for (int t = 0, pos = 0; t <= nt; ++t) {  // heads attached to each trunk link
+                h->th_begin[t] = pos;
+                if (t == nt) break;
+                for (int c = 0; c < nh; ++c)
+                    if (h->parent[heads[c]] == h->trunk_link[t]) h->th_heads[pos++] = c;
+            }
+            for (int r = 0; r < best_r; ++r) {
+                bool mine[32] = {false};
+                int c2 = 0;
+                for (int a = 0; a < nh; ++a) {  // chains in dealing order, each tip -> head
+                    const int c = order[a];
+                    if (owner[c] != r) continue;
+                    for (int cur = tip[c];; cur = h->parent[cur]) {
+                        h->list2[r][c2++] = cur; mine[cur] = true;
+                        if (cur == heads[c]) break;
+                    }
+                }
+                const int nchain = c2;
+                if (r == 0) {
+                    for (int t = nt - 1; t >= 1; --t) h->list2[0][c2++] = h->trunk_link[t];
+                    h->list2[0][c2++] = 0;
+                }
+                h->n2[r] = c2;
+                h->sync2[r] = (r == 0) ? nchain : c2;
+                h->sync3[r] = nchain - 1;  // role 0 without chains: -1 = barrier after the sweep
+                int c1 = 0;
+                for (int i = 1; i < L; ++i)
+                    if (trunk[i] || mine[i]) h->list1[r][c1++] = i;
+                h->n1[r] = c1;
+            }
+        }
+    }
     h->jump_rounds = 0;
     while ((1 << h->jump_rounds) < h->max_depth) ++h->jump_rounds;
     for (int i = 0; i < L; ++i) {
@@ -1132,7 +1269,8 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
     h->k_c = d->contact_stiffness; h->d_c = d->contact_damping; h->mu = d->friction_mu; h->c_visc = d->friction_viscous;
     h->k_lim = d->limit_stiffness; h->d_lim = d->limit_damping; h->max_qd = d->max_joint_velocity; h->ang_damp = d->angular_damping;
 
-    const int tpe_ok = h->tpe_ok;
+    const int tpe_ok = h->tpe_ok, role_ok = h->role_ok, nroles = h->nroles;
+    const int role_smem = (h->nheads * 27 + h->ntrunk * 7 + 1) * 32 * (int)sizeof(float);
     void* dev = nullptr;
     cudaError_t e = cudaMalloc(&dev, sizeof(DevModel));
     if (e == cudaSuccess) e = cudaMemcpy(dev, h, sizeof(DevModel), cudaMemcpyHostToDevice);
@@ -1144,6 +1282,7 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
     }
     OigeModel* m = new OigeModel();
     m->dev_table = dev; m->num_links = L; m->num_dof = L - 1; m->num_sensors = d->num_sensors; m->tpe_ok = tpe_ok;
+    m->role_ok = role_ok; m->nroles = nroles; m->role_smem = role_smem;
     return m;
 }
 

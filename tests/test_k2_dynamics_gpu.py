@@ -16,7 +16,7 @@ pytestmark = pytest.mark.gpu
 DT = 0.0083
 
 
-@pytest.fixture(autouse=True, params=["warp", "thread"])
+@pytest.fixture(autouse=True, params=["warp", "thread", "role"])
 def k2_kernel(request, monkeypatch):
     """Every test runs against BOTH articulation kernels: warp-per-env (lane = link, shuffles) and
     thread-per-env (lane = env, local-memory link arrays).  OIGE_K2_MODE overrides the size-based choice."""
@@ -121,6 +121,10 @@ def test_both_kernels_agree_with_each_other(cuda_lib, monkeypatch):
     b = dh.run_gpu(cuda_lib, model, spec, st, 2, DT)
     assert _err(a["q"], b["q"]) < 5e-5 and _err(a["pos"], b["pos"]) < 5e-5
     assert (np.abs(a["qd"] - b["qd"]) / np.maximum(1.0, np.abs(a["qd"]))).max() < 5e-3
+    monkeypatch.setenv("OIGE_K2_MODE", "role")  # role-split: the thread-per-env sums, trunk / limbs on separate warps
+    c = dh.run_gpu(cuda_lib, model, spec, st, 2, DT)
+    assert _err(c["q"], b["q"]) < 5e-5 and _err(c["pos"], b["pos"]) < 5e-5
+    assert (np.abs(c["qd"] - b["qd"]) / np.maximum(1.0, np.abs(b["qd"]))).max() < 5e-3
 
 
 @pytest.mark.parametrize("robot,n", [("Humanoid", 65536), ("Ant", 262144)])
@@ -143,7 +147,7 @@ def test_full_size_rows_are_independent(cuda_lib, robot, n, monkeypatch):
     a, b = n // 2 - 1000, n // 2 + 1048
     part = dh.run_gpu(cuda_lib, model, spec, {k: np.ascontiguousarray(v[a:b]) for k, v in st.items()}, 2, DT)
     import os
-    same_kernel = (os.environ.get("OIGE_K2_MODE") in ("warp", "thread"))  # forced: slice and whole use one kernel
+    same_kernel = (os.environ.get("OIGE_K2_MODE") in ("warp", "thread", "role"))  # forced: slice and whole use one kernel
     for k in full:
         if same_kernel:
             assert np.array_equal(part[k], full[k][a:b]), k
