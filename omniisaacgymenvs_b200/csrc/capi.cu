@@ -81,13 +81,19 @@ static int check_common(const char* who, const OigeTaskParams* p, const OigeStat
 }
 
 // lazily created per-device copy/compute pipeline of oige_env_step_host_f32
-constexpr int kHostChunks = 4;
+constexpr int kHostChunks = 8;  // streams / events; the chunk count used is host_chunk_count()
 struct HostPipe {
     cudaStream_t streams[kHostChunks];
     cudaEvent_t start, done[kHostChunks];
     cudaEvent_t t0, t[kHostChunks][3];  // OIGE_HOST_TRACE=1: after H2D, after the kernels, after D2H (timing events)
     bool trace, pending;
+    int last_used;
 };
+static int host_chunk_count() {  // OIGE_HOST_CHUNKS=1..8 (default 4, measured: tools/e2e_breakdown.py)
+    const char* e = getenv("OIGE_HOST_CHUNKS");
+    const int v = e ? atoi(e) : 4;
+    return v < 1 ? 1 : (v > kHostChunks ? kHostChunks : v);
+}
 static HostPipe* host_pipe() {
     static HostPipe* pipes[64] = {nullptr};
     int dev = 0;
@@ -240,11 +246,12 @@ int oige_env_step_host_f32(const OigeModel* model, const OigeTaskParams* params,
         else if (zc && zc[0] == '1')
             cudaGetLastError();  // unregistered host memory reports an error on older drivers: clear it
     }
-    int64_t per = ((n_envs + kHostChunks - 1) / kHostChunks + 31) / 32 * 32;  // tile-aligned chunk size
+    const int nchunks = host_chunk_count();
+    int64_t per = ((n_envs + nchunks - 1) / nchunks + 31) / 32 * 32;  // tile-aligned chunk size
     if (n_envs < 4096) per = n_envs;                                           // too small to be worth splitting
     if (hp->trace && hp->pending) {  // diagnostic: timeline of the PREVIOUS call (after it has completed)
-        cudaEventSynchronize(hp->t[kHostChunks - 1][2]);
-        for (int c = 0; c < kHostChunks; ++c) {
+        cudaEventSynchronize(hp->t[hp->last_used - 1][2]);
+        for (int c = 0; c < hp->last_used; ++c) {
             float a = 0, b = 0, d = 0;
             cudaEventElapsedTime(&a, hp->t0, hp->t[c][0]); cudaEventElapsedTime(&b, hp->t0, hp->t[c][1]);
             cudaEventElapsedTime(&d, hp->t0, hp->t[c][2]);
@@ -291,6 +298,7 @@ int oige_env_step_host_f32(const OigeModel* model, const OigeTaskParams* params,
         cudaEventRecord(hp->done[used], s);
         cudaStreamWaitEvent(user, hp->done[used], 0);  // the caller's stream observes the whole step
     }
+    hp->last_used = used;
     e = cudaMemcpyAsync(rew_host, buf->rew, (size_t)n_envs * sizeof(float), cudaMemcpyDeviceToHost, user);
     if (e == cudaSuccess)
         e = cudaMemcpyAsync(reset_host, buf->reset_buf, (size_t)n_envs * sizeof(int64_t), cudaMemcpyDeviceToHost, user);
