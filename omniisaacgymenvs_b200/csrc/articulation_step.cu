@@ -982,7 +982,10 @@ static bool use_role_split(int64_t n, int num_links) {
     const char* e = getenv("OIGE_K2_MODE");
     if (e && e[0] == 'r') return true;
     if (e && (e[0] == 'w' || e[0] == 't')) return false;
-    return n >= (num_links <= 12 ? kRoleMinEnvsSmall : kRoleMinEnvs) && n <= kRoleMaxEnvs;
+    // upper end: the launch must fit in ONE wave at 4 CTAs (of 32 envs) per SM -- 18944 envs on a 148-SM B200; a second
+    // wave doubles the time (Humanoid 16384: 84 us, 20480: 135 us) and K2-T takes over
+    const long long one_wave = 4ll * sm_count() * 32;
+    return n >= (num_links <= 12 ? kRoleMinEnvsSmall : kRoleMinEnvs) && n <= (one_wave < kRoleMaxEnvs ? one_wave : kRoleMaxEnvs);
 }
 
 // `decision_n`: env count the kernel choice is based on (the whole step's count when the caller

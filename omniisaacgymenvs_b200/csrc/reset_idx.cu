@@ -60,19 +60,21 @@ __device__ __forceinline__ void reset_one_env(const OigeTaskParams& P, const K3A
     }
 }
 
+// One CTA (4 warps) per 32 consecutive envs: the action rows are clamped by all 128 threads; every warp ballots the
+// same 32 reset flags and takes every 4th flagged env, so a group with several resets (random policies reset ~4 % of
+// the envs per step) does not serialise them on one warp.
 __global__ void __launch_bounds__(128) reset_masked_kernel(const __grid_constant__ OigeTaskParams P,
                                                            const __grid_constant__ K3Args A) {
-    const int lane = threadIdx.x & 31;
-    const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const long long base = warp * 32;
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const long long base = (long long)blockIdx.x * 32;
     if (base >= A.n) return;
     if (A.actions_in != nullptr) {
         // VecEnvRLGames.step's torch.clamp(actions, -clip, clip) (envs/vec_env_rlgames.py:57) for the 32 envs
-        // of this warp: one contiguous, coalesced chunk of the [N,D] action tensor
+        // of this group: one contiguous, coalesced chunk of the [N,D] action tensor
         const long long cnt = ((A.n - base) < 32 ? (A.n - base) : 32) * A.num_dof;
         const float* in = A.actions_in + base * A.num_dof;
         float* out = A.actions_out + base * A.num_dof;
-        for (long long i = lane; i < cnt; i += 32) {
+        for (long long i = threadIdx.x; i < cnt; i += 128) {
             const float v = in[i];
             out[i] = v < -A.clip ? -A.clip : (v > A.clip ? A.clip : v);
         }
@@ -83,10 +85,12 @@ __global__ void __launch_bounds__(128) reset_masked_kernel(const __grid_constant
     if (m == 0) return;
     K3Args B = A;
     if (A.counter_dev != nullptr) B.counter = *A.counter_dev;
-    while (m) {
+    // every warp must have read the flags before any warp clears one (reset_one_env zeroes reset[env])
+    __syncthreads();
+    for (int k = 0; m; ++k) {
         const int b = __ffs(m) - 1;
         m &= m - 1;
-        reset_one_env(P, B, base + b, base + b, lane);
+        if ((k & 3) == wib) reset_one_env(P, B, base + b, base + b, lane);
     }
 }
 
@@ -124,8 +128,7 @@ int k3_masked(const OigeTaskParams* P, const OigeState* st, const OigeTaskBuffer
     A.counter_dev = actions_in ? reinterpret_cast<const unsigned long long*>(b->reset_counter) : nullptr;
     if (actions_in && !b->actions) return fail(OIGE_E_NULL, "reset: null actions buffer");
     A.seed = seed; A.counter = counter; A.env_id_offset = env_id_offset; A.n = n;
-    const long long warps = (n + 31) / 32;
-    const unsigned blocks = (unsigned)((warps + 3) / 4);
+    const unsigned blocks = (unsigned)((n + 31) / 32);
     reset_masked_kernel<<<blocks, 128, 0, stream>>>(*P, A);
     count_launch();
     return check_launch("reset_masked_kernel");
