@@ -35,6 +35,8 @@ articulation_step_role_kernel(const DevModel* __restrict__ gmodel, const __grid_
         for (int i = threadIdx.x; i < (int)(sizeof(DevModel) / 16); i += blockDim.x) dst[i] = src[i];
     }
     __syncthreads();
+    pdl_wait();     // state / actions are written by the preceding kernel (reset) -- the model table is not
+    pdl_trigger();  // the observation kernel's CTAs may take the SM slots this launch frees as it drains
     const int role = threadIdx.x >> 5, lane = threadIdx.x & 31, nthr = blockDim.x;
     float* xI = dynsm;                                  // [nheads][27][32]
     float* xA = xI + M.nheads * 27 * 32;                // [ntrunk][7][32]: acceleration (6), joint acceleration

@@ -1014,10 +1014,10 @@ int k2_step(const OigeModel* model, const OigeTaskParams* P, const OigeState* st
         const int sm = model->role_smem;
 #define OIGE_ROLE_LAUNCH(MAXL)                                                                                  \
     do {                                                                                                        \
-        if (roomy) articulation_step_role_kernel<MAXL, kMaxRoles, 2><<<tb, bs, sm, stream>>>(dm, *P, A);        \
-        else if (model->nroles == 2) articulation_step_role_kernel<MAXL, 2, 4><<<tb, bs, sm, stream>>>(dm, *P, A); \
-        else if (model->nroles == 3) articulation_step_role_kernel<MAXL, 3, 4><<<tb, bs, sm, stream>>>(dm, *P, A); \
-        else articulation_step_role_kernel<MAXL, 4, 4><<<tb, bs, sm, stream>>>(dm, *P, A);                      \
+        if (roomy) launch_pdl(articulation_step_role_kernel<MAXL, kMaxRoles, 2>, tb, bs, sm, stream, dm, *P, A);        \
+        else if (model->nroles == 2) launch_pdl(articulation_step_role_kernel<MAXL, 2, 4>, tb, bs, sm, stream, dm, *P, A); \
+        else if (model->nroles == 3) launch_pdl(articulation_step_role_kernel<MAXL, 3, 4>, tb, bs, sm, stream, dm, *P, A); \
+        else launch_pdl(articulation_step_role_kernel<MAXL, 4, 4>, tb, bs, sm, stream, dm, *P, A);                      \
     } while (0)
         if (model->num_links <= 12) OIGE_ROLE_LAUNCH(12);
         else OIGE_ROLE_LAUNCH(24);

@@ -36,6 +36,12 @@ int check_launch(const char* what) {
 
 void count_launch(uint64_t n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
+bool pdl_enabled() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("OIGE_PDL"); v = (e && e[0] == '0') ? 0 : 1; }
+    return v != 0;
+}
+
 int sm_count() {
     static int cached = -1;
     if (cached < 0) {

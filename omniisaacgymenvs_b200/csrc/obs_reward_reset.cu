@@ -217,6 +217,7 @@ __global__ void __launch_bounds__(4 * E) obs_reward_reset_kernel(const __grid_co
     }
 
     // ---- stage the tile -------------------------------------------------------------------
+    pdl_wait();  // everything below reads what the articulation kernel wrote
     if (bulk) {
         if (tid == 0) {
             mbar_init(s_bar, 1);
@@ -472,7 +473,7 @@ int launch_k1(const OigeTaskParams& P, const K1Args& A, cudaStream_t stream) {
         configured = true;
     }
     const long long tiles = (A.n + E - 1) / E;
-    kern<<<(unsigned)tiles, 4 * E, smem, stream>>>(P, A);
+    launch_pdl(kern, (unsigned)tiles, 4 * E, smem, stream, P, A);
     count_launch();
     return check_launch("obs_reward_reset_kernel");
 }

@@ -67,6 +67,7 @@ __global__ void __launch_bounds__(128) reset_masked_kernel(const __grid_constant
                                                            const __grid_constant__ K3Args A) {
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const long long base = (long long)blockIdx.x * 32;
+    pdl_trigger();  // the articulation kernel may stage its model table while this one runs
     if (base >= A.n) return;
     if (A.actions_in != nullptr) {
         // VecEnvRLGames.step's torch.clamp(actions, -clip, clip) (envs/vec_env_rlgames.py:57) for the 32 envs

@@ -247,6 +247,38 @@ def test_non_finite_state_is_parked_for_reset(cuda_lib):
     assert g["pos"][0, 2] > 0.0
 
 
+@pytest.mark.parametrize("robot", ["Humanoid", "Ant"])
+@pytest.mark.parametrize("n", [1, 31, 33, 77])
+def test_ragged_env_counts_equal_rows_of_a_full_launch(cuda_lib, robot, n):
+    """Env counts that do not fill a warp / a 32-env CTA: the padded lanes of the last group must neither change the
+    real rows (bit for bit the rows of a 96-env launch) nor write past the end of the tensors."""
+    model, spec = dh.specs(robot)
+    st = dh.random_state(model, 96, 17, height=model.spawn_height * 0.8, tilt=0.2)
+    full = dh.run_gpu(cuda_lib, model, spec, st, 2, DT)
+    part = dh.run_gpu(cuda_lib, model, spec, {k: np.ascontiguousarray(v[:n]) for k, v in st.items()}, 2, DT)
+    for k in full:
+        assert part[k].shape[0] == n and np.array_equal(part[k], full[k][:n]), k
+
+
+def test_non_finite_state_in_a_limb_parks_the_env_in_every_kernel(cuda_lib):
+    """A NaN that only one limb sees (role-split kernel: only one warp of the CTA) must park the WHOLE env: root below
+    the termination height, every joint zeroed, sensors zeroed -- and leave the neighbours alone."""
+    model, spec = dh.specs("Humanoid")
+    st = dh.random_state(model, 64, 9)
+    clean = dh.run_gpu(cuda_lib, model, spec, st, 2, DT)
+    for d in (model.num_dof - 1, 0, model.num_dof // 2):  # last / first / middle dof: different limbs and the trunk
+        bad = {k: v.copy() for k, v in st.items()}
+        bad["qd"][5, d] = np.nan
+        g = dh.run_gpu(cuda_lib, model, spec, bad, 2, DT)
+        for k in g:
+            assert np.isfinite(g[k]).all(), (d, k)
+        assert g["pos"][5, 2] < spec.termination_height, d
+        assert np.all(g["q"][5] == 0.0) and np.all(g["qd"][5] == 0.0), d
+        keep = np.arange(64) != 5
+        for k in g:
+            assert np.array_equal(g[k][keep], clean[k][keep]), (d, k)
+
+
 def test_model_create_rejects_malformed_trees(cuda_lib):
     import ctypes as C
 
