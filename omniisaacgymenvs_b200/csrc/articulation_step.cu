@@ -4,14 +4,17 @@
 // (tasks/shared/locomotion.py:108-114, envs/vec_env_rlgames.py:64-66), i.e. for the PhysX 5 GPU
 // articulation pipeline that cannot be installed here.  See DESIGN.md "K2" for the model.
 //
-// Two kernels integrate the same equations with the same device functions:
+// Three kernels integrate the same equations with the same device functions:
 //   articulation_step_kernel      one WARP per env, lane = link (lane 0 = floating root, one link per
 //                                 DoF); parent<->child exchange by warp shuffles; forward kinematics by
 //                                 pointer jumping; small robots packed several envs per warp.  Lowest
 //                                 latency for few environments.
 //   articulation_step_tpe_kernel  one THREAD per env; per-link intermediates in per-thread local memory,
 //                                 articulated inertias carried up heavy paths in registers.  ~7x fewer
-//                                 issue slots per env: used from 8192 environments on.
+//                                 issue slots per env: used when the launch spans several waves.
+//   articulation_step_role_kernel one CTA per 32 envs, lane = env, warp = ROLE (trunk + limb chains of the tree on
+//                                 separate warps, shared-memory hand-over, named barriers; articulation_role.cuh):
+//                                 about half the dependency chain per warp -- used while the launch fits one wave.
 //
 //   spatial vectors   = (angular xyz, linear xyz) in WORLD-aligned axes about the point O that
 //                       coincides with the root origin at the start of the substep, so that
