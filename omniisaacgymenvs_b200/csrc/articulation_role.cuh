@@ -159,9 +159,16 @@ articulation_step_role_kernel(const DevModel* __restrict__ gmodel, const __grid_
             }
             S6 IA;
             V6 pA;
-            link_inertia_bias(M, i, R, p, v, grav, IA, pA);
-            link_contacts(M, i, R, p, v, b, root_z, dt, IA, pA);
             const int flags = M.rflags[i];
+            if (flags & kRMassless) {  // intermediate link of a multi-dof joint: no inertia, no bias, no contacts
+#pragma unroll
+                for (int j = 0; j < 21; ++j) IA.a[j] = 0.f;
+#pragma unroll
+                for (int j = 0; j < 6; ++j) pA.a[j] = 0.f;
+            } else {
+                link_inertia_bias(M, i, R, p, v, grav, IA, pA);
+                link_contacts(M, i, R, p, v, b, root_z, dt, IA, pA);
+            }
             if (flags & kRTrunk) {
                 const int t = M.trunk_idx[i];
 #pragma unroll

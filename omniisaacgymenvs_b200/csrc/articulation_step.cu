@@ -62,7 +62,7 @@ constexpr long long kRoleMinEnvs = 4096, kRoleMinEnvsSmall = 1024, kRoleMaxEnvs 
 constexpr long long kTpeMinEnvs = 8192;  // measured crossover, see profiles/
 constexpr int kHasHeavy = 1, kIsHead = 2, kFirstLight = 4;
 constexpr int kMaxRoles = 4, kMaxTrunk = 8, kMaxHeads = 8;
-constexpr int kRTip = 1, kRHead = 2, kRTrunk = 4;
+constexpr int kRTip = 1, kRHead = 2, kRTrunk = 4, kRMassless = 8;
 
 struct DevModel {
     int num_links, num_spheres, num_sensors, max_depth;
@@ -1245,6 +1245,13 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
         h->drive_kp[i] = d->drive_stiffness[i]; h->drive_kd[i] = d->drive_damping[i]; h->drive_fmax[i] = d->drive_max_force[i];
     }
     h->jquat[0][0] = 1.f;
+    for (int i = 1; i < L; ++i) {  // K2-R skips the own-inertia work of massless, sphere-less links
+        bool zero = d->mass[i] == 0.f;
+        for (int k = 0; k < 6; ++k) zero = zero && d->inertia[i][k] == 0.f;
+        for (int s = 0; s < d->num_spheres; ++s) zero = zero && d->sphere_link[s] != i;
+        for (int s = 0; s < d->num_sensors; ++s) zero = zero && d->sensor_link[s] != i;
+        if (zero) h->rflags[i] |= kRMassless;
+    }
     // spheres sorted by link (stable)
     int pos = 0;
     for (int i = 0; i < L; ++i) {
