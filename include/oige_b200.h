@@ -174,6 +174,9 @@ int oige_abi_version(void);
 const char* oige_last_error(void);
 /* number of kernels this library has launched since load (monotonic; for bench.py's gpu_launches) */
 uint64_t oige_kernel_launch_count(void);
+/* Diagnostic: with OIGE_HOST_TRACE=1 in the environment, prints the per-chunk timeline (H2D / kernels / D2H done, us)
+ * of the last oige_env_step_host_f32 call -- or CUDA-graph replay of it -- to stderr.  No reference counterpart. */
+int oige_host_trace_dump(void);
 
 /* ---- K1: fused observation / reward / termination pass ----
  * Replaces, in one launch: RLTask.post_physics_step's `progress_buf += 1` (rl_task.py:242),

@@ -122,7 +122,7 @@ class OigeNoiseState(C.Structure):
 
 # every symbol include/oige_b200.h declares (tests/test_capi_symbols.py checks the .so exports them)
 EXPORTED_SYMBOLS = [
-    "oige_abi_version", "oige_last_error", "oige_kernel_launch_count",
+    "oige_abi_version", "oige_last_error", "oige_kernel_launch_count", "oige_host_trace_dump",
     "oige_obs_reward_reset_f32", "oige_obs_reward_reset_tile_f32",
     "oige_reset_masked_f32", "oige_reset_idx_f32",
     "oige_model_create", "oige_model_destroy", "oige_articulation_step_f32",

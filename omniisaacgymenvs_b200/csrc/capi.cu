@@ -255,7 +255,9 @@ int oige_env_step_host_f32(const OigeModel* model, const OigeTaskParams* params,
     const int nchunks = host_chunk_count();
     int64_t per = ((n_envs + nchunks - 1) / nchunks + 31) / 32 * 32;  // tile-aligned chunk size
     if (n_envs < 4096) per = n_envs;                                           // too small to be worth splitting
-    if (hp->trace && hp->pending) {  // diagnostic: timeline of the PREVIOUS call (after it has completed)
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    cudaStreamIsCapturing(user, &cap);
+    if (hp->trace && hp->pending && cap == cudaStreamCaptureStatusNone) {  // diagnostic: timeline of the PREVIOUS call
         cudaEventSynchronize(hp->t[hp->last_used - 1][2]);
         for (int c = 0; c < hp->last_used; ++c) {
             float a = 0, b = 0, d = 0;
@@ -314,6 +316,22 @@ int oige_env_step_host_f32(const OigeModel* model, const OigeTaskParams* params,
         count_launch();
         return check_launch("bump_counter_kernel");
     }
+    return OIGE_OK;
+}
+
+// Diagnostic (OIGE_HOST_TRACE=1): timeline of the last completed oige_env_step_host_f32 call or graph replay of it.
+int oige_host_trace_dump(void) {
+    HostPipe* hp = host_pipe();
+    if (!hp || !hp->trace || hp->last_used <= 0) return fail(OIGE_E_RANGE, "oige_host_trace_dump: no trace (set OIGE_HOST_TRACE=1)");
+    if (cudaEventSynchronize(hp->t[hp->last_used - 1][2]) != cudaSuccess) { cudaGetLastError(); return fail(OIGE_E_RANGE, "trace events not recorded"); }
+    for (int c = 0; c < hp->last_used; ++c) {
+        float a = 0, b = 0, d = 0;
+        cudaEventElapsedTime(&a, hp->t0, hp->t[c][0]); cudaEventElapsedTime(&b, hp->t0, hp->t[c][1]);
+        cudaEventElapsedTime(&d, hp->t0, hp->t[c][2]);
+        fprintf(stderr, "[oige host step] chunk %d: H2D done %.1f us, kernels done %.1f us, D2H done %.1f us\n", c,
+                a * 1e3f, b * 1e3f, d * 1e3f);
+    }
+    cudaGetLastError();
     return OIGE_OK;
 }
 
