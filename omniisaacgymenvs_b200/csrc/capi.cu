@@ -243,14 +243,23 @@ int oige_env_step_host_f32(const OigeModel* model, const OigeTaskParams* params,
     // stores its observation tiles straight into it over PCIe (bulk shared->global stores) instead of a D2H copy per
     // chunk; buf->obs on the device is then NOT written by this call.  Measured 272 vs 284 us per 16384-env step.
     float* obs_host_dev = nullptr;
+    const float* actions_host_dev = nullptr;
     {
         const char* zc = getenv("OIGE_HOST_ZEROCOPY");
         cudaPointerAttributes at;
-        if (zc && zc[0] == '1' && cudaPointerGetAttributes(&at, obs_host) == cudaSuccess &&
+        const int zmode = zc ? atoi(zc) : 0;  // bit 0: observations written straight to the host, bit 1: actions read from it
+        if ((zmode & 1) && cudaPointerGetAttributes(&at, obs_host) == cudaSuccess &&
             at.type == cudaMemoryTypeHost && at.devicePointer != nullptr)
             obs_host_dev = static_cast<float*>(at.devicePointer);
-        else if (zc && zc[0] == '1')
+        else if (zmode & 1)
             cudaGetLastError();  // unregistered host memory reports an error on older drivers: clear it
+        // zero-copy actions: K3's clamp pass reads the pinned host rows over PCIe (coalesced) and writes the clamped
+        // copy to HBM -- no H2D copy-engine transfer, no staging buffer, one stream operation less per chunk
+        if ((zmode & 2) && cudaPointerGetAttributes(&at, actions_host) == cudaSuccess &&
+            at.type == cudaMemoryTypeHost && at.devicePointer != nullptr)
+            actions_host_dev = static_cast<const float*>(at.devicePointer);
+        else if (zmode & 2)
+            cudaGetLastError();
     }
     const int nchunks = host_chunk_count();
     int64_t per = ((n_envs + nchunks - 1) / nchunks + 31) / 32 * 32;  // tile-aligned chunk size
@@ -288,9 +297,14 @@ int oige_env_step_host_f32(const OigeModel* model, const OigeTaskParams* params,
         // captured in a CUDA graph) -- the device scalar, which K3 only reads; it is bumped once after the last chunk
         OigeResetInit in = *init;
         in.initial_root_pos += off * 3; in.initial_root_rot += off * 4; in.initial_dof_pos += off * D;
-        float* stage = actions_dev_staging + off * D;
-        e = cudaMemcpyAsync(stage, actions_host + off * D, (size_t)cnt * D * sizeof(float), cudaMemcpyHostToDevice, s);
-        if (e != cudaSuccess) return fail((int)e, "H2D actions: %s", cudaGetErrorString(e));
+        const float* stage = actions_dev_staging + off * D;
+        if (actions_host_dev) {
+            stage = actions_host_dev + off * D;
+        } else {
+            e = cudaMemcpyAsync(actions_dev_staging + off * D, actions_host + off * D, (size_t)cnt * D * sizeof(float),
+                                cudaMemcpyHostToDevice, s);
+            if (e != cudaSuccess) return fail((int)e, "H2D actions: %s", cudaGetErrorString(e));
+        }
         if (hp->trace) cudaEventRecord(hp->t[used][0], s);
         if (int rc = env_step_impl(model, params, &st, &bf, &in, stage, clip_actions, seed, counter,
                                    env_id_offset + off, cnt, substeps, dt, (void*)s, n_envs))
