@@ -58,7 +58,7 @@ constexpr int kMaxLevels = 16;
 constexpr int kMaxChildren = 4;
 constexpr int kMaxJump = 4;  // 2^4 = 16 >= kMaxLevels
 constexpr int kMaxSlots = 8;
-constexpr long long kRoleMinEnvs = 4096, kRoleMinEnvsSmall = 1024, kRoleMaxEnvs = 32768;  // measured, profiles/r1_k2_modes.txt
+constexpr long long kRoleMinEnvs = 4096, kRoleMinEnvsSmall = 1024;  // measured, profiles/r1_k2_modes.txt
 constexpr long long kTpeMinEnvs = 8192;  // measured crossover, see profiles/
 constexpr int kHasHeavy = 1, kIsHead = 2, kFirstLight = 4;
 constexpr int kMaxRoles = 4, kMaxTrunk = 8, kMaxHeads = 8;
@@ -985,10 +985,11 @@ static bool use_role_split(int64_t n, int num_links) {
     const char* e = getenv("OIGE_K2_MODE");
     if (e && e[0] == 'r') return true;
     if (e && (e[0] == 'w' || e[0] == 't')) return false;
-    // upper end: the launch must fit in ONE wave at 4 CTAs (of 32 envs) per SM -- 18944 envs on a 148-SM B200; a second
-    // wave doubles the time (Humanoid 16384: 84 us, 20480: 135 us) and K2-T takes over
-    const long long one_wave = 4ll * sm_count() * 32;
-    return n >= (num_links <= 12 ? kRoleMinEnvsSmall : kRoleMinEnvs) && n <= (one_wave < kRoleMaxEnvs ? one_wave : kRoleMaxEnvs);
+    // upper end: TWO waves at 4 CTAs (of 32 envs) per SM -- 37888 envs on a 148-SM B200.  Humanoid, K2-R vs K2-T:
+    // 16384: 82 vs 110 us, 20480 (2nd wave starts): 132 vs 136, 36864: 152 vs 183, 40960 (3rd wave): 202 vs 210,
+    // 57344: 253 vs 241 -> K2-T from there (profiles/r1_k2_modes.txt)
+    const long long two_waves = 2ll * 4ll * sm_count() * 32;
+    return n >= (num_links <= 12 ? kRoleMinEnvsSmall : kRoleMinEnvs) && n <= two_waves;
 }
 
 // `decision_n`: env count the kernel choice is based on (the whole step's count when the caller
