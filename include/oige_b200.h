@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define OIGE_ABI_VERSION 1
+#define OIGE_ABI_VERSION 2
 #define OIGE_MAX_DOF 32      /* one lane per link in the articulation kernel */
 #define OIGE_MAX_LINKS 32
 #define OIGE_MAX_SPHERES 48  /* collision spheres per robot */
@@ -113,9 +113,11 @@ typedef struct OigeTaskBuffers {
     float* heading_vec;      /* [N,3] out */
     float* actions;          /* [N,D] the task's stored (clamped) actions */
     double* episode_stats;   /* [OIGE_STATS_SLOTS,4] accumulators or NULL: sum(rew), #done, sum(len at done), #env-steps */
-    uint64_t* reset_counter; /* NULL, or a device scalar: oige_env_step_f32 then takes the Philox reset counter from
-                                it (instead of its `counter` argument) and increments it at the end of the step, so
-                                that the step can be captured once in a CUDA graph and replayed */
+    uint64_t* reset_counter; /* NULL, or TWO device words {counter, 0}: oige_env_step_f32 then takes the Philox reset
+                                counter from word 0 (instead of its `counter` argument) and increments it at the end of
+                                the step, so that the step can be captured once in a CUDA graph and replayed; word 1 is
+                                scratch of the single-launch step (its CTAs take a ticket there: the last one to finish
+                                advances the counter) and must be zero between steps */
 } OigeTaskBuffers;
 
 /* Per-env initial state captured at post_reset (locomotion.py:148-150). */
@@ -174,6 +176,14 @@ int oige_abi_version(void);
 const char* oige_last_error(void);
 /* number of kernels this library has launched since load (monotonic; for bench.py's gpu_launches) */
 uint64_t oige_kernel_launch_count(void);
+/* The OIGE_* environment knobs are read ONCE, at the first call that needs them; this re-reads
+ * them (the test-suite switches the articulation kernel between tests).  No reference counterpart. */
+void oige_reload_env(void);
+/* Environments the articulation kernels parked below the termination height because their state became non-finite
+ * (solver divergence), summed over the current device since the library was loaded.  A healthy run reports 0; a
+ * parked env is indistinguishable from a fall in reset_buf / rew_buf, so episode statistics should be read next to
+ * this counter.  Synchronises the device (diagnostic).  No reference counterpart. */
+uint64_t oige_nonfinite_env_count(void);
 /* Diagnostic: with OIGE_HOST_TRACE=1 in the environment, prints the per-chunk timeline (H2D / kernels / D2H done, us)
  * of the last oige_env_step_host_f32 call -- or CUDA-graph replay of it -- to stderr.  No reference counterpart. */
 int oige_host_trace_dump(void);
@@ -216,10 +226,14 @@ void oige_model_destroy(OigeModel* model);
 int oige_articulation_step_f32(const OigeModel* model, const OigeTaskParams* params, const OigeState* state,
                                const float* actions, int64_t n_envs, int32_t substeps, float dt, void* stream);
 
-/* ---- whole VecEnvRLGames.step on device buffers (K3 -> K2 -> K1) ----
- * Replaces VecEnvRLGames.step (envs/vec_env_rlgames.py:56-78) minus the rl_device copies:
- * clamps `actions_in` to +-clip_actions into buf->actions (inside the reset kernel), then masked reset,
- * articulation step, fused obs/reward/reset: three launches, no host synchronisation. */
+/* ---- whole VecEnvRLGames.step on device buffers ----
+ * Replaces VecEnvRLGames.step (envs/vec_env_rlgames.py:56-78) minus the rl_device copies: clamps `actions_in` to
+ * +-clip_actions into buf->actions, masked reset_idx of the flagged envs (tasks/shared/locomotion.py:103-145),
+ * `substeps` articulation substeps, progress += 1 / observations / reward / done (tasks/base/rl_task.py:242,
+ * locomotion.py:190-321).  No host synchronisation.  ONE launch (K2-F, env_step_role_kernel: prologue + substeps +
+ * epilogue in the role-split articulation kernel) whenever that kernel serves the model and env count -- Humanoid
+ * from 4096 envs, Ant from 1024; three launches (K3 -> K2-W / K2-T -> K1) otherwise.  Both paths produce the same
+ * bits as calling the three entry points above one after the other. */
 int oige_env_step_f32(const OigeModel* model, const OigeTaskParams* params, const OigeState* state,
                       const OigeTaskBuffers* buf, const OigeResetInit* init, const float* actions_in,
                       float clip_actions, uint64_t seed, uint64_t counter, int64_t env_id_offset,

@@ -17,6 +17,7 @@ MAX_LINKS = 32
 MAX_SPHERES = 48
 MAX_SENSORS = 4
 STATS_SLOTS = 2048
+ABI_VERSION = 2
 LIMIT_COST_HUMANOID = 0
 LIMIT_COST_ANT = 1
 
@@ -123,6 +124,7 @@ class OigeNoiseState(C.Structure):
 # every symbol include/oige_b200.h declares (tests/test_capi_symbols.py checks the .so exports them)
 EXPORTED_SYMBOLS = [
     "oige_abi_version", "oige_last_error", "oige_kernel_launch_count", "oige_host_trace_dump",
+    "oige_reload_env", "oige_nonfinite_env_count",
     "oige_obs_reward_reset_f32", "oige_obs_reward_reset_tile_f32",
     "oige_reset_masked_f32", "oige_reset_idx_f32",
     "oige_model_create", "oige_model_destroy", "oige_articulation_step_f32",
@@ -152,6 +154,8 @@ def load() -> C.CDLL:
     lib.oige_abi_version.restype = C.c_int
     lib.oige_last_error.restype = C.c_char_p
     lib.oige_kernel_launch_count.restype = u64
+    lib.oige_nonfinite_env_count.restype = u64
+    lib.oige_reload_env.restype = None
     lib.oige_obs_reward_reset_f32.argtypes = [P(OigeTaskParams), P(OigeState), P(OigeTaskBuffers), i64, vp]
     lib.oige_obs_reward_reset_tile_f32.argtypes = [P(OigeTaskParams), P(OigeState), P(OigeTaskBuffers), i64, i32, vp]
     lib.oige_reset_masked_f32.argtypes = [P(OigeTaskParams), P(OigeState), P(OigeTaskBuffers), P(OigeResetInit),
@@ -191,8 +195,8 @@ def load() -> C.CDLL:
                  "oige_cartpole_obs_reward_reset_f32", "oige_cartpole_reset_masked_f32",
                  "oige_cartpole_reset_idx_f32", "oige_cartpole_env_step_f32"):
         getattr(lib, name).restype = C.c_int
-    if lib.oige_abi_version() != 1:
-        raise RuntimeError(f"liboige_b200.so ABI version {lib.oige_abi_version()} != 1: rebuild the library")
+    if lib.oige_abi_version() != ABI_VERSION:
+        raise RuntimeError(f"liboige_b200.so ABI version {lib.oige_abi_version()} != {ABI_VERSION}: rebuild the library")
     _lib = lib
     return lib
 
@@ -205,6 +209,16 @@ def check(rc: int, what: str) -> None:
 
 def launch_count() -> int:
     return int(load().oige_kernel_launch_count())
+
+
+def reload_env() -> None:
+    """Re-reads the OIGE_* environment knobs (the library reads them once, at first use)."""
+    load().oige_reload_env()
+
+
+def nonfinite_env_count() -> int:
+    """Envs parked by the articulation kernels' non-finite guard on the current device since load (0 when healthy)."""
+    return int(load().oige_nonfinite_env_count())
 
 
 def current_stream_ptr(device=None) -> int:

@@ -12,9 +12,10 @@
 //   articulation_step_tpe_kernel  one THREAD per env; per-link intermediates in per-thread local memory,
 //                                 articulated inertias carried up heavy paths in registers.  ~7x fewer
 //                                 issue slots per env: used when the launch spans several waves.
-//   articulation_step_role_kernel one CTA per 32 envs, lane = env, warp = ROLE (trunk + limb chains of the tree on
-//                                 separate warps, shared-memory hand-over, named barriers; articulation_role.cuh):
-//                                 about half the dependency chain per warp -- used while the launch fits one wave.
+//   env_step_role_kernel          K2-F: lane = env, warp = ROLE (trunk + limb chains of the tree on separate warps),
+//                                 every per-link intermediate in shared memory, and the WHOLE env step in the launch:
+//                                 action clamp + masked reset before, observations / reward / termination after the
+//                                 substeps (env_step_role.cuh).  The default from a few thousand envs on.
 //
 //   spatial vectors   = (angular xyz, linear xyz) in WORLD-aligned axes about the point O that
 //                       coincides with the root origin at the start of the substep, so that
@@ -34,17 +35,22 @@
 #include <math.h>
 #include <stdlib.h>
 
+#include <atomic>
+#include <mutex>
+
+#include "locomotion_math.cuh"
 #include "oige_common.cuh"
 
 struct OigeModel {
     void* dev_table;      // DevModel in device memory
+    void* dev_role;       // RoleModel in device memory (K2-F) or null
     int num_links;
     int num_dof;
     int num_sensors;
     int tpe_ok;
-    int role_ok;      // K2-R tables valid (>= 2 roles)
-    int nroles;
-    int role_smem;    // dynamic shared memory of the role-split kernel
+    int role_ok;          // K2-F applicable: trunk is a path, (roles, chain links per role) is an instantiated combination
+    int nroles, maxc;     // roles per 32-env group; link slots per role the kernel is instantiated for (3 or 6)
+    int group_floats;     // shared-memory floats (x32 lanes) of one group's scratch
 };
 
 namespace oige {
@@ -61,8 +67,7 @@ constexpr int kMaxSlots = 8;
 constexpr long long kRoleMinEnvs = 4096, kRoleMinEnvsSmall = 1024;  // measured, profiles/r1_k2_modes.txt
 constexpr long long kTpeMinEnvs = 8192;  // measured crossover, see profiles/
 constexpr int kHasHeavy = 1, kIsHead = 2, kFirstLight = 4;
-constexpr int kMaxRoles = 4, kMaxTrunk = 8, kMaxHeads = 8;
-constexpr int kRTip = 1, kRHead = 2, kRTrunk = 4, kRMassless = 8;
+constexpr int kMaxRoles = 4;
 
 struct DevModel {
     int num_links, num_spheres, num_sensors, max_depth;
@@ -82,18 +87,6 @@ struct DevModel {
     int sph_start[32];
     int sph_count[32];
     int sensor_of_link[32];
-    // role-split kernel (K2-R): trunk = root + every link with a branching descendant-or-self; what hangs off the
-    // trunk are plain chains, dealt to `nroles` warps; role 0 also owns the trunk
-    int nroles, ntrunk, nheads, role_ok;
-    int rflags[32];                  // kRTip | kRHead | kRTrunk
-    int trunk_idx[32];               // index among the trunk links (root = 0), else -1
-    int head_slot[32];               // hand-over slot of a chain head, else -1
-    int trunk_link[kMaxTrunk];       // trunk links in increasing index order
-    int th_begin[kMaxTrunk + 4];     // heads attached to trunk link t: th_heads[th_begin[t] .. th_begin[t+1])
-    int th_heads[kMaxHeads];
-    int n1[kMaxRoles], n2[kMaxRoles], sync2[kMaxRoles], sync3[kMaxRoles];
-    int list1[kMaxRoles][32];        // kinematics order: trunk (non-root) + own links, increasing index
-    int list2[kMaxRoles][32];        // inertia order: own chains tip->head, then (role 0) trunk downwards, root last
     float jpos[3][32];
     float jquat[4][32];
     float axis[3][32];
@@ -195,7 +188,8 @@ struct Contact {
     V3 F0;   // force at the current state incl. the velocity-product correction C*(P b)
     V3 C;    // dt * G (diagonal: tangential, tangential, normal)
 };
-__device__ __forceinline__ bool contact_eval(const DevModel& M, int s, const M3& R, V3 p, const V6& v, const V6& b,
+template <class MT>
+__device__ __forceinline__ bool contact_eval(const MT& M, int s, const M3& R, V3 p, const V6& v, const V6& b,
                                              float root_z, float dt, Contact& c) {
     const V3 local = {M.sph_pos[0][s], M.sph_pos[1][s], M.sph_pos[2][s]};
     const float rad = M.sph_r[s];
@@ -229,7 +223,8 @@ struct K2Args {
 
 // World-frame spatial inertia of link i about O (symmetric 6x6) and its bias force
 // p = v x* (I v) - gravity wrench.  R, p: link frame in the O-frame; v: spatial velocity.
-__device__ __forceinline__ void link_inertia_bias(const DevModel& M, int li, const M3& R, V3 p, const V6& v, V3 grav,
+template <class MT>
+__device__ __forceinline__ void link_inertia_bias(const MT& M, int li, const M3& R, V3 p, const V6& v, V3 grav,
                                                   S6& IA, V6& pA) {
     const float m = M.mass[li];
     const V3 cl = {M.com[0][li], M.com[1][li], M.com[2][li]};
@@ -273,7 +268,8 @@ __device__ __forceinline__ void link_inertia_bias(const DevModel& M, int li, con
 
 // Adds the linearly-implicit ground contacts of link li: P^T C P to the inertia, -wrench(F0) to the bias.
 // `nloop` = loop bound (uniform across a warp-per-env warp: the model's max spheres per link).
-__device__ __forceinline__ void link_contacts(const DevModel& M, int li, const M3& R, V3 p, const V6& v, const V6& b,
+template <class MT>
+__device__ __forceinline__ void link_contacts(const MT& M, int li, const M3& R, V3 p, const V6& v, const V6& b,
                                               float root_z, float dt, S6& IA, V6& pA, int nloop = -1) {
     const int s0 = M.sph_start[li];
     const int sc = M.sph_count[li];
@@ -303,7 +299,8 @@ __device__ __forceinline__ void link_contacts(const DevModel& M, int li, const M
 
 // Joint-space force at the end-of-step position (actuation + passive spring/damper + limit penalty)
 // and the implicit diagonal term armature + dt D + dt^2 K.
-__device__ __forceinline__ void joint_force(const DevModel& M, int li, float q, float qd, float effort, float dt,
+template <class MT>
+__device__ __forceinline__ void joint_force(const MT& M, int li, float q, float qd, float effort, float dt,
                                             bool has_target, float target, float& tau0, float& dextra) {
     const float Ks = M.stiffness[li], Dj = M.damping[li];
     const float qn = fmaf(dt, qd, q);  // position the springs see at the end of the step
@@ -373,7 +370,8 @@ __device__ __forceinline__ void chol6_solve(const S6& IA, const V6& pA, V6& a) {
 }
 
 // Net ground wrench on link li (force, torque about the link origin) in the link frame -> out[6].
-__device__ __forceinline__ void sensor_wrench(const DevModel& M, int li, const M3& R, V3 p, const V6& v, const V6& b,
+template <class MT>
+__device__ __forceinline__ void sensor_wrench(const MT& M, int li, const M3& R, V3 p, const V6& v, const V6& b,
                                               const V6& a, float root_z, float dt, float* out) {
     V3 F = {0.f, 0.f, 0.f}, Tq = {0.f, 0.f, 0.f};
     const int s0 = M.sph_start[li], sc = M.sph_count[li];
@@ -391,7 +389,8 @@ __device__ __forceinline__ void sensor_wrench(const DevModel& M, int li, const M
 }
 
 // Semi-implicit Euler for the floating root (exponential map for the quaternion).
-__device__ __forceinline__ void integrate_root(const DevModel& M, const V6& a, float dt, V3& rpos, Q4& rquat, V6& rvel) {
+template <class MT>
+__device__ __forceinline__ void integrate_root(const MT& M, const V6& a, float dt, V3& rpos, Q4& rquat, V6& rvel) {
     const V3 w0 = ang(rvel), v0 = lin(rvel);
     const V3 vdot = lin(a) + cross(w0, v0);  // classical acceleration of the root origin
     float damp = 1.f - dt * M.ang_damp;
@@ -967,29 +966,151 @@ articulation_step_tpe_kernel(const DevModel* __restrict__ gmodel, const __grid_c
     vv[3] = rvel.a[0]; vv[4] = rvel.a[1]; vv[5] = rvel.a[2];
 }
 
-#include "articulation_role.cuh"  // K2-R: role-split kernel (same device functions)
+#include "env_step_role.cuh"  // K2-F: role-split whole-step kernel (same device functions)
 
 }  // namespace
 
+// ---- run-time knobs (OIGE_K2_MODE, OIGE_K2_MINB, OIGE_K2_EPC): read ONCE, at the first use; oige_reload_env()
+// re-reads them (the test-suite switches kernels between tests) ------------------------------------------------
+struct K2Knobs {
+    int mode;   // 0 auto, 'w' warp-per-env, 't' thread-per-env, 'r' role split
+    int minb;   // 0 auto, 2, 4: register-budget variant of K2-T
+    int epc;    // 0 auto, 32, 128: envs per CTA of K2-F
+};
+static K2Knobs g_knobs = {0, 0, 0};
+static std::once_flag g_knobs_once;
+static void read_knobs() {
+    K2Knobs k = {0, 0, 0};
+    const char* e = getenv("OIGE_K2_MODE");
+    if (e && (e[0] == 'w' || e[0] == 't' || e[0] == 'r')) k.mode = e[0];
+    const char* mb = getenv("OIGE_K2_MINB");
+    if (mb && (mb[0] == '2' || mb[0] == '4')) k.minb = mb[0] - '0';
+    const char* ep = getenv("OIGE_K2_EPC");
+    if (ep) { const int v = atoi(ep); if (v == 32 || v == 128) k.epc = v; }
+    g_knobs = k;
+}
+static const K2Knobs& knobs() {
+    std::call_once(g_knobs_once, read_knobs);
+    return g_knobs;
+}
+void k2_reload_env() { knobs(); read_knobs(); }
+
 // Kernel choice: OIGE_K2_MODE=warp|thread forces one; otherwise thread-per-env from kTpeMinEnvs envs on.
 static bool use_thread_per_env(int64_t n) {
-    const char* e = getenv("OIGE_K2_MODE");  // read per call so tests can switch it
-    if (e && e[0] == 'w') return false;
-    if (e && e[0] == 't') return true;
+    const int m = knobs().mode;
+    if (m == 'w') return false;
+    if (m == 't') return true;
     return n >= kTpeMinEnvs;
 }
 
-// Role-split kernel (K2-R): between the warp-per-env kernel's range and the point where one thread per env fills the
-// machine by itself.  OIGE_K2_MODE=role forces it; warp|thread exclude it.
+// Role-split kernel (K2-F): from the point where the warp-per-env kernel runs out of issue slots.  OIGE_K2_MODE=role
+// forces it; warp|thread exclude it.
 static bool use_role_split(int64_t n, int num_links) {
-    const char* e = getenv("OIGE_K2_MODE");
-    if (e && e[0] == 'r') return true;
-    if (e && (e[0] == 'w' || e[0] == 't')) return false;
-    // upper end: TWO waves at 4 CTAs (of 32 envs) per SM -- 37888 envs on a 148-SM B200.  Humanoid, K2-R vs K2-T:
-    // 16384: 82 vs 110 us, 20480 (2nd wave starts): 132 vs 136, 36864: 152 vs 183, 40960 (3rd wave): 202 vs 210,
-    // 57344: 253 vs 241 -> K2-T from there (profiles/r1_k2_modes.txt)
-    const long long two_waves = 2ll * 4ll * sm_count() * 32;
-    return n >= (num_links <= 12 ? kRoleMinEnvsSmall : kRoleMinEnvs) && n <= two_waves;
+    const int m = knobs().mode;
+    if (m == 'r') return true;
+    if (m == 'w' || m == 't') return false;
+    return n >= (num_links <= 12 ? kRoleMinEnvsSmall : kRoleMinEnvs);
+}
+
+bool k2_uses_role_kernel(const OigeModel* model, int64_t decision_n) {
+    return model->role_ok && use_role_split(decision_n, model->num_links);
+}
+
+namespace {
+
+// dynamic shared memory of one K2-F CTA: the groups' scratch, aliased by the input tile and by the output tile
+size_t role_smem_bytes(const OigeModel* model, int epc, int D, int S) {
+    const int OBS = 12 + 3 * D + 6 * S;
+    const size_t scratch = (size_t)(epc / 32) * model->group_floats * 32;
+    const size_t tile_in = (size_t)epc * (3 * D + 13);
+    const size_t tile_out = (size_t)epc * (2 * D + 6 * S + 13) + (size_t)epc * (D + OBS + 6 + 1 + 12) + 128;
+    size_t fl = scratch > tile_in ? scratch : tile_in;
+    if (tile_out > fl) fl = tile_out;
+    return fl * sizeof(float);
+}
+
+template <typename K>
+int role_launch(K kern, int variant, int nthreads, int epc, const OigeModel* model, const OigeTaskParams* P,
+                const FArgs& A, cudaStream_t stream) {
+    static std::atomic<int> configured[8][64];  // [variant][device]: max dynamic smem the kernel was configured for
+    const size_t smem = role_smem_bytes(model, epc, A.D, A.S);
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) dev = 0;
+    if ((size_t)configured[variant][dev].load(std::memory_order_acquire) < smem) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return fail((int)e, "cudaFuncSetAttribute(env_step_role_kernel, %zu B): %s", smem, cudaGetErrorString(e));
+        configured[variant][dev].store((int)smem, std::memory_order_release);
+    }
+    const unsigned grid = (unsigned)((A.n + epc - 1) / epc);
+    launch_pdl(kern, grid, (unsigned)nthreads, smem, stream, reinterpret_cast<const RoleModel*>(model->dev_role), *P, A);
+    count_launch();
+    return check_launch("env_step_role_kernel");
+}
+
+// `dn`: env count of the whole step (chunked callers), decides the CTA shape so that chunks == one shot bit for bit
+int role_dispatch(const OigeModel* model, const OigeTaskParams* P, const FArgs& A, cudaStream_t stream, int64_t dn) {
+    const bool tgt = A.targets != nullptr;
+    if (model->nroles == 3 && model->maxc == 6 && !tgt) {
+        // up to three 32-env CTAs per SM fit in shared memory; beyond that one 128-env CTA per SM (the model table is
+        // staged once per CTA, and four groups is what one wave of 16384 envs needs on 148 SMs)
+        const int force = knobs().epc;
+        const bool big = force ? force == 128 : (dn + 31) / 32 > 3ll * sm_count();
+        if (big) return role_launch(env_step_role_kernel<6, 3, false, 128, 1>, 0, 3 * 128, 128, model, P, A, stream);
+        return role_launch(env_step_role_kernel<6, 3, false, 32, 3>, 1, 3 * 32, 32, model, P, A, stream);
+    }
+    if (model->nroles == 4 && model->maxc == 3) {
+        if (tgt) return role_launch(env_step_role_kernel<3, 4, true, 32, 4>, 2, 4 * 32, 32, model, P, A, stream);
+        return role_launch(env_step_role_kernel<3, 4, false, 32, 4>, 3, 4 * 32, 32, model, P, A, stream);
+    }
+    return fail(OIGE_E_MODEL, "env_step_role_kernel: no instantiation for %d roles x %d links%s", model->nroles,
+                model->maxc, tgt ? " with position targets" : "");
+}
+
+bool role_variant_exists(const OigeModel* model, bool tgt) {
+    return (model->nroles == 3 && model->maxc == 6 && !tgt) || (model->nroles == 4 && model->maxc == 3);
+}
+
+inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+}  // namespace
+
+// Whole env step in one launch (K2-F with prologue and epilogue).  Returns OIGE_E_MODEL + 1000 ("not applicable") when
+// the model / env count is not served by the role kernel -- the caller then runs the K3 -> K2 -> K1 sequence.
+int k2_fused_step(const OigeModel* model, const OigeTaskParams* P, const OigeState* st, const OigeTaskBuffers* b,
+                  const OigeResetInit* init, const float* actions_in, float clip, uint64_t seed, uint64_t counter,
+                  int64_t env_id_offset, int64_t n, int32_t substeps, float dt, cudaStream_t stream, int64_t decision_n,
+                  bool bump_counter) {
+    const int64_t dn = decision_n > 0 ? decision_n : n;
+    if (!k2_uses_role_kernel(model, dn) || !role_variant_exists(model, st->dof_pos_targets != nullptr)) return 1000;
+    if (P->num_dof != model->num_dof)
+        return fail(OIGE_E_SHAPE, "env_step: params.num_dof %d != model dofs %d", P->num_dof, model->num_dof);
+    if (P->num_sensors != model->num_sensors || P->num_obs != 12 + 3 * P->num_dof + 6 * P->num_sensors)
+        return fail(OIGE_E_SHAPE, "env_step: params (sensors %d, obs %d) do not match the model (%d sensors)",
+                    P->num_sensors, P->num_obs, model->num_sensors);
+    FArgs A{};
+    A.pos = st->root_pos; A.quat = st->root_quat; A.vel = st->root_vel; A.q = st->dof_pos; A.qd = st->dof_vel;
+    A.sens = st->sensors; A.targets = st->dof_pos_targets; A.actions = b->actions; A.n = n; A.substeps = substeps; A.dt = dt;
+    A.D = P->num_dof; A.S = P->num_sensors; A.OBS = P->num_obs;
+    A.pro = 1; A.epi = 1; A.bump = bump_counter ? 1 : 0;
+    A.actions_in = actions_in; A.actions_out = b->actions; A.clip = clip;
+    A.init_pos = init->initial_root_pos; A.init_rot = init->initial_root_rot; A.init_q = init->initial_dof_pos;
+    A.rand_pos = nullptr; A.rand_vel = nullptr; A.seed = seed; A.counter = counter;
+    A.counter_dev = reinterpret_cast<unsigned long long*>(b->reset_counter);
+    A.env_id_offset = env_id_offset;
+    A.obs = b->obs; A.rew = b->rew; A.pot = b->potentials; A.prev_pot = b->prev_potentials; A.up = b->up_vec;
+    A.head = b->heading_vec; A.reset = reinterpret_cast<long long*>(b->reset_buf);
+    A.progress = reinterpret_cast<long long*>(b->progress_buf); A.stats = b->episode_stats;
+    const void* ptrs[] = {A.pos, A.quat, A.vel, A.q, A.qd, A.sens, A.actions_in, A.actions_out, A.init_pos, A.init_rot,
+                          A.init_q, A.obs, A.rew, A.pot, A.prev_pot, A.up, A.head, A.reset, A.progress};
+    A.use_bulk = 1;
+    for (const void* p : ptrs) {
+        if (p == nullptr) return fail(OIGE_E_NULL, "oige_env_step_f32: null device pointer");
+        if (!al16(p)) A.use_bulk = 0;  // plain coalesced path for oddly offset views
+    }
+    if (reinterpret_cast<uintptr_t>(A.quat) & 15u) return fail(OIGE_E_ALIGN, "env_step: root_quat not 16B aligned");
+    if (reinterpret_cast<uintptr_t>(A.init_rot) & 15u) return fail(OIGE_E_ALIGN, "env_step: initial_root_rot not 16B aligned");
+    return role_dispatch(model, P, A, stream, dn);
 }
 
 // `decision_n`: env count the kernel choice is based on (the whole step's count when the caller
@@ -1006,41 +1127,30 @@ int k2_step(const OigeModel* model, const OigeTaskParams* P, const OigeState* st
     if (reinterpret_cast<uintptr_t>(A.quat) & 15u) return fail(OIGE_E_ALIGN, "articulation_step: root_quat not 16B aligned");
     if (model->num_sensors > 0 && P->num_sensors != model->num_sensors)
         return fail(OIGE_E_SHAPE, "articulation_step: params.num_sensors %d != model %d", P->num_sensors, model->num_sensors);
-    if (model->role_ok && use_role_split(decision_n > 0 ? decision_n : n, model->num_links)) {
-        const unsigned tb = (unsigned)((n + 31) / 32);
-        const DevModel* dm = reinterpret_cast<const DevModel*>(model->dev_table);
-        const int bs = model->nroles * 32;
-        // One wave with up to two CTAs per SM: 255-register budget (latency schedule); up to four: a budget sized for
-        // the model's warp count.  Decided on the WHOLE step's env count (chunked == one-shot stays bit-identical).
-        const long long dn = decision_n > 0 ? decision_n : n;
-        const char* mb = getenv("OIGE_K2_MINB");
-        const bool roomy = mb ? mb[0] == '2' : (dn + 31) / 32 <= 2ll * sm_count();
-        const int sm = model->role_smem;
-#define OIGE_ROLE_LAUNCH(MAXL)                                                                                  \
-    do {                                                                                                        \
-        if (roomy) launch_pdl(articulation_step_role_kernel<MAXL, kMaxRoles, 2>, tb, bs, sm, stream, dm, *P, A);        \
-        else if (model->nroles == 2) launch_pdl(articulation_step_role_kernel<MAXL, 2, 4>, tb, bs, sm, stream, dm, *P, A); \
-        else if (model->nroles == 3) launch_pdl(articulation_step_role_kernel<MAXL, 3, 4>, tb, bs, sm, stream, dm, *P, A); \
-        else launch_pdl(articulation_step_role_kernel<MAXL, 4, 4>, tb, bs, sm, stream, dm, *P, A);                      \
-    } while (0)
-        if (model->num_links <= 12) OIGE_ROLE_LAUNCH(12);
-        else OIGE_ROLE_LAUNCH(24);
-#undef OIGE_ROLE_LAUNCH
-        count_launch();
-        return check_launch("articulation_step_role_kernel");
+    const int64_t dn = decision_n > 0 ? decision_n : n;
+    if (k2_uses_role_kernel(model, dn) && role_variant_exists(model, A.targets != nullptr)) {
+        FArgs F{};  // physics only: the same instantiation as the fused step with prologue / epilogue switched off
+        F.pos = A.pos; F.quat = A.quat; F.vel = A.vel; F.q = A.q; F.qd = A.qd; F.sens = A.sens; F.actions = actions;
+        F.targets = A.targets; F.n = n; F.substeps = substeps; F.dt = dt;
+        F.D = model->num_dof; F.S = model->num_sensors; F.OBS = 12 + 3 * F.D + 6 * F.S;
+        F.use_bulk = 1;
+        const void* ptrs[] = {F.pos, F.quat, F.vel, F.q, F.qd, F.actions, F.sens};
+        for (const void* p : ptrs)
+            if (p != nullptr && !al16(p)) F.use_bulk = 0;
+        if (F.sens == nullptr && F.S > 0) F.use_bulk = F.use_bulk;  // sensors are optional for a physics-only call
+        return role_dispatch(model, P, F, stream, dn);
     }
-    if (model->tpe_ok && use_thread_per_env(decision_n > 0 ? decision_n : n)) {
+    if (model->tpe_ok && use_thread_per_env(dn)) {
         const int bs = 128;
         const unsigned tb = (unsigned)((n + bs - 1) / bs);
         const DevModel* dm = reinterpret_cast<const DevModel*>(model->dev_table);
         // Up to two CTAs per SM cover the launch in one wave: the register budget per thread is then 255 instead of
         // 126 and ptxas schedules for latency (the regime where one warp per scheduler runs alone).  Same PTX; ptxas
         // schedules (and may fuse mul+add) differently, so the two variants agree to rounding, not bit for bit.
-        const char* mb = getenv("OIGE_K2_MINB");
-        // (decided on the WHOLE step's env count, like the kernel choice: ptxas may contract mul+add differently in
-        // the two instantiations, and chunked and one-shot steps must stay bit-identical)
-        const long long dn = decision_n > 0 ? decision_n : n;
-        const bool roomy = mb ? mb[0] == '2' : (dn + bs - 1) / bs <= 2ll * sm_count();
+        // (decided on the WHOLE step's env count, like the kernel choice: chunked and one-shot steps must stay
+        // bit-identical)
+        const int mb = knobs().minb;
+        const bool roomy = mb ? mb == 2 : (dn + bs - 1) / bs <= 2ll * sm_count();
         if (roomy) {
             if (model->num_links <= 12) articulation_step_tpe_kernel<12, 2><<<tb, bs, 0, stream>>>(dm, *P, A);
             else if (model->num_links <= 24) articulation_step_tpe_kernel<24, 2><<<tb, bs, 0, stream>>>(dm, *P, A);
@@ -1064,6 +1174,12 @@ int k2_step(const OigeModel* model, const OigeTaskParams* P, const OigeState* st
             reinterpret_cast<const DevModel*>(model->dev_table), *P, A);
     count_launch();
     return check_launch("articulation_step_kernel");
+}
+
+uint64_t k2_nonfinite_count() {
+    unsigned long long v = 0;
+    if (cudaMemcpyFromSymbol(&v, g_nonfinite_envs, sizeof(v)) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return v;
 }
 
 OigeModel* k2_model_create(const OigeModelDesc* d) {
@@ -1150,21 +1266,27 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
         }
         if (heavy[0] >= 0) h->tflags[0] |= kHasHeavy;
     }
-    {   // role split (K2-R): trunk = root + ancestors-or-self of every branching link; the rest are chains
+    // ---- role split (K2-F): trunk = root + ancestors-or-self of every branching link; the rest are plain chains ----
+    RoleModel* rm = new RoleModel();
+    memset(rm, 0, sizeof(RoleModel));
+    int role_ok = 0, role_nroles = 0, role_maxc = 0;
+    {
         bool trunk[32] = {false};
         trunk[0] = true;
         for (int i = 0; i < L; ++i)
             if (nchild[i] >= 2)
                 for (int a = i; a > 0 && !trunk[a]; a = h->parent[a]) trunk[a] = true;
-        for (int i = 0; i < 32; ++i) { h->trunk_idx[i] = -1; h->head_slot[i] = -1; h->rflags[i] = 0; }
-        int nt = 0, nh = 0, heads[32], hlen[32], tip[32];
-        bool fits = true;
-        for (int i = 0; i < L; ++i) {
+        int tidx[32], nt = 0, nh = 0, heads[32], hlen[32], tip[32];
+        bool fits = L <= kRL && d->num_spheres <= OIGE_MAX_SPHERES;
+        for (int i = 0; i < 32; ++i) tidx[i] = -1;
+        for (int i = 0; i < L && fits; ++i) {
             if (trunk[i]) {
-                if (nt >= kMaxTrunk) { fits = false; break; }
-                h->trunk_idx[i] = nt; h->trunk_link[nt++] = i; h->rflags[i] |= kRTrunk;
+                if (nt >= kRT) { fits = false; break; }
+                // the trunk must be a PATH: link nt-1 is the parent of link nt
+                if (nt > 0 && h->parent[i] != rm->tlink[nt - 1]) { fits = false; break; }
+                tidx[i] = nt; rm->tlink[nt++] = (unsigned char)i;
             } else if (trunk[h->parent[i]]) {
-                if (nh >= kMaxHeads) { fits = false; break; }
+                if (nh >= 32) { fits = false; break; }
                 heads[nh++] = i;
             }
         }
@@ -1172,11 +1294,9 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
             int len = 1, cur = heads[c];
             while (nchild[cur] == 1) { cur = h->child[0][cur]; ++len; }
             hlen[c] = len; tip[c] = cur;
-            h->head_slot[heads[c]] = c; h->rflags[heads[c]] |= kRHead; h->rflags[cur] |= kRTip;
         }
         // smallest number of roles that reaches the best critical path (longest-processing-time dealing)
-        int best_r = 1, best_load = 1 << 30, owner[32];
-        int order[32];
+        int best_r = 1, best_load = 1 << 30, owner[32], order[32];
         for (int c = 0; c < nh; ++c) order[c] = c;
         for (int a = 0; a < nh; ++a)
             for (int b = a + 1; b < nh; ++b)
@@ -1191,49 +1311,92 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
             for (int q = 0; q < r; ++q) if (load[q] > mx) mx = load[q];
             if (mx < best_load) { best_load = mx; best_r = r; }
         }
-        {
-            int load[kMaxRoles] = {0};
-            for (int a = 0; a < nh; ++a) {
-                int w = 0;
-                for (int q = 1; q < best_r; ++q) if (load[q] < load[w]) w = q;
-                load[w] += hlen[order[a]];
-                owner[order[a]] = w;
-            }
+        int load[kMaxRoles] = {0};
+        for (int a = 0; a < nh; ++a) {
+            int w = 0;
+            for (int q = 1; q < best_r; ++q) if (load[q] < load[w]) w = q;
+            load[w] += hlen[order[a]];
+            owner[order[a]] = w;
         }
-        h->nroles = best_r; h->ntrunk = nt; h->nheads = nh;
-        h->role_ok = (fits && best_r >= 2 && h->tpe_ok && L <= 24) ? 1 : 0;
-        if (h->role_ok) {
-            for (int t = 0, pos = 0; t <= nt; ++t) {  // heads attached to each trunk link
-                h->th_begin[t] = pos;
-                if (t == nt) break;
-                for (int c = 0; c < nh; ++c)
-                    if (h->parent[heads[c]] == h->trunk_link[t]) h->th_heads[pos++] = c;
+        // instantiated combinations: 3 roles x <= 6 chain links (Humanoid), 4 roles x <= 3 (Ant, Anymal)
+        const int maxc = (best_r == 3 && best_load <= 6) ? 6 : (best_r == 4 && best_load <= 3) ? 3 : 0;
+        fits = fits && maxc > 0 && nh > 0;
+        if (fits) {
+            rm->num_links = L; rm->num_sensors = d->num_sensors; rm->fixed_base = d->fixed_base != 0; rm->nroles = best_r;
+            rm->ntrunk = nt; rm->maxc = maxc;
+            for (int i = 0; i < kRT; ++i) { rm->tpub[i] = 255; rm->town[i] = 0; }
+            for (int r = 0; r < 4; ++r) { rm->own_t[r] = 255; rm->own_slot[r] = 0; }
+            // hand-over slots: one per (role, attach trunk link)
+            int slot_of[kMaxRoles][kRT];
+            for (int r = 0; r < kMaxRoles; ++r) for (int t = 0; t < kRT; ++t) slot_of[r][t] = -1;
+            int nslots = 0;
+            for (int a = 0; a < nh && fits; ++a) {
+                const int c = order[a], r = owner[c], t = tidx[h->parent[heads[c]]];
+                if (slot_of[r][t] < 0) {
+                    if (nslots >= kRSlots) { fits = false; break; }
+                    slot_of[r][t] = nslots++;
+                }
             }
-            for (int r = 0; r < best_r; ++r) {
-                bool mine[32] = {false};
-                int c2 = 0;
-                for (int a = 0; a < nh; ++a) {  // chains in dealing order, each tip -> head
+            rm->nslots = nslots;
+            int pos = 0, npub = 0;
+            for (int t = 0; t < nt; ++t) {
+                rm->ts_begin[t] = (unsigned char)pos;
+                for (int r = 0; r < best_r; ++r)
+                    if (slot_of[r][t] >= 0) rm->ts_slot[pos++] = (unsigned char)slot_of[r][t];
+                if (pos > rm->ts_begin[t]) rm->tpub[t] = (unsigned char)npub++;
+            }
+            rm->ts_begin[nt] = (unsigned char)pos;
+            rm->npub = npub;
+            // own inertia of a trunk link goes to the least loaded role that has a slot on it (one link per role)
+            for (int t = 0; t < nt; ++t) {
+                int pick = -1;
+                for (int r = 0; r < best_r; ++r)
+                    if (slot_of[r][t] >= 0 && rm->own_t[r] == 255 && (pick < 0 || load[r] < load[pick])) pick = r;
+                if (pick >= 0) { rm->own_t[pick] = (unsigned char)t; rm->own_slot[pick] = (unsigned char)slot_of[pick][t]; rm->town[t] = 1; }
+            }
+            // per-role programs: chains in dealing order, each head -> tip
+            int sensor_chains[kMaxRoles] = {0};
+            bool slot_written[kRSlots] = {false};
+            for (int r = 0; r < best_r; ++r)
+                if (rm->own_t[r] != 255) slot_written[rm->own_slot[r]] = true;
+            bool sensor_seen[OIGE_MAX_SENSORS] = {false};
+            for (int r = 0; r < best_r && fits; ++r) {
+                int k = 0;
+                for (int a = 0; a < nh; ++a) {
                     const int c = order[a];
                     if (owner[c] != r) continue;
-                    for (int cur = tip[c];; cur = h->parent[cur]) {
-                        h->list2[r][c2++] = cur; mine[cur] = true;
-                        if (cur == heads[c]) break;
+                    const int t = tidx[h->parent[heads[c]]], sl = slot_of[r][t];
+                    int sens = -1;
+                    for (int s2 = 0; s2 < d->num_sensors; ++s2) if (d->sensor_link[s2] == tip[c]) sens = s2;
+                    if (sens >= 0) { ++sensor_chains[r]; sensor_seen[sens] = true; }
+                    int links[32], n = 0;
+                    for (int cur = tip[c];; cur = h->parent[cur]) { links[n++] = cur; if (cur == heads[c]) break; }
+                    for (int j = n - 1; j >= 0; --j, ++k) {  // head first
+                        unsigned char f = 0;
+                        if (j == n - 1) f |= kPHead;
+                        if (j == 0) f |= kPTip;
+                        if (sens >= 0) f |= kPSensor;
+                        if (j == n - 1 && !slot_written[sl]) { f |= kPSlotFirst; slot_written[sl] = true; }
+                        rm->plink[r][k] = (unsigned char)links[j]; rm->pflag[r][k] = f;
+                        rm->patt[r][k] = (unsigned char)t; rm->pslot[r][k] = (unsigned char)sl;
                     }
                 }
-                const int nchain = c2;
-                if (r == 0) {
-                    for (int t = nt - 1; t >= 1; --t) h->list2[0][c2++] = h->trunk_link[t];
-                    h->list2[0][c2++] = 0;
-                }
-                h->n2[r] = c2;
-                h->sync2[r] = (r == 0) ? nchain : c2;
-                h->sync3[r] = nchain - 1;  // role 0 without chains: -1 = barrier after the sweep
-                int c1 = 0;
-                for (int i = 1; i < L; ++i)
-                    if (trunk[i] || mine[i]) h->list1[r][c1++] = i;
-                h->n1[r] = c1;
+                rm->npos[r] = (unsigned char)k;
+                if (sensor_chains[r] > 1) fits = false;  // one sensor wrench is held in registers per role
             }
+            for (int s2 = 0; s2 < d->num_sensors; ++s2) fits = fits && sensor_seen[s2];  // sensors sit on chain tips
+            // scratch layout of a 32-env group (float offsets, x32 lanes)
+            rm->oI = 0;
+            rm->oA = rm->oI + nslots * kHand;
+            rm->oK = rm->oA + npub * 6;
+            rm->oT = rm->oK + nt * kKin;
+            rm->oS = rm->oT + (nt - 1) * 4;
+            rm->oM = rm->oS + d->num_sensors * 7;
+            rm->oL = rm->oM + 2;
+            rm->group_floats = rm->oL + best_r * maxc * kPu;
         }
+        role_ok = (fits && h->tpe_ok) ? 1 : 0;
+        role_nroles = best_r; role_maxc = maxc;
     }
     h->jump_rounds = 0;
     while ((1 << h->jump_rounds) < h->max_depth) ++h->jump_rounds;
@@ -1246,13 +1409,6 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
         h->drive_kp[i] = d->drive_stiffness[i]; h->drive_kd[i] = d->drive_damping[i]; h->drive_fmax[i] = d->drive_max_force[i];
     }
     h->jquat[0][0] = 1.f;
-    for (int i = 1; i < L; ++i) {  // K2-R skips the own-inertia work of massless, sphere-less links
-        bool zero = d->mass[i] == 0.f;
-        for (int k = 0; k < 6; ++k) zero = zero && d->inertia[i][k] == 0.f;
-        for (int s = 0; s < d->num_spheres; ++s) zero = zero && d->sphere_link[s] != i;
-        for (int s = 0; s < d->num_sensors; ++s) zero = zero && d->sensor_link[s] != i;
-        if (zero) h->rflags[i] |= kRMassless;
-    }
     // spheres sorted by link (stable)
     int pos = 0;
     for (int i = 0; i < L; ++i) {
@@ -1269,12 +1425,14 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
     if (pos != d->num_spheres) {
         set_error("oige_model_create: sphere_link out of range");
         delete h;
+        delete rm;
         return nullptr;
     }
     for (int s = 0; s < d->num_sensors; ++s) {
         if (d->sensor_link[s] < 0 || d->sensor_link[s] >= L) {
             set_error("oige_model_create: sensor_link out of range");
             delete h;
+            delete rm;
             return nullptr;
         }
         h->sensor_of_link[d->sensor_link[s]] = s;
@@ -1283,25 +1441,57 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
     h->k_c = d->contact_stiffness; h->d_c = d->contact_damping; h->mu = d->friction_mu; h->c_visc = d->friction_viscous;
     h->k_lim = d->limit_stiffness; h->d_lim = d->limit_damping; h->max_qd = d->max_joint_velocity; h->ang_damp = d->angular_damping;
 
-    const int tpe_ok = h->tpe_ok, role_ok = h->role_ok, nroles = h->nroles;
-    const int role_smem = (h->nheads * 27 + h->ntrunk * 7 + 1) * 32 * (int)sizeof(float);
+    const int tpe_ok = h->tpe_ok;
+    void* dev_role = nullptr;
+    if (role_ok) {  // compact copy of the tables for K2-F
+        for (int k = 0; k < 4; ++k) rm->gravity[k] = h->gravity[k];
+        rm->k_c = h->k_c; rm->d_c = h->d_c; rm->mu = h->mu; rm->c_visc = h->c_visc; rm->k_lim = h->k_lim;
+        rm->d_lim = h->d_lim; rm->max_qd = h->max_qd; rm->ang_damp = h->ang_damp;
+        for (int i = 0; i < L; ++i) {
+            for (int k = 0; k < 3; ++k) { rm->jpos[k][i] = h->jpos[k][i]; rm->axis[k][i] = h->axis[k][i]; rm->com[k][i] = h->com[k][i]; }
+            for (int k = 0; k < 4; ++k) rm->jquat[k][i] = h->jquat[k][i];
+            for (int k = 0; k < 6; ++k) rm->inertia[k][i] = h->inertia[k][i];
+            rm->mass[i] = h->mass[i]; rm->armature[i] = h->armature[i]; rm->damping[i] = h->damping[i];
+            rm->stiffness[i] = h->stiffness[i]; rm->sref[i] = h->sref[i]; rm->lo[i] = h->lo[i]; rm->hi[i] = h->hi[i];
+            rm->drive_kp[i] = h->drive_kp[i]; rm->drive_kd[i] = h->drive_kd[i]; rm->drive_fmax[i] = h->drive_fmax[i];
+            rm->dof[i] = (unsigned char)(i > 0 ? h->dof[i] : 0); rm->jtype[i] = (unsigned char)h->jtype[i];
+            rm->sph_start[i] = (unsigned char)h->sph_start[i]; rm->sph_count[i] = (unsigned char)h->sph_count[i];
+            rm->sensor_of_link[i] = (signed char)h->sensor_of_link[i];
+            // intermediate link of a multi-dof joint: no mass, no spheres, no sensor -> its own inertia is skipped
+            bool zero = i > 0 && d->mass[i] == 0.f && h->sph_count[i] == 0 && h->sensor_of_link[i] < 0;
+            for (int k = 0; k < 6; ++k) zero = zero && d->inertia[i][k] == 0.f;
+            rm->massless[i] = zero ? 1 : 0;
+        }
+        for (int s2 = 0; s2 < d->num_spheres; ++s2) {
+            for (int k = 0; k < 3; ++k) rm->sph_pos[k][s2] = h->sph_pos[k][s2];
+            rm->sph_r[s2] = h->sph_r[s2];
+        }
+    }
+    const int group_floats = rm->group_floats;
     void* dev = nullptr;
     cudaError_t e = cudaMalloc(&dev, sizeof(DevModel));
     if (e == cudaSuccess) e = cudaMemcpy(dev, h, sizeof(DevModel), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && role_ok) {
+        e = cudaMalloc(&dev_role, sizeof(RoleModel));
+        if (e == cudaSuccess) e = cudaMemcpy(dev_role, rm, sizeof(RoleModel), cudaMemcpyHostToDevice);
+    }
     delete h;
+    delete rm;
     if (e != cudaSuccess) {
         set_error("oige_model_create: %s", cudaGetErrorString(e));
         if (dev) cudaFree(dev);
+        if (dev_role) cudaFree(dev_role);
         return nullptr;
     }
     OigeModel* m = new OigeModel();
-    m->dev_table = dev; m->num_links = L; m->num_dof = L - 1; m->num_sensors = d->num_sensors; m->tpe_ok = tpe_ok;
-    m->role_ok = role_ok; m->nroles = nroles; m->role_smem = role_smem;
+    m->dev_table = dev; m->dev_role = dev_role; m->num_links = L; m->num_dof = L - 1; m->num_sensors = d->num_sensors;
+    m->tpe_ok = tpe_ok; m->role_ok = role_ok; m->nroles = role_nroles; m->maxc = role_maxc; m->group_floats = group_floats;
     return m;
 }
 
 void k2_model_destroy(OigeModel* m) {
     if (m->dev_table) cudaFree(m->dev_table);
+    if (m->dev_role) cudaFree(m->dev_role);
     delete m;
 }
 

@@ -1,6 +1,7 @@
 // C ABI of liboige_b200.so (declared in include/oige_b200.h).  Thin argument checking + dispatch;
 // the kernels live in obs_reward_reset.cu (K1), articulation_step.cu (K2), reset_idx.cu (K3).
 #include <atomic>
+#include <mutex>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -37,21 +38,22 @@ int check_launch(const char* what) {
 void count_launch(uint64_t n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
 bool pdl_enabled() {
-    static int v = -1;
-    if (v < 0) { const char* e = getenv("OIGE_PDL"); v = (e && e[0] == '0') ? 0 : 1; }
-    return v != 0;
+    static std::atomic<int> v{-1};
+    int cur = v.load(std::memory_order_acquire);
+    if (cur < 0) { const char* e = getenv("OIGE_PDL"); cur = (e && e[0] == '0') ? 0 : 1; v.store(cur, std::memory_order_release); }
+    return cur != 0;
 }
 
-int sm_count() {
-    static int cached = -1;
-    if (cached < 0) {
-        int dev = 0, n = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess ||
-            cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
-            return 148;
-        cached = n;
+int sm_count() {  // of the CURRENT device (a process may drive several GPUs)
+    static std::atomic<int> cached[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    int n = cached[dev].load(std::memory_order_acquire);
+    if (n <= 0) {
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) return 148;
+        cached[dev].store(n, std::memory_order_release);
     }
-    return cached;
+    return n;
 }
 
 // kernels' host-side dispatchers
@@ -62,6 +64,11 @@ int k3_idx(const OigeTaskParams*, const OigeState*, const OigeTaskBuffers*, cons
            int64_t, const float*, const float*, uint64_t, uint64_t, int64_t, cudaStream_t);
 int k2_step(const OigeModel*, const OigeTaskParams*, const OigeState*, const float*, int64_t, int32_t, float,
             cudaStream_t, int64_t decision_n);
+int k2_fused_step(const OigeModel*, const OigeTaskParams*, const OigeState*, const OigeTaskBuffers*, const OigeResetInit*,
+                  const float* actions_in, float clip, uint64_t seed, uint64_t counter, int64_t env_id_offset, int64_t n,
+                  int32_t substeps, float dt, cudaStream_t, int64_t decision_n, bool bump_counter);
+void k2_reload_env();
+uint64_t k2_nonfinite_count();
 OigeModel* k2_model_create(const OigeModelDesc*);
 int dr_apply(const OigeNoiseSpec*, const OigeNoiseSpec*, const OigeNoiseState*, const float*, float*, const int64_t*,
              int64_t, int32_t, float, float, const float*, const float*, uint64_t, uint64_t, const uint64_t*, int32_t,
@@ -77,6 +84,7 @@ int cartpole_pre(const OigeCartpoleParams*, const OigeState*, const OigeCartpole
 int cartpole_reset_idx(const OigeCartpoleParams*, const OigeState*, const OigeCartpoleBuffers*, const int64_t*, int64_t,
                        const float*, uint64_t, uint64_t, int64_t, cudaStream_t);
 void k2_model_destroy(OigeModel*);
+void host_knobs_reload();
 
 static int check_common(const char* who, const OigeTaskParams* p, const OigeState* s, const OigeTaskBuffers* b,
                         int64_t n) {
@@ -95,15 +103,26 @@ struct HostPipe {
     bool trace, pending;
     int last_used;
 };
-static int host_chunk_count() {  // OIGE_HOST_CHUNKS=1..8 (default 4, measured: tools/e2e_breakdown.py)
-    const char* e = getenv("OIGE_HOST_CHUNKS");
-    const int v = e ? atoi(e) : 4;
-    return v < 1 ? 1 : (v > kHostChunks ? kHostChunks : v);
+// run-time knobs of the host-buffer step, read once (oige_reload_env() re-reads them)
+struct HostKnobs { int chunks, zerocopy, trace; };
+static HostKnobs g_hk = {4, 0, 0};
+static std::once_flag g_hk_once;
+static void host_knobs_read() {
+    HostKnobs k = {4, 0, 0};
+    if (const char* e = getenv("OIGE_HOST_CHUNKS")) { const int v = atoi(e); k.chunks = v < 1 ? 1 : (v > kHostChunks ? kHostChunks : v); }
+    if (const char* e = getenv("OIGE_HOST_ZEROCOPY")) k.zerocopy = atoi(e);
+    if (const char* e = getenv("OIGE_HOST_TRACE")) k.trace = e[0] == '1';
+    g_hk = k;
 }
+static const HostKnobs& host_knobs() { std::call_once(g_hk_once, host_knobs_read); return g_hk; }
+void host_knobs_reload() { host_knobs(); host_knobs_read(); }
+static int host_chunk_count() { return host_knobs().chunks; }  // OIGE_HOST_CHUNKS=1..8 (default 4, tools/e2e_breakdown.py)
 static HostPipe* host_pipe() {
     static HostPipe* pipes[64] = {nullptr};
+    static std::mutex mu;  // creation is serialised: the C ABI may be entered from several host threads
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    std::lock_guard<std::mutex> lock(mu);
     if (!pipes[dev]) {
         HostPipe* p = new HostPipe();
         bool ok = cudaEventCreateWithFlags(&p->start, cudaEventDisableTiming) == cudaSuccess;
@@ -111,8 +130,7 @@ static HostPipe* host_pipe() {
             ok = cudaStreamCreateWithFlags(&p->streams[i], cudaStreamNonBlocking) == cudaSuccess &&
                  cudaEventCreateWithFlags(&p->done[i], cudaEventDisableTiming) == cudaSuccess;
         }
-        const char* tr = getenv("OIGE_HOST_TRACE");
-        p->trace = tr && tr[0] == '1';
+        p->trace = host_knobs().trace != 0;
         p->pending = false;
         if (p->trace) {
             ok = ok && cudaEventCreate(&p->t0) == cudaSuccess;
@@ -134,6 +152,8 @@ using namespace oige;
 extern "C" {
 
 int oige_abi_version(void) { return OIGE_ABI_VERSION; }
+void oige_reload_env(void) { k2_reload_env(); host_knobs_reload(); }
+uint64_t oige_nonfinite_env_count(void) { return k2_nonfinite_count(); }
 const char* oige_last_error(void) { return g_err; }
 uint64_t oige_kernel_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
@@ -205,6 +225,13 @@ static int env_step_impl(const OigeModel* model, const OigeTaskParams* params, c
     cudaStream_t s = (cudaStream_t)stream;
     // VecEnvRLGames.step: clamp -> pre_physics_step (reset flagged envs, store actions, efforts)
     //                     -> control_frequency_inv x world.step -> post_physics_step
+    // ONE launch when the role-split kernel serves this model and env count (K2-F: prologue + substeps + epilogue) ...
+    {
+        const int rc = k2_fused_step(model, params, state, buf, init, actions_in, clip_actions, seed, counter,
+                                     env_id_offset, n_envs, substeps, dt, s, decision_n, decision_n <= 0);
+        if (rc != 1000) return rc;
+    }
+    // ... otherwise three: K3 (reset + clamp) -> K2-W / K2-T -> K1
     if (int rc = k3_masked(params, state, buf, init, nullptr, nullptr, seed, counter, env_id_offset, n_envs, s,
                            actions_in, clip_actions))
         return rc;
@@ -245,9 +272,8 @@ int oige_env_step_host_f32(const OigeModel* model, const OigeTaskParams* params,
     float* obs_host_dev = nullptr;
     const float* actions_host_dev = nullptr;
     {
-        const char* zc = getenv("OIGE_HOST_ZEROCOPY");
         cudaPointerAttributes at;
-        const int zmode = zc ? atoi(zc) : 0;  // bit 0: observations written straight to the host, bit 1: actions read from it
+        const int zmode = host_knobs().zerocopy;  // bit 0: observations written straight to the host, bit 1: actions read from it
         if ((zmode & 1) && cudaPointerGetAttributes(&at, obs_host) == cudaSuccess &&
             at.type == cudaMemoryTypeHost && at.devicePointer != nullptr)
             obs_host_dev = static_cast<float*>(at.devicePointer);

@@ -1,0 +1,824 @@
+// K2-F `env_step_role_kernel` -- the whole VecEnvRLGames.step of a locomotion task in ONE launch:
+//   prologue  action clamp + masked reset_idx                (envs/vec_env_rlgames.py:57, tasks/shared/locomotion.py:103-145)
+//   main      `substeps` articulation substeps                (vec_env_rlgames.py:64-66; PhysX stand-in)
+//   epilogue  progress += 1, observations, reward, done       (tasks/base/rl_task.py:242, locomotion.py:190-321)
+// (Included by articulation_step.cu inside its anonymous namespace: same device functions as K2-W / K2-T.)
+// The prologue and the epilogue are switched by run-time flags of the SAME instantiation, so the physics of the fused
+// step and of a stand-alone oige_articulation_step_f32 call are the same machine code (bit-identical results); the
+// epilogue evaluates locomotion_math.cuh, the arithmetic K1 evaluates, on the tile it just staged for the write-back.
+//
+// Mapping.  lane = env, warp = ROLE, a GROUP = 32 envs x `nroles` warps, a CTA = EPC/32 groups.  The tree is cut on the
+// host into a TRUNK (root + every link with a branching link at or below it; must be a path) and the plain CHAINS
+// hanging off it, dealt to the roles; role 0 also owns the trunk.  Per substep (three named barriers per group):
+//   S0  role 0: kinematics of the trunk -> shared memory (xK)                                        | barrier K
+//   S1  every role, chain by chain: kinematics head -> tip (frames into the chain's link slots), then the articulated
+//       inertia tip -> head in registers; each link leaves (s, U/d, u''') in its slot; the head's I^a, p^a are added to
+//       the role's hand-over slot (xI).  A role with a slot on trunk link t may also take t's OWN inertia / bias /
+//       contacts off role 0's hands.                                                                  | barrier H
+//   S2  role 0: trunk tip -> root (own inertia + hand-over slots + carry), 6x6 Cholesky at the root, trunk accelerations
+//       root -> tip, trunk joints and root integrated, accelerations of the attach links published (xA) | barrier A
+//   S3  every role: accelerations down its chains -- 13 FMAs per link: qdd = u''' - (U/d).a', a' += s qdd -- and joint
+//       integration; the foot-sensor wrench in the last substep.
+// Everything a link must remember between the sweeps lives in SHARED memory, 13 floats per link:
+//   after the kinematics sweep   quat (4), p (3)              -- v, b are rebuilt on the way up (v_parent = v - s qd)
+//   after the inertia sweep      s (6), U/d (6), u''' (1)     -- with a' = a - b (acceleration minus the velocity-
+//                                                                product path sum) the downward sweep needs nothing else
+// and the joint state q, qd, effort (target) of a role's <= MAXC chain links stays in REGISTERS (select chains instead
+// of dynamic indexing).  No per-thread local memory, hence none of the L1-miss / DRAM spill traffic of K2-T / the
+// former K2-R (profiles/r1_ncu_k2r_16384.txt: 37.8 MB of local-memory writes per launch).
+constexpr int kRL = 24;      // links
+constexpr int kRPos = 8;     // chain links per role (>= MAXC)
+constexpr int kRT = 4;       // trunk links incl. the root
+constexpr int kRSlots = 8;   // hand-over slots
+constexpr int kPHead = 1, kPTip = 2, kPSlotFirst = 4, kPSensor = 8;
+constexpr int kKin = 19;     // quat 4, p 3, v 6, b 6
+constexpr int kPu = 13;      // s 6, U/d 6, u'''
+constexpr int kHand = 27;    // I^a 21, p^a 6
+
+struct alignas(16) RoleModel {
+    int num_links, num_sensors, fixed_base, nroles;
+    int ntrunk, nslots, npub, group_floats;
+    int oI, oA, oK, oT, oS, oM, oL, maxc;   // float offsets (x32 lanes) of the regions of a group's scratch
+    float gravity[4];
+    float k_c, d_c, mu, c_visc, k_lim, d_lim, max_qd, ang_damp;
+    float jpos[3][kRL];
+    float jquat[4][kRL];
+    float axis[3][kRL];
+    float mass[kRL];
+    float com[3][kRL];
+    float inertia[6][kRL];
+    float armature[kRL], damping[kRL], stiffness[kRL], sref[kRL], lo[kRL], hi[kRL];
+    float drive_kp[kRL], drive_kd[kRL], drive_fmax[kRL];
+    float sph_pos[3][OIGE_MAX_SPHERES];
+    float sph_r[OIGE_MAX_SPHERES];
+    unsigned char dof[kRL], jtype[kRL], sph_start[kRL], sph_count[kRL], massless[kRL];
+    signed char sensor_of_link[kRL];
+    unsigned char npos[4];
+    unsigned char plink[4][kRPos], pflag[4][kRPos], patt[4][kRPos], pslot[4][kRPos];
+    unsigned char own_t[4], own_slot[4];   // trunk link whose own inertia role r evaluates in S1 (255: none), into which slot
+    unsigned char tlink[kRT], town[kRT], tpub[kRT];      // trunk idx -> link, own inertia handed to a role?, xA index (255: none)
+    unsigned char ts_begin[kRT + 1], ts_slot[kRSlots];   // hand-over slots attached to trunk link t
+    unsigned char pad[7];
+};
+static_assert(sizeof(RoleModel) % 16 == 0, "RoleModel must be int4-copyable");
+
+struct FArgs {
+    float* pos; float* quat; float* vel; float* q; float* qd; float* sens;
+    const float* actions;   // [N,D] what the efforts are formed from (fused step: the clamped copy in actions_out)
+    const float* targets;   // [N,D] PD position targets or null
+    long long n;
+    int substeps;
+    float dt;
+    int D, S, OBS;
+    int pro, epi, use_bulk, bump;
+    // prologue (masked reset + clamp)
+    const float* actions_in; float* actions_out; float clip;
+    const float* init_pos; const float* init_rot; const float* init_q;
+    const float* rand_pos; const float* rand_vel;
+    unsigned long long seed, counter;
+    unsigned long long* counter_dev;   // [2]: Philox reset counter, CTA ticket (see OigeTaskBuffers.reset_counter)
+    long long env_id_offset;
+    // epilogue
+    float* obs; float* rew; float* pot; float* prev_pot; float* up; float* head;
+    long long* reset; long long* progress;
+    double* stats;
+};
+
+__device__ unsigned long long g_nonfinite_envs = 0;  // envs parked by the non-finite guard since load (diagnostic)
+
+__device__ __forceinline__ void group_barrier(int id, int nthreads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+// register arrays with a run-time index: select chains keep them in registers (no local memory)
+template <int N>
+__device__ __forceinline__ float rsel(const float (&r)[N], int k) {
+    float v = r[0];
+#pragma unroll
+    for (int j = 1; j < N; ++j) v = (k == j) ? r[j] : v;
+    return v;
+}
+template <int N>
+__device__ __forceinline__ void rput(float (&r)[N], int k, float v) {
+#pragma unroll
+    for (int j = 0; j < N; ++j) r[j] = (k == j) ? v : r[j];
+}
+
+struct KinCtx {  // frame, spatial velocity and velocity-product path sum of the link the sweep stands on
+    Q4 q;
+    M3 R;
+    V3 p;
+    V6 v, b;
+};
+
+// parent context -> this link's context (same arithmetic as pass 1 of K2-T)
+template <class MT>
+__device__ __forceinline__ void kin_step(const MT& M, int i, float qj, float qdj, KinCtx& c) {
+    const V3 axis = {M.axis[0][i], M.axis[1][i], M.axis[2][i]};
+    const bool prismatic = M.jtype[i] == OIGE_JOINT_PRISMATIC;
+    float sh, ch;
+    sincosf(prismatic ? 0.f : 0.5f * qj, &sh, &ch);
+    const Q4 ql = qmul(Q4{M.jquat[0][i], M.jquat[1][i], M.jquat[2][i], M.jquat[3][i]},
+                       Q4{ch, sh * axis.x, sh * axis.y, sh * axis.z});
+    const Q4 qi = qmul(c.q, ql);
+    V3 p = c.p + mulv(c.R, V3{M.jpos[0][i], M.jpos[1][i], M.jpos[2][i]});
+    const M3 R = qmat(qi);
+    const V3 aw = mulv(R, axis);
+    if (prismatic) p = p + qj * aw;
+    const V6 s = joint_subspace(prismatic, aw, p);
+    V6 v;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) v.a[k] = fmaf(s.a[k], qdj, c.v.a[k]);
+    const V6 cc = velocity_product(v, s, qdj);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) c.b.a[k] += cc.a[k];
+    c.q = qi; c.R = R; c.p = p; c.v = v;
+}
+
+// own spatial inertia, bias force and linearly-implicit ground contacts of link i (zero for a massless,
+// sphere-less intermediate link of a multi-dof joint)
+template <class MT>
+__device__ __forceinline__ void own_inertia(const MT& M, int i, const M3& R, V3 p, const V6& v, const V6& b,
+                                            float root_z, float dt, V3 grav, S6& IA, V6& pA) {
+    if (M.massless[i]) {
+#pragma unroll
+        for (int j = 0; j < 21; ++j) IA.a[j] = 0.f;
+#pragma unroll
+        for (int j = 0; j < 6; ++j) pA.a[j] = 0.f;
+    } else {
+        link_inertia_bias(M, i, R, p, v, grav, IA, pA);
+        link_contacts(M, i, R, p, v, b, root_z, dt, IA, pA);
+    }
+}
+
+// One joint of the bottom-up sweep: (I^A, p^A) of link i -> (I^a, p^a) seen by its parent; leaves (s, U/d, u''') in
+// `pu` (stride 32) and turns (v, b) into the parent's.
+template <class MT>
+__device__ __forceinline__ void joint_reduce(const MT& M, int i, const M3& R, V3 p, V6& v, V6& b, float qj, float qdj,
+                                             float eff, bool has_tgt, float tgt, float dt, S6& IA, V6& pA, float* pu) {
+    const V3 axis = {M.axis[0][i], M.axis[1][i], M.axis[2][i]};
+    const V6 s = joint_subspace(M.jtype[i] == OIGE_JOINT_PRISMATIC, mulv(R, axis), p);
+    const V6 c = velocity_product(v, s, qdj);
+    float tau0, dextra;
+    joint_force(M, i, qj, qdj, eff, dt, has_tgt, tgt, tau0, dextra);
+    const V6 U = s6mul(IA, s);
+    const float dinv = 1.f / (dot6(s, U) + dextra);
+    const float u = tau0 - dot6(s, pA);
+#pragma unroll
+    for (int a1 = 0; a1 < 6; ++a1) {
+        const float ui = U.a[a1] * dinv;
+#pragma unroll
+        for (int a2 = a1; a2 < 6; ++a2) IA.a[sidx(a1, a2)] = fmaf(-ui, U.a[a2], IA.a[sidx(a1, a2)]);
+    }
+    const V6 Iac = s6mul(IA, c);
+    const float ud = u * dinv;
+#pragma unroll
+    for (int j = 0; j < 6; ++j) pA.a[j] = pA.a[j] + Iac.a[j] + U.a[j] * ud;
+    // downward sweep: qdd = (u - U.(a_parent + c)) / d with a = a' + b (b = path sum of the c's), i.e.
+    // qdd = u''' - (U/d).a'_parent, u''' = (u - U.b_i) / d
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+        pu[j * 32] = s.a[j];
+        pu[(6 + j) * 32] = U.a[j] * dinv;
+    }
+    pu[12 * 32] = (u - dot6(U, b)) * dinv;
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+        v.a[j] = fmaf(-s.a[j], qdj, v.a[j]);
+        b.a[j] -= c.a[j];
+    }
+}
+
+template <int MAXC, int NR, bool TGT, int EPC, int MINB>
+__global__ void __launch_bounds__(NR * EPC, MINB)
+env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant__ OigeTaskParams P,
+                     const __grid_constant__ FArgs A) {
+    __shared__ __align__(16) RoleModel M;
+    __shared__ __align__(8) uint64_t s_bar;
+    __shared__ float s_stat[(EPC / 32) * 3];
+    extern __shared__ __align__(128) float dynsm[];
+    constexpr int NT = NR * EPC;
+    constexpr int GT = NR * 32;  // threads of a group
+    const int tid = threadIdx.x;
+    {
+        const int4* src = reinterpret_cast<const int4*>(gmodel);
+        int4* dst = reinterpret_cast<int4*>(&M);
+        for (int i = tid; i < (int)(sizeof(RoleModel) / 16); i += NT) dst[i] = src[i];
+    }
+    const int grp = tid / GT, role = (tid / 32) % NR, lane = tid & 31;
+    const int bar_id = 1 + grp;
+    const int D = A.D;
+    const long long e0 = (long long)blockIdx.x * EPC;
+    const int cnt = (int)((A.n - e0) < (long long)EPC ? (A.n - e0) : (long long)EPC);
+    const bool bulk = A.use_bulk && cnt == EPC;
+    const int e_raw = grp * 32 + lane;
+    const bool valid = e_raw < cnt;
+    const int e = valid ? e_raw : cnt - 1;  // idle lanes shadow the tile's last env and store nothing
+    const long long env = e0 + e;
+    const float dt = A.dt;
+
+    // ================= stage the tile: q, qd, actions, root state ========================================
+    float* s_q = dynsm;
+    float* s_qd = s_q + EPC * D;
+    float* s_act = s_qd + EPC * D;
+    float* s_pos = s_act + EPC * D;
+    float* s_quat = s_pos + EPC * 3;
+    float* s_vel = s_quat + EPC * 4;
+    const float* act_src = A.pro ? A.actions_in : A.actions;
+    pdl_wait();  // state / actions may be written by a preceding kernel; the model table is not
+    if (bulk) {
+        if (tid == 0) {
+            mbar_init(&s_bar, 1);
+            mbar_fence_init();
+            mbar_expect_tx(&s_bar, (uint32_t)EPC * (3u * D + 13u) * 4u);
+            bulk_g2s(s_q, A.q + e0 * D, EPC * D * 4, &s_bar);
+            bulk_g2s(s_qd, A.qd + e0 * D, EPC * D * 4, &s_bar);
+            bulk_g2s(s_act, act_src + e0 * D, EPC * D * 4, &s_bar);
+            bulk_g2s(s_pos, A.pos + e0 * 3, EPC * 12, &s_bar);
+            bulk_g2s(s_quat, A.quat + e0 * 4, EPC * 16, &s_bar);
+            bulk_g2s(s_vel, A.vel + e0 * 6, EPC * 24, &s_bar);
+        }
+        __syncthreads();  // barrier initialised (and the model table staged) before anyone polls
+        mbar_wait(&s_bar, 0);
+    } else {
+        for (int i = tid; i < cnt * D; i += NT) { s_q[i] = A.q[e0 * D + i]; s_qd[i] = A.qd[e0 * D + i]; s_act[i] = act_src[e0 * D + i]; }
+        for (int i = tid; i < cnt * 3; i += NT) s_pos[i] = A.pos[e0 * 3 + i];
+        for (int i = tid; i < cnt * 4; i += NT) s_quat[i] = A.quat[e0 * 4 + i];
+        for (int i = tid; i < cnt * 6; i += NT) s_vel[i] = A.vel[e0 * 6 + i];
+        __syncthreads();
+    }
+    pdl_trigger();
+    unsigned long long rcounter = A.counter;
+    bool rflag = false;
+    if (A.pro) {
+        rflag = A.reset[env] != 0;  // read by every role BEFORE the barrier below; role 0 clears the flag after it
+        // VecEnvRLGames.step's torch.clamp(actions, -clip, clip) (envs/vec_env_rlgames.py:57): the clamped copy the
+        // task keeps (locomotion.py:108) goes to actions_out, coalesced; the tile copy feeds the efforts below
+        const float c = A.clip;
+        for (int i = tid; i < cnt * D; i += NT) {
+            const float v = s_act[i];
+            const float w = v < -c ? -c : (v > c ? c : v);
+            s_act[i] = w;
+            A.actions_out[e0 * D + i] = w;
+        }
+        if (A.counter_dev != nullptr) rcounter = *A.counter_dev;
+        __syncthreads();
+    }
+    // masked reset_idx (locomotion.py:116-145), same arithmetic as reset_idx.cu, evaluated by the threads that own
+    // the values
+    const int np = M.npos[role];
+    float qr[MAXC], qdr[MAXC], effr[MAXC], tgtr[TGT ? MAXC : 1];
+    float tq0[kRT - 1], tq1[kRT - 1], tq2[kRT - 1], tq3[kRT - 1];  // role 0: trunk q, qd, effort, target on their way to xT
+    auto load_joint = [&](int link, float& qo, float& qdo, float& effo, float& tgo) {
+        const int d = M.dof[link];
+        float qv = s_q[e * D + d], qdv = s_qd[e * D + d];
+        if (rflag) {
+            const uint64_t gid = (uint64_t)(A.env_id_offset + env);
+            const float up = A.rand_pos ? A.rand_pos[env * D + d] : reset_uniform(A.seed, rcounter, gid, d, 0);
+            const float uv = A.rand_vel ? A.rand_vel[env * D + d] : reset_uniform(A.seed, rcounter, gid, d, 1);
+            const float noise = __fadd_rn(__fmul_rn(0.2f - (-0.2f), up), -0.2f);          // locomotion.py:120
+            qv = __fadd_rn(A.init_q[env * D + d], noise);
+            qv = fmaxf(fminf(qv, P.dof_limits_upper[d]), P.dof_limits_lower[d]);          // locomotion.py:121-123
+            qdv = __fadd_rn(__fmul_rn(0.1f - (-0.1f), uv), -0.1f);                        // locomotion.py:124
+        }
+        qo = qv; qdo = qdv;
+        effo = s_act[e * D + d] * P.joint_gears[d] * P.power_scale;                       // locomotion.py:109
+        tgo = (TGT && A.targets != nullptr) ? A.targets[env * D + d] : 0.f;
+    };
+#pragma unroll
+    for (int k = 0; k < MAXC; ++k) {
+        qr[k] = 0.f; qdr[k] = 0.f; effr[k] = 0.f;
+        if (TGT) tgtr[k] = 0.f;
+        if (k < np) {
+            float tg;
+            load_joint(M.plink[role][k], qr[k], qdr[k], effr[k], tg);
+            if (TGT) tgtr[k] = tg;
+        }
+    }
+    V3 rpos = {0.f, 0.f, 0.f};
+    Q4 rquat = {1.f, 0.f, 0.f, 0.f};
+    V6 rvel = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
+    if (role == 0) {
+#pragma unroll
+        for (int t = 1; t < kRT; ++t) {
+            tq0[t - 1] = 0.f; tq1[t - 1] = 0.f; tq2[t - 1] = 0.f; tq3[t - 1] = 0.f;
+            if (t < M.ntrunk) load_joint(M.tlink[t], tq0[t - 1], tq1[t - 1], tq2[t - 1], tq3[t - 1]);
+        }
+        if (rflag) {
+            rpos = {A.init_pos[env * 3], A.init_pos[env * 3 + 1], A.init_pos[env * 3 + 2]};
+            const float4 t = *reinterpret_cast<const float4*>(A.init_rot + env * 4);
+            rquat = {t.x, t.y, t.z, t.w};
+            if (valid) {
+                // potentials = -|| (targets - initial_root_pos)_xy || / dt         (locomotion.py:136-139)
+                const float tx = __fsub_rn(P.targets[0], rpos.x);
+                const float ty = __fsub_rn(P.targets[1], rpos.y);
+                const float nrm = sqrtf(fmaf(0.0f, 0.0f, fmaf(ty, ty, __fmul_rn(tx, tx))));
+                const float pp = __fdiv_rn(-nrm, P.dt);
+                A.prev_pot[env] = pp;
+                A.pot[env] = pp;
+                A.reset[env] = 0;     // locomotion.py:142-143
+                A.progress[env] = 0;
+            }
+        } else {
+            rpos = {s_pos[e * 3], s_pos[e * 3 + 1], s_pos[e * 3 + 2]};
+            const float4 t = *reinterpret_cast<const float4*>(s_quat + e * 4);
+            rquat = {t.x, t.y, t.z, t.w};
+            const float* vv = s_vel + e * 6;
+            rvel = {{vv[3], vv[4], vv[5], vv[0], vv[1], vv[2]}};
+        }
+    }
+    __syncthreads();  // the staging tile is dead from here on: the scratch regions below alias it
+
+    // ================= scratch of this group ============================================================
+    float* const G0 = dynsm + (size_t)grp * M.group_floats * 32 + lane;
+    float* const xI = G0 + M.oI * 32;   // [nslots][27]   hand-over: I^a, p^a of the chains (+ own inertia of a trunk link)
+    float* const xA = G0 + M.oA * 32;   // [npub][6]      a' of the trunk links that chains attach to
+    float* const xK = G0 + M.oK * 32;   // [ntrunk][19]   trunk kinematics; rows t >= 1 become (s, U/d, u''') in S2
+    float* const xT = G0 + M.oT * 32;   // [ntrunk-1][4]  trunk q, qd, effort, target
+    float* const xS = G0 + M.oS * 32;   // [nsensors][7]  frame of the sensor links (last substep)
+    float* const xM = G0 + M.oM * 32;   // [2]            root height, non-finite flag
+    float* const LS = G0 + (M.oL + role * MAXC * kPu) * 32;  // [MAXC][13] link slots of this role
+    const int ntrunk = M.ntrunk;
+    const bool fixed_base = M.fixed_base != 0;
+    const V3 grav = {M.gravity[0], M.gravity[1], M.gravity[2]};
+    const bool has_tgt = TGT && A.targets != nullptr;
+    if (role == 0) {
+#pragma unroll
+        for (int t = 1; t < kRT; ++t) {
+            if (t < ntrunk) {
+                xT[((t - 1) * 4 + 0) * 32] = tq0[t - 1];
+                xT[((t - 1) * 4 + 1) * 32] = tq1[t - 1];
+                xT[((t - 1) * 4 + 2) * 32] = tq2[t - 1];
+                xT[((t - 1) * 4 + 3) * 32] = tq3[t - 1];
+            }
+        }
+        xM[32] = 0.f;
+    }
+    float sw[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // sensor wrench of this role's sensor chain
+    int sw_idx = -1;
+    V6 vatt = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}}, batt = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
+
+    for (int step = 0; step < A.substeps; ++step) {
+        const bool last = (step == A.substeps - 1);
+        // ---- S0 (role 0): trunk kinematics -> xK ------------------------------------------------------------
+        if (role == 0) {
+            KinCtx c;
+            c.q = rquat; c.R = qmat(rquat); c.p = {0.f, 0.f, 0.f}; c.v = rvel;
+            {
+                const V3 wxv = cross(ang(rvel), lin(rvel));
+                c.b = {{0.f, 0.f, 0.f, -wxv.x, -wxv.y, -wxv.z}};
+            }
+            xM[0] = rpos.z;
+            for (int t = 0; t < ntrunk; ++t) {
+                if (t > 0) kin_step(M, M.tlink[t], xT[((t - 1) * 4 + 0) * 32], xT[((t - 1) * 4 + 1) * 32], c);
+                float* k = xK + t * kKin * 32;
+                k[0] = c.q.w; k[32] = c.q.x; k[64] = c.q.y; k[96] = c.q.z;
+                k[4 * 32] = c.p.x; k[5 * 32] = c.p.y; k[6 * 32] = c.p.z;
+#pragma unroll
+                for (int j = 0; j < 6; ++j) { k[(7 + j) * 32] = c.v.a[j]; k[(13 + j) * 32] = c.b.a[j]; }
+            }
+        }
+        group_barrier(bar_id, GT);  // K
+        const float root_z = xM[0];
+
+        // ---- S1: own chains (+ the own inertia of one trunk link, if this role was given one) ---------------
+        if (M.own_t[role] != 255) {
+            const int t = M.own_t[role];
+            const float* k = xK + t * kKin * 32;
+            const M3 R = qmat(Q4{k[0], k[32], k[64], k[96]});
+            const V3 p = {k[4 * 32], k[5 * 32], k[6 * 32]};
+            V6 v, b;
+#pragma unroll
+            for (int j = 0; j < 6; ++j) { v.a[j] = k[(7 + j) * 32]; b.a[j] = k[(13 + j) * 32]; }
+            S6 IA;
+            V6 pA;
+            own_inertia(M, M.tlink[t], R, p, v, b, root_z, dt, grav, IA, pA);
+            float* dst = xI + M.own_slot[role] * kHand * 32;  // first writer of the slot: the chains below add to it
+#pragma unroll
+            for (int j = 0; j < 21; ++j) dst[j * 32] = IA.a[j];
+#pragma unroll
+            for (int j = 0; j < 6; ++j) dst[(21 + j) * 32] = pA.a[j];
+        }
+        for (int k0 = 0; k0 < np;) {
+            // kinematics head -> tip; frames into the link slots
+            KinCtx c;
+            {
+                const float* k = xK + M.patt[role][k0] * kKin * 32;
+                c.q = {k[0], k[32], k[64], k[96]};
+                c.R = qmat(c.q);
+                c.p = {k[4 * 32], k[5 * 32], k[6 * 32]};
+#pragma unroll
+                for (int j = 0; j < 6; ++j) { c.v.a[j] = k[(7 + j) * 32]; c.b.a[j] = k[(13 + j) * 32]; }
+            }
+            int k1 = k0;
+            for (;; ++k1) {
+                const int link = M.plink[role][k1];
+                kin_step(M, link, rsel(qr, k1), rsel(qdr, k1), c);
+                float* slot = LS + k1 * kPu * 32;
+                slot[0] = c.q.w; slot[32] = c.q.x; slot[64] = c.q.y; slot[96] = c.q.z;
+                slot[4 * 32] = c.p.x; slot[5 * 32] = c.p.y; slot[6 * 32] = c.p.z;
+                if (M.pflag[role][k1] & kPTip) break;
+            }
+            const int cflag = M.pflag[role][k0];
+            if (last && (cflag & kPSensor)) {  // the foot's frame is needed again after the downward sweep
+                const int link = M.plink[role][k1];
+                float* f = xS + M.sensor_of_link[link] * 7 * 32;
+                f[0] = c.q.w; f[32] = c.q.x; f[64] = c.q.y; f[96] = c.q.z;
+                f[4 * 32] = c.p.x; f[5 * 32] = c.p.y; f[6 * 32] = c.p.z;
+            }
+            // articulated inertia tip -> head in registers; (v, b) are walked back up with it
+            V6 v = c.v, b = c.b;
+            S6 carryI;
+            V6 carryP;
+            for (int kk = k1; kk >= k0; --kk) {
+                const int link = M.plink[role][kk];
+                float* slot = LS + kk * kPu * 32;
+                const M3 R = qmat(Q4{slot[0], slot[32], slot[64], slot[96]});
+                const V3 p = {slot[4 * 32], slot[5 * 32], slot[6 * 32]};
+                S6 IA;
+                V6 pA;
+                own_inertia(M, link, R, p, v, b, root_z, dt, grav, IA, pA);
+                if (kk != k1) {
+#pragma unroll
+                    for (int j = 0; j < 21; ++j) IA.a[j] += carryI.a[j];
+#pragma unroll
+                    for (int j = 0; j < 6; ++j) pA.a[j] += carryP.a[j];
+                }
+                joint_reduce(M, link, R, p, v, b, rsel(qr, kk), rsel(qdr, kk), rsel(effr, kk), has_tgt,
+                             TGT ? rsel(tgtr, kk) : 0.f, dt, IA, pA, slot);
+                carryI = IA; carryP = pA;
+            }
+            if (last && (cflag & kPSensor)) { vatt = v; batt = b; }  // = the attach link's v, b
+            {   // hand the head's I^a, p^a to the trunk
+                float* dst = xI + M.pslot[role][k0] * kHand * 32;
+                if (cflag & kPSlotFirst) {
+#pragma unroll
+                    for (int j = 0; j < 21; ++j) dst[j * 32] = carryI.a[j];
+#pragma unroll
+                    for (int j = 0; j < 6; ++j) dst[(21 + j) * 32] = carryP.a[j];
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 21; ++j) dst[j * 32] += carryI.a[j];
+#pragma unroll
+                    for (int j = 0; j < 6; ++j) dst[(21 + j) * 32] += carryP.a[j];
+                }
+            }
+            k0 = k1 + 1;
+        }
+        group_barrier(bar_id, GT);  // H
+
+        // ---- S2 (role 0): trunk tip -> root, root solve, trunk accelerations root -> tip ----------------------
+        if (role == 0) {
+            S6 carryI;
+            V6 carryP;
+            for (int t = ntrunk - 1; t >= 0; --t) {
+                const int link = M.tlink[t];
+                float* k = xK + t * kKin * 32;
+                const M3 R = qmat(Q4{k[0], k[32], k[64], k[96]});
+                const V3 p = {k[4 * 32], k[5 * 32], k[6 * 32]};
+                V6 v, b;
+#pragma unroll
+                for (int j = 0; j < 6; ++j) { v.a[j] = k[(7 + j) * 32]; b.a[j] = k[(13 + j) * 32]; }
+                S6 IA;
+                V6 pA;
+                if (M.town[t]) {  // a chain role already put this link's own inertia into its hand-over slot
+#pragma unroll
+                    for (int j = 0; j < 21; ++j) IA.a[j] = 0.f;
+#pragma unroll
+                    for (int j = 0; j < 6; ++j) pA.a[j] = 0.f;
+                } else {
+                    own_inertia(M, link, R, p, v, b, root_z, dt, grav, IA, pA);
+                }
+                if (t != ntrunk - 1) {
+#pragma unroll
+                    for (int j = 0; j < 21; ++j) IA.a[j] += carryI.a[j];
+#pragma unroll
+                    for (int j = 0; j < 6; ++j) pA.a[j] += carryP.a[j];
+                }
+                for (int h = M.ts_begin[t]; h < M.ts_begin[t + 1]; ++h) {
+                    const float* src = xI + M.ts_slot[h] * kHand * 32;
+#pragma unroll
+                    for (int j = 0; j < 21; ++j) IA.a[j] += src[j * 32];
+#pragma unroll
+                    for (int j = 0; j < 6; ++j) pA.a[j] += src[(21 + j) * 32];
+                }
+                if (t > 0) {
+                    const float* x = xT + (t - 1) * 4 * 32;
+                    joint_reduce(M, link, R, p, v, b, x[0], x[32], x[64], has_tgt, x[96], dt, IA, pA, k);
+                }
+                carryI = IA; carryP = pA;
+            }
+            V6 a0 = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
+            if (!fixed_base) chol6_solve(carryI, carryP, a0);  // a welded base does not accelerate
+            V6 ap = a0;  // a' = a - b; b_root = -(0, w x v)
+            {
+                const V3 wxv = cross(ang(rvel), lin(rvel));
+                ap.a[3] += wxv.x; ap.a[4] += wxv.y; ap.a[5] += wxv.z;
+            }
+            for (int t = 0; t < ntrunk; ++t) {
+                if (t > 0) {
+                    const float* k = xK + t * kKin * 32;
+                    float acc = k[12 * 32];
+#pragma unroll
+                    for (int j = 0; j < 6; ++j) acc = fmaf(-k[(6 + j) * 32], ap.a[j], acc);
+#pragma unroll
+                    for (int j = 0; j < 6; ++j) ap.a[j] = fmaf(k[j * 32], acc, ap.a[j]);
+                    float* x = xT + (t - 1) * 4 * 32;
+                    float qd = fmaf(dt, acc, x[32]);
+                    qd = fminf(fmaxf(qd, -M.max_qd), M.max_qd);
+                    x[32] = qd;
+                    x[0] = fmaf(dt, qd, x[0]);
+                }
+                if (M.tpub[t] != 255) {
+                    float* dst = xA + M.tpub[t] * 6 * 32;
+#pragma unroll
+                    for (int j = 0; j < 6; ++j) dst[j * 32] = ap.a[j];
+                }
+            }
+            if (!fixed_base) integrate_root(M, a0, dt, rpos, rquat, rvel);
+        }
+        group_barrier(bar_id, GT);  // A
+
+        // ---- S3: accelerations down the own chains, joint integration, foot sensors ---------------------------
+        for (int k0 = 0; k0 < np;) {
+            const int cflag = M.pflag[role][k0];
+            const bool sens_chain = last && (cflag & kPSensor) && A.sens != nullptr;
+            V6 ap;
+            {
+                const float* src = xA + M.tpub[M.patt[role][k0]] * 6 * 32;
+#pragma unroll
+                for (int j = 0; j < 6; ++j) ap.a[j] = src[j * 32];
+            }
+            V6 v = vatt, b = batt;
+            int k1 = k0;
+            for (;; ++k1) {
+                const float* slot = LS + k1 * kPu * 32;
+                V6 s;
+#pragma unroll
+                for (int j = 0; j < 6; ++j) s.a[j] = slot[j * 32];
+                float qdd = slot[12 * 32];
+#pragma unroll
+                for (int j = 0; j < 6; ++j) qdd = fmaf(-slot[(6 + j) * 32], ap.a[j], qdd);
+#pragma unroll
+                for (int j = 0; j < 6; ++j) ap.a[j] = fmaf(s.a[j], qdd, ap.a[j]);
+                const float qd0 = rsel(qdr, k1);
+                if (sens_chain) {  // rebuild the start-of-substep v, b down to the foot
+#pragma unroll
+                    for (int j = 0; j < 6; ++j) v.a[j] = fmaf(s.a[j], qd0, v.a[j]);
+                    const V6 cc = velocity_product(v, s, qd0);
+#pragma unroll
+                    for (int j = 0; j < 6; ++j) b.a[j] += cc.a[j];
+                }
+                float qd = fmaf(dt, qdd, qd0);
+                qd = fminf(fmaxf(qd, -M.max_qd), M.max_qd);
+                rput(qdr, k1, qd);
+                rput(qr, k1, fmaf(dt, qd, rsel(qr, k1)));
+                if (M.pflag[role][k1] & kPTip) break;
+            }
+            if (sens_chain) {
+                const int link = M.plink[role][k1];
+                sw_idx = M.sensor_of_link[link];
+                const float* f = xS + sw_idx * 7 * 32;
+                const M3 R = qmat(Q4{f[0], f[32], f[64], f[96]});
+                const V3 p = {f[4 * 32], f[5 * 32], f[6 * 32]};
+                V6 a;
+#pragma unroll
+                for (int j = 0; j < 6; ++j) a.a[j] = ap.a[j] + b.a[j];
+                sensor_wrench(M, link, R, p, v, b, a, root_z, dt, sw);
+            }
+            k0 = k1 + 1;
+        }
+    }
+
+    // ================= non-finite guard (agreed across the roles of an env) ================================
+    bool bad = false;
+#pragma unroll
+    for (int k = 0; k < MAXC; ++k) bad = bad || !(isfinite(qr[k]) && isfinite(qdr[k]));
+    float tq[kRT - 1], tqd[kRT - 1];
+    if (role == 0) {
+        bad = bad || !(isfinite(rpos.x) && isfinite(rpos.y) && isfinite(rpos.z) && isfinite(rquat.w) &&
+                       isfinite(rquat.x) && isfinite(rquat.y) && isfinite(rquat.z));
+#pragma unroll
+        for (int j = 0; j < 6; ++j) bad = bad || !isfinite(rvel.a[j]);
+#pragma unroll
+        for (int t = 1; t < kRT; ++t) {
+            tq[t - 1] = 0.f; tqd[t - 1] = 0.f;
+            if (t < ntrunk) {
+                tq[t - 1] = xT[((t - 1) * 4 + 0) * 32];
+                tqd[t - 1] = xT[((t - 1) * 4 + 1) * 32];
+                bad = bad || !(isfinite(tq[t - 1]) && isfinite(tqd[t - 1]));
+            }
+        }
+    }
+    if (bad) xM[32] = 1.f;  // (zeroed by role 0 before the first barrier K)
+    group_barrier(bar_id, GT);
+    bad = xM[32] != 0.f;
+    if (bad && !fixed_base) {  // parked below the termination height so that the observation pass flags it for reset
+        rpos = {0.f, 0.f, -1.f};
+        rquat = {1.f, 0.f, 0.f, 0.f};
+        rvel = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
+    }
+    if (bad && role == 0 && valid) atomicAdd(&g_nonfinite_envs, 1ull);
+    __syncthreads();  // every group is done with its scratch: the output tile below aliases it
+
+    // ================= output tile ============================================================================
+    const int S6n = A.S * 6, OBS = A.OBS;
+    float* o_q = dynsm;
+    float* o_qd = o_q + EPC * D;
+    float* o_sens = o_qd + EPC * D;
+    float* o_pos = o_sens + EPC * S6n;
+    float* o_quat = o_pos + EPC * 3;
+    float* o_vel = o_quat + EPC * 4;
+    float* o_act = o_vel + EPC * 6;         // epilogue only from here on
+    float* o_obs = o_act + EPC * D;
+    float* o_up = o_obs + EPC * OBS;
+    float* o_head = o_up + EPC * 3;
+    float* o_pot = o_head + EPC * 3;
+    float* s_part = o_pot + EPC;            // [3 reductions][4 quarters][EPC]
+    float* s_lo = s_part + 12 * EPC;        // per-dof constants
+    float* s_hi = s_lo + 32;
+    float* s_ratio = s_hi + 32;
+    float* s_rcp = s_ratio + 32;
+    if (valid) {
+#pragma unroll
+        for (int k = 0; k < MAXC; ++k) {
+            if (k < np) {
+                const int d = M.dof[M.plink[role][k]];
+                o_q[e * D + d] = bad ? 0.f : qr[k];
+                o_qd[e * D + d] = bad ? 0.f : qdr[k];
+            }
+        }
+        if (role == 0) {
+#pragma unroll
+            for (int t = 1; t < kRT; ++t) {
+                if (t < ntrunk) {
+                    const int d = M.dof[M.tlink[t]];
+                    o_q[e * D + d] = bad ? 0.f : tq[t - 1];
+                    o_qd[e * D + d] = bad ? 0.f : tqd[t - 1];
+                }
+            }
+            o_pos[e * 3] = rpos.x; o_pos[e * 3 + 1] = rpos.y; o_pos[e * 3 + 2] = rpos.z;
+            *reinterpret_cast<float4*>(o_quat + e * 4) = make_float4(rquat.w, rquat.x, rquat.y, rquat.z);
+            float* vv = o_vel + e * 6;
+            vv[0] = rvel.a[3]; vv[1] = rvel.a[4]; vv[2] = rvel.a[5];
+            vv[3] = rvel.a[0]; vv[4] = rvel.a[1]; vv[5] = rvel.a[2];
+        }
+        if (sw_idx >= 0) {
+#pragma unroll
+            for (int j = 0; j < 6; ++j) o_sens[e * S6n + sw_idx * 6 + j] = bad ? 0.f : sw[j];
+        }
+    }
+    if (A.epi) {
+        for (int i = tid; i < cnt * D; i += NT) o_act[i] = A.actions[e0 * D + i];
+        if (tid < 32) {
+            s_lo[tid] = tid < D ? P.dof_limits_lower[tid] : 0.0f;
+            s_hi[tid] = tid < D ? P.dof_limits_upper[tid] : 0.0f;
+            s_ratio[tid] = tid < D ? P.motor_effort_ratio[tid] : 0.0f;
+            s_rcp[tid] = tid < D ? 1.0f / (P.dof_limits_upper[tid] - P.dof_limits_lower[tid]) : 0.0f;
+        }
+    }
+    __syncthreads();
+
+    // ================= epilogue: observations, reward, termination (locomotion_math.cuh = K1's arithmetic) ==
+    float st_rew = 0.0f, st_done = 0.0f, st_len = 0.0f;
+    if (A.epi) {
+        const bool closed = P.closed_form_angles != 0;
+        if (valid) {
+            float* row = o_obs + e * OBS;
+            for (int r = role; r < 4; r += NR) {  // quarter r of env e: K1's thread (e, r)
+                lm::Partial part;
+                lm::partial_init(part);
+                for (int k = 0; k < (D + 3) / 4; ++k) {
+                    const int d = lm::owned_index_rt(D, r, k, e);
+                    if (d < D) {
+                        const float qs = lm::unscale(o_q[e * D + d], s_lo[d], s_hi[d], s_rcp[d]);
+                        const float dv = lm::mul(o_qd[e * D + d], P.dof_vel_scale);
+                        const float a = o_act[e * D + d];
+                        row[12 + d] = qs;
+                        row[12 + D + d] = dv;
+                        row[12 + 2 * D + S6n + d] = a;
+                        lm::partial_add(P, part, qs, dv, a, s_ratio[d]);
+                    }
+                }
+                lm::partial_finish(P, part);
+                s_part[(0 * 4 + r) * EPC + e] = part.limit;
+                s_part[(1 * 4 + r) * EPC + e] = part.act;
+                s_part[(2 * 4 + r) * EPC + e] = part.elec;
+                for (int k = 0; k < (S6n + 3) / 4; ++k) {
+                    const int j = lm::owned_index_rt(S6n, r, k, e);
+                    if (j < S6n) row[12 + 2 * D + j] = lm::mul(o_sens[e * S6n + j], P.contact_force_scale);
+                }
+                const float4 q4 = *reinterpret_cast<const float4*>(o_quat + 4 * e);
+                const float rot[4] = {q4.x, q4.y, q4.z, q4.w};
+                float tqq[4];
+                lm::torso_quat(P, rot, tqq);
+                const float px = o_pos[3 * e], py = o_pos[3 * e + 1], pz = o_pos[3 * e + 2];
+                if (r == 0) {
+                    lm::root_part0(P, tqq, closed, row, o_up + 3 * e);
+                } else if (r == 1) {
+                    lm::root_part1(P, tqq, px, py, pz, closed, row);
+                } else if (r == 2) {
+                    lm::root_part2(P, tqq, px, py, row, o_head + 3 * e, o_pot + e);
+                } else {
+                    const float lin3[3] = {o_vel[6 * e], o_vel[6 * e + 1], o_vel[6 * e + 2]};
+                    const float ang3[3] = {o_vel[6 * e + 3], o_vel[6 * e + 4], o_vel[6 * e + 5]};
+                    lm::root_part3(P, tqq, pz, lin3, ang3, row);
+                }
+            }
+        }
+        __syncthreads();
+        if (role == 0 && valid) {  // reward + termination: one thread per env, coalesced [N] accesses
+            const float* row = o_obs + e * OBS;
+            float red[3];
+#pragma unroll
+            for (int c = 0; c < 3; ++c)
+                red[c] = lm::combine4(s_part[(c * 4 + 0) * EPC + e], s_part[(c * 4 + 1) * EPC + e],
+                                      s_part[(c * 4 + 2) * EPC + e], s_part[(c * 4 + 3) * EPC + e]);
+            const float prev = A.pot[env];
+            float total;
+            long long prog, rst;
+            lm::reward_done(P, row[0], row[10], row[11], o_pot[e], prev, red, A.progress[env], A.reset[env], total,
+                            prog, rst);
+            A.progress[env] = prog;
+            A.reset[env] = rst;
+            A.rew[env] = total;
+            A.prev_pot[env] = prev;
+            A.pot[env] = o_pot[e];
+            st_rew = total;
+            st_done = rst != 0 ? 1.0f : 0.0f;
+            st_len = rst != 0 ? (float)prog : 0.0f;
+        }
+        if (A.stats != nullptr && role == 0) {  // warp-uniform
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                st_rew += __shfl_xor_sync(0xffffffffu, st_rew, o);
+                st_done += __shfl_xor_sync(0xffffffffu, st_done, o);
+                st_len += __shfl_xor_sync(0xffffffffu, st_len, o);
+            }
+            if (lane == 0) { s_stat[grp * 3 + 0] = st_rew; s_stat[grp * 3 + 1] = st_done; s_stat[grp * 3 + 2] = st_len; }
+        }
+        if (P.clip_obs < INFINITY) {  // uniform; the stored rows are clamped after the metrics were evaluated
+            __syncthreads();
+            const float c = P.clip_obs;
+            for (int i = tid; i < cnt * OBS; i += NT) o_obs[i] = lm::clampf(o_obs[i], c);
+        }
+    }
+
+    // ================= drain ==================================================================================
+    if (bulk) {
+        fence_async_smem();
+        __syncthreads();
+        if (tid == 0) {
+            bulk_s2g(A.q + e0 * D, o_q, EPC * D * 4);
+            bulk_s2g(A.qd + e0 * D, o_qd, EPC * D * 4);
+            if (A.sens != nullptr && S6n > 0) bulk_s2g(A.sens + e0 * S6n, o_sens, EPC * S6n * 4);
+            bulk_s2g(A.pos + e0 * 3, o_pos, EPC * 12);
+            bulk_s2g(A.quat + e0 * 4, o_quat, EPC * 16);
+            bulk_s2g(A.vel + e0 * 6, o_vel, EPC * 24);
+            if (A.epi) {
+                bulk_s2g(A.obs + e0 * OBS, o_obs, EPC * OBS * 4);
+                bulk_s2g(A.up + e0 * 3, o_up, EPC * 12);
+                bulk_s2g(A.head + e0 * 3, o_head, EPC * 12);
+            }
+            bulk_commit();
+        }
+    } else {
+        __syncthreads();
+        for (int i = tid; i < cnt * D; i += NT) { A.q[e0 * D + i] = o_q[i]; A.qd[e0 * D + i] = o_qd[i]; }
+        if (A.sens != nullptr)
+            for (int i = tid; i < cnt * S6n; i += NT) A.sens[e0 * S6n + i] = o_sens[i];
+        for (int i = tid; i < cnt * 3; i += NT) A.pos[e0 * 3 + i] = o_pos[i];
+        for (int i = tid; i < cnt * 4; i += NT) A.quat[e0 * 4 + i] = o_quat[i];
+        for (int i = tid; i < cnt * 6; i += NT) A.vel[e0 * 6 + i] = o_vel[i];
+        if (A.epi) {
+            for (int i = tid; i < cnt * OBS; i += NT) A.obs[e0 * OBS + i] = o_obs[i];
+            for (int i = tid; i < cnt * 3; i += NT) { A.up[e0 * 3 + i] = o_up[i]; A.head[e0 * 3 + i] = o_head[i]; }
+        }
+    }
+    if (tid == 0) {
+        if (A.epi && A.stats != nullptr) {
+            double r = 0.0, d = 0.0, l = 0.0;
+            for (int w = 0; w < EPC / 32; ++w) {
+                r += (double)s_stat[w * 3 + 0];
+                d += (double)s_stat[w * 3 + 1];
+                l += (double)s_stat[w * 3 + 2];
+            }
+            double* slot = A.stats + (blockIdx.x % OIGE_STATS_SLOTS) * 4;
+            atomicAdd(slot + 0, r);
+            atomicAdd(slot + 1, d);
+            atomicAdd(slot + 2, l);
+            atomicAdd(slot + 3, (double)cnt);
+        }
+        if (A.bump && A.counter_dev != nullptr) {
+            // every CTA read the reset counter in its prologue; the last one to get here advances it for the next
+            // replay of a captured step (ticket in counter_dev[1])
+            __threadfence();
+            const unsigned long long t = atomicAdd(A.counter_dev + 1, 1ull);
+            if (t == (unsigned long long)gridDim.x - 1) {
+                A.counter_dev[1] = 0ull;
+                A.counter_dev[0] += 1ull;
+            }
+        }
+        if (bulk) bulk_wait_read0();  // smem must stay alive until the TMA engine has read it
+    }
+}

@@ -20,61 +20,16 @@
 // FMA (vector norm, cross product) use explicit fmaf.
 #include <math.h>
 
+#include <atomic>
+
+#include "locomotion_math.cuh"
 #include "oige_common.cuh"
 
 namespace oige {
 
 namespace {
 
-constexpr float kTwoPi = 6.283185307179586f;  // (float)(2*pi), as torch casts the python scalar
-
-__device__ __forceinline__ float normalize_angle(float x) {  // locomotion.py:190-192
-    return atan2f(sinf(x), cosf(x));
-}
-
-// torch.cross CPU kernel contracts a1*b2 - a2*b1 into fma(a1, b2, -(a2*b1))
-__device__ __forceinline__ void cross3(const float a[3], const float b[3], float c[3]) {
-    c[0] = fmaf(a[1], b[2], -(a[2] * b[1]));
-    c[1] = fmaf(a[2], b[0], -(a[0] * b[2]));
-    c[2] = fmaf(a[0], b[1], -(a[1] * b[0]));
-}
-
-// v(2w^2-1) +- 2w (q x v) + 2 q (q.v)      (quat_rotate / quat_rotate_inverse)
-template <bool INVERSE>
-__device__ __forceinline__ void quat_rotate(const float q[4], const float v[3], float out[3]) {
-    const float w = q[0];
-    const float qv[3] = {q[1], q[2], q[3]};
-    const float s = 2.0f * (w * w) - 1.0f;
-    float cr[3];
-    cross3(qv, v, cr);
-    const float dot = (qv[0] * v[0] + qv[1] * v[1]) + qv[2] * v[2];
-#pragma unroll
-    for (int i = 0; i < 3; ++i) {
-        const float a = v[i] * s;
-        const float b = (cr[i] * w) * 2.0f;
-        const float c = (qv[i] * dot) * 2.0f;
-        out[i] = INVERSE ? ((a - b) + c) : ((a + b) + c);
-    }
-}
-
-// factored 9-multiply Hamilton product (quat_mul)
-__device__ __forceinline__ void quat_mul(const float a[4], const float b[4], float o[4]) {
-    const float w1 = a[0], x1 = a[1], y1 = a[2], z1 = a[3];
-    const float w2 = b[0], x2 = b[1], y2 = b[2], z2 = b[3];
-    const float ww = (z1 + x1) * (x2 + y2);
-    const float yy = (w1 - y1) * (w2 + z2);
-    const float zz = (w1 + y1) * (w2 - z2);
-    const float xx = (ww + yy) + zz;
-    const float qq = 0.5f * (xx + (z1 - x1) * (x2 - y2));
-    o[0] = (qq - ww) + (z1 - y1) * (y2 - z2);
-    o[1] = (qq - xx) + (x1 + w1) * (x2 + w2);
-    o[2] = (qq - yy) + (w1 - x1) * (y2 + z2);
-    o[3] = (qq - zz) + (z1 + y1) * (w2 - x2);
-}
-
-__device__ __forceinline__ float clampf(float v, float c) {  // torch.clamp semantics (NaN propagates)
-    return v < -c ? -c : (v > c ? c : v);
-}
+using namespace lm;  // exact-order arithmetic shared with the whole-step kernel (locomotion_math.cuh)
 
 template <int D, int S>
 struct Tile {
@@ -114,53 +69,6 @@ __device__ __forceinline__ void coop_load(T* dst, const T* src, int count, int t
 template <typename T>
 __device__ __forceinline__ void coop_store(T* dst, const T* src, int count, int tid, int nthr) {
     for (int i = tid; i < count; i += nthr) dst[i] = src[i];
-}
-
-// Correctly rounded a / b from y = RN(1/b): q0 = RN(a*y), r = a - q0*b (exact, one FMA), q1 = RN(q0 + r*y)
-// (Markstein 1990: q1 == RN(a/b) whenever y is the correctly rounded reciprocal and nothing over/underflows).
-// Three instructions instead of the ~15 of the IEEE division subroutine.  Inputs outside the normal
-// range (|a/b| near the fp32 limits, non-finite values) take the IEEE path so NaN/inf propagate as in torch.
-__device__ __forceinline__ float div_rn(float a, float b, float y) {
-    const float q0 = a * y;
-    const float aq = fabsf(q0);
-    if (!(aq > 1e-30f && aq < 1e30f)) return a / b;
-    const float r = fmaf(-q0, b, a);
-    return fmaf(r, y, q0);
-}
-
-// wrap an angle x (|x| < 4 pi) into (-pi, pi] the way atan2(sin x, cos x) does, without the three
-// transcendentals: sin/cos see the FLOAT x, so the exact result is x -/+ 2*pi (true pi), i.e.
-// (x -/+ 2pi_f) +/- (2pi_f - 2pi).  Agrees with the literal chain to 1-2 ulp (tests run both).
-__device__ __forceinline__ float wrap_pi(float x) {
-    constexpr float kPi = 3.14159265358979f;  // rounds to pi_f, the smallest float above pi
-    constexpr float kDelta = 1.7484555e-7f;   // 2pi_f - 2pi
-    if (x >= kPi) return (x - kTwoPi) + kDelta;
-    if (x < -kPi) return (x + kTwoPi) - kDelta;
-    return x;
-}
-
-__device__ __forceinline__ float norm_angle(float x, bool closed_form) {
-    return closed_form ? wrap_pi(x) : normalize_angle(x);
-}
-
-// atan2 result r in [-pi, pi]; torch's `r % (2*pi)` (python remainder) is r or r + 2pi_f
-__device__ __forceinline__ float mod_2pi_of_atan2(float r) { return r < 0.0f ? r + kTwoPi : r; }
-
-// Which of the LEN per-env columns thread r of env e handles in iteration k.  The lanes of a warp
-// walk consecutive envs, i.e. shared-memory stride LEN words:
-//   LEN odd        -> r + 4k: the stride is coprime with the 32 banks, conflict-free as is;
-//   LEN % 8 == 0   -> the stride only reaches 4 banks, so ownership is skewed by the env index
-//                     (column = 8m + ((2r + j + (e >> 2)) & 7)): 8 consecutive env groups hit the 8
-//                     residues and a warp covers all 32 banks.  Each thread still owns exactly
-//                     LEN/4 columns of its env; for the Ant (2 dofs per thread) the partial sums
-//                     are order-independent.
-template <int LEN>
-__device__ __forceinline__ int owned_index(int r, int k, int e) {
-    if constexpr (LEN % 8 == 0) {
-        return 8 * (k >> 1) + ((2 * r + (k & 1) + (e >> 2)) & 7);
-    } else {
-        return r + 4 * k;
-    }
 }
 
 // Block = 4*E threads.  After the flat phase every env of the tile is served by FOUR threads that
@@ -266,92 +174,46 @@ __global__ void __launch_bounds__(4 * E) obs_reward_reset_kernel(const __grid_co
     const bool closed = P.closed_form_angles != 0;
     if (live) {
         float* row = o_obs + e * OBS;
-        float p_limit = 0.0f, p_act = 0.0f, p_elec = 0.0f;
-        int p_count = 0;
+        Partial part;
+        partial_init(part);
 #pragma unroll
         for (int k = 0; k < (D + 3) / 4; ++k) {
             const int d = owned_index<D>(r, k, e);
             if (d < D) {
-                const float lo = s_lo[d], hi = s_hi[d];
-                const float num = (2.0f * s_q[e * D + d] - hi) - lo;
-                const float qs = div_rn(num, hi - lo, s_rcp[d]);  // maths.unscale
-                const float dv = s_qd[e * D + d] * P.dof_vel_scale;
+                const float qs = unscale(s_q[e * D + d], s_lo[d], s_hi[d], s_rcp[d]);  // maths.unscale
+                const float dv = mul(s_qd[e * D + d], P.dof_vel_scale);
                 const float a = s_act[e * D + d];
                 row[12 + d] = qs;
                 row[12 + D + d] = dv;
                 row[12 + 2 * D + 6 * S + d] = a;
-                const float ratio = s_ratio[d];
-                if (P.limit_cost_kind == OIGE_LIMIT_COST_ANT) {
-                    p_count += (qs > 0.99f) ? 1 : 0;  // ant.py:95
-                } else {                               // humanoid.py:123-126 (masked-out terms are exact zeros)
-                    const float aq = fabsf(qs);
-                    const float sc = div_rn(P.joints_at_limit_cost_scale * (aq - 0.98f), 0.02f, 50.0f) * ratio;
-                    p_limit = p_limit + (aq > 0.98f ? sc : 0.0f);
-                }
-                p_act = p_act + a * a;
-                p_elec = p_elec + fabsf(a * dv) * ratio;
+                partial_add(P, part, qs, dv, a, s_ratio[d]);
             }
         }
-        if (P.limit_cost_kind == OIGE_LIMIT_COST_ANT) p_limit = (float)p_count;
-        s_part[(0 * 4 + r) * E + e] = p_limit;
-        s_part[(1 * 4 + r) * E + e] = p_act;
-        s_part[(2 * 4 + r) * E + e] = p_elec;
+        partial_finish(P, part);
+        s_part[(0 * 4 + r) * E + e] = part.limit;
+        s_part[(1 * 4 + r) * E + e] = part.act;
+        s_part[(2 * 4 + r) * E + e] = part.elec;
 #pragma unroll
         for (int k = 0; k < (6 * S + 3) / 4; ++k) {
             const int j = owned_index<6 * S>(r, k, e);
-            if (j < 6 * S) row[12 + 2 * D + j] = s_sens[e * 6 * S + j] * P.contact_force_scale;
+            if (j < 6 * S) row[12 + 2 * D + j] = mul(s_sens[e * 6 * S + j], P.contact_force_scale);
         }
 
         const float4 q4 = *reinterpret_cast<const float4*>(s_quat + 4 * e);
         const float rot[4] = {q4.x, q4.y, q4.z, q4.w};
         float tq[4];
-        quat_mul(rot, P.inv_start_rot, tq);  // compute_heading_and_up: torso_quat
-        const float w = tq[0], x = tq[1], y = tq[2], z = tq[3];
+        torso_quat(P, rot, tq);
         const float px = s_pos[3 * e], py = s_pos[3 * e + 1], pz = s_pos[3 * e + 2];
         if (r == 0) {
-            const float sinr_cosp = 2.0f * (w * x + y * z);
-            const float cosr_cosp = ((w * w - x * x) - y * y) + z * z;
-            const float roll = mod_2pi_of_atan2(atan2f(sinr_cosp, cosr_cosp));
-            row[8] = norm_angle(roll, closed);
-            float upv[3];
-            quat_rotate<false>(tq, P.basis_vec1, upv);
-            row[10] = upv[2];  // up_proj
-            o_up[3 * e] = upv[0];
-            o_up[3 * e + 1] = upv[1];
-            o_up[3 * e + 2] = upv[2];
+            root_part0(P, tq, closed, row, o_up + 3 * e);
         } else if (r == 1) {
-            const float siny_cosp = 2.0f * (w * z + x * y);
-            const float cosy_cosp = ((w * w + x * x) - y * y) - z * z;
-            const float yaw = mod_2pi_of_atan2(atan2f(siny_cosp, cosy_cosp));
-            const float walk = P.walk_target_uses_z ? atan2f(P.targets[2] - pz, P.targets[0] - px)
-                                                    : atan2f(P.targets[1] - py, P.targets[0] - px);
-            row[7] = norm_angle(yaw, closed);
-            row[9] = norm_angle(walk - yaw, closed);
+            root_part1(P, tq, px, py, pz, closed, row);
         } else if (r == 2) {
-            // heading: normalize(to_target) . quat_rotate(torso_quat, basis_vec0)
-            const float tx = P.targets[0] - px, ty = P.targets[1] - py, tz = 0.0f;
-            const float nrm = sqrtf(fmaf(tz, tz, fmaf(ty, ty, tx * tx)));  // torch's vector norm is an fma chain
-            const float nc = fmaxf(nrm, 1e-9f);
-            float hdv[3];
-            quat_rotate<false>(tq, P.basis_vec0, hdv);
-            row[11] = (hdv[0] * (tx / nc) + hdv[1] * (ty / nc)) + hdv[2] * (tz / nc);
-            o_head[3 * e] = hdv[0];
-            o_head[3 * e + 1] = hdv[1];
-            o_head[3 * e + 2] = hdv[2];
-            o_pot[e] = (-nrm) / P.dt;  // potentials (locomotion.py:219-223)
+            root_part2(P, tq, px, py, row, o_head + 3 * e, o_pot + e);
         } else {
             const float lin[3] = {s_vel[6 * e], s_vel[6 * e + 1], s_vel[6 * e + 2]};
             const float ang[3] = {s_vel[6 * e + 3], s_vel[6 * e + 4], s_vel[6 * e + 5]};
-            float vloc[3], wloc[3];
-            quat_rotate<true>(tq, lin, vloc);
-            quat_rotate<true>(tq, ang, wloc);
-            row[0] = pz;
-            row[1] = vloc[0];
-            row[2] = vloc[1];
-            row[3] = vloc[2];
-            row[4] = wloc[0] * P.angular_velocity_scale;
-            row[5] = wloc[1] * P.angular_velocity_scale;
-            row[6] = wloc[2] * P.angular_velocity_scale;
+            root_part3(P, tq, pz, lin, ang, row);
         }
     }
     __syncthreads();
@@ -360,32 +222,15 @@ __global__ void __launch_bounds__(4 * E) obs_reward_reset_kernel(const __grid_co
     float st_rew = 0.0f, st_done = 0.0f, st_len = 0.0f;
     if (live && r == 0) {
         const float* row = o_obs + e * OBS;
-        const float pz = row[0], up_proj = row[10], heading_proj = row[11];
-        const float pot = o_pot[e], prev_pot = s_pot[e];
         // the four partial sums of each reduction are combined in a fixed order
         float red[3];
 #pragma unroll
         for (int c = 0; c < 3; ++c)
-            red[c] = ((s_part[(c * 4 + 0) * E + e] + s_part[(c * 4 + 1) * E + e]) + s_part[(c * 4 + 2) * E + e]) +
-                     s_part[(c * 4 + 3) * E + e];
-        const float limit_cost = red[0], actions_cost = red[1], electricity = red[2];
-        // calculate_metrics (locomotion.py:288-321)
-        const float heading_reward = heading_proj > 0.8f ? P.heading_weight : (P.heading_weight * heading_proj) / 0.8f;
-        const float up_reward = up_proj > 0.93f ? (0.0f + P.up_weight) : 0.0f;
-        const float progress_reward = pot - prev_pot;
-        float total = progress_reward + P.alive_reward_scale;
-        total = total + up_reward;
-        total = total + heading_reward;
-        total = total - P.actions_cost_scale * actions_cost;
-        total = total - P.energy_cost_scale * electricity;
-        total = total - limit_cost;
-        const bool fallen = pz < P.termination_height;
-        if (fallen) total = P.death_cost;
-        // rl_task.py:242 then is_done (locomotion.py:266-267; compare in fp32 as torch promotes)
-        const long long prog = s_prog[e] + (P.progress_increment ? 1 : 0);
-        long long rst = s_reset[e];
-        if (fallen) rst = 1;
-        if ((float)prog >= P.max_episode_length - 1.0f) rst = 1;
+            red[c] = combine4(s_part[(c * 4 + 0) * E + e], s_part[(c * 4 + 1) * E + e], s_part[(c * 4 + 2) * E + e],
+                              s_part[(c * 4 + 3) * E + e]);
+        float total;
+        long long prog, rst;
+        reward_done(P, row[0], row[10], row[11], o_pot[e], s_pot[e], red, s_prog[e], s_reset[e], total, prog, rst);
         s_prog[e] = prog;
         s_reset[e] = rst;
         o_rew[e] = total;
@@ -464,13 +309,15 @@ constexpr size_t k1_smem_bytes() {
 
 template <int D, int S, int E>
 int launch_k1(const OigeTaskParams& P, const K1Args& A, cudaStream_t stream) {
-    static bool configured = false;
+    static std::atomic<bool> configured[64];  // per device: the attribute belongs to the device's copy of the function
     constexpr size_t smem = k1_smem_bytes<D, S, E>();
     auto kern = obs_reward_reset_kernel<D, S, E>;
-    if (!configured) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
+    if (!configured[dev].load(std::memory_order_acquire)) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return fail((int)e, "cudaFuncSetAttribute(K1): %s", cudaGetErrorString(e));
-        configured = true;
+        configured[dev].store(true, std::memory_order_release);
     }
     const long long tiles = (A.n + E - 1) / E;
     launch_pdl(kern, (unsigned)tiles, 4 * E, smem, stream, P, A);

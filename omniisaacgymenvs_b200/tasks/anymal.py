@@ -121,7 +121,7 @@ class AnymalTask(RLTask):
             p.command_yaw[k] = float(self.command_yaw_range[k])
         p.fallen_threshold = 0.51  # anymal.py:284
         p.max_episode_length = float(self.max_episode_length)
-        p.clip_obs = float(self.clip_obs)
+        p.clip_obs = self._kernel_clip_obs()
         dflt = self.default_dof_pos[0].tolist()
         lo, hi = self.anymal_dof_lower_limits.tolist(), self.anymal_dof_upper_limits.tolist()
         for k in range(12):
@@ -141,7 +141,7 @@ class AnymalTask(RLTask):
         self._unit_gear_params.power_scale = 1.0
         ptrs = self._buffer_ptrs()
         self._buffers = _lib.OigeAnymalBuffers(*ptrs, self.episode_stats.data_ptr(), None)
-        self._reset_counter_dev = torch.zeros(1, dtype=torch.int64, device=self._device)
+        self._ensure_reset_counter()
         self._buffers_graph = _lib.OigeAnymalBuffers(*ptrs, self.episode_stats.data_ptr(),
                                                      self._reset_counter_dev.data_ptr())
         # staging twins for the individually-callable get_observations / calculate_metrics / is_done
@@ -160,6 +160,7 @@ class AnymalTask(RLTask):
     def _check_bound(self) -> None:
         if self._buffer_ptrs() != self._bound:
             self._bind_buffers()
+            self._invalidate_graphs()
 
     def _stream(self) -> int:
         return _lib.current_stream_ptr(self._device)

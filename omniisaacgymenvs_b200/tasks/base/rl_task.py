@@ -84,6 +84,30 @@ class RLTask(BaseTask):
             self._dr_randomizer.set_up_domain_randomization(self)
             self._dr_is_set_up = True
 
+    # ---- helpers shared by the task classes' C-ABI plumbing -------------------------------------------------
+    def _kernel_clip_obs(self) -> float:
+        """clip_obs as the observation kernels see it: +inf while observation noise is active, because the
+        wrapper's clamp then has to come AFTER the noise (vec_env_rlgames.py:42 vs :70-71) and moves into the noise
+        launch.  Survives every rebuild of the parameter structs."""
+        return float("inf") if getattr(self, "randomize_observations", False) else float(self.clip_obs)
+
+    def _ensure_reset_counter(self) -> torch.Tensor:
+        """Device words {Philox reset counter, CTA ticket} of the CUDA-graph twin (OigeTaskBuffers.reset_counter).
+        Allocated ONCE per task: captured graphs and the Randomizer keep the pointer."""
+        if getattr(self, "_reset_counter_words", None) is None:
+            self._reset_counter_words = torch.zeros(2, dtype=torch.int64, device=self._device)
+            self._reset_counter_dev = self._reset_counter_words[:1]  # fill_() on the view leaves the ticket at 0
+        return self._reset_counter_dev
+
+    def _invalidate_graphs(self) -> None:
+        """Buffers were re-bound: graphs captured with the old pointers must not be replayed."""
+        env = getattr(self, "_env", None)
+        if env is not None:
+            if getattr(env, "_graph", None) is not None:
+                env._graph = None
+            if getattr(env, "_host_graphs", None):
+                env._host_graphs = {}
+
     def cleanup(self) -> None:
         """Allocates the RL buffers (rl_task.py:98-107)."""
         dev = self._device

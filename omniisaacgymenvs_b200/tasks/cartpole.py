@@ -67,7 +67,7 @@ class CartpoleTask(RLTask):
         p.reset_dist = float(self._reset_dist)
         p.max_push_effort = float(self._max_push_effort)
         p.max_episode_length = float(self._max_episode_length)
-        p.clip_obs = float(self.clip_obs)
+        p.clip_obs = self._kernel_clip_obs()
         return p
 
     def _bind_buffers(self) -> None:
@@ -82,7 +82,7 @@ class CartpoleTask(RLTask):
         ptrs = (self.obs_buf.data_ptr(), self.rew_buf.data_ptr(), self.reset_buf.data_ptr(),
                 self.progress_buf.data_ptr(), v.dof_efforts.data_ptr())
         self._buffers = _lib.OigeCartpoleBuffers(*ptrs, self.episode_stats.data_ptr(), None)
-        self._reset_counter_dev = torch.zeros(1, dtype=torch.int64, device=self._device)
+        self._ensure_reset_counter()
         self._buffers_graph = _lib.OigeCartpoleBuffers(*ptrs, self.episode_stats.data_ptr(),
                                                        self._reset_counter_dev.data_ptr())
         # staging twins for the individually-callable get_observations / calculate_metrics / is_done
@@ -99,6 +99,7 @@ class CartpoleTask(RLTask):
                self.progress_buf.data_ptr(), self._cartpoles.dof_efforts.data_ptr())
         if cur != self._bound:
             self._bind_buffers()
+            self._invalidate_graphs()
 
     def _stream(self) -> int:
         return _lib.current_stream_ptr(self._device)

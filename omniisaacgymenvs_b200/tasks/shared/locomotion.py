@@ -84,7 +84,7 @@ class LocomotionTask(RLTask):
         p.termination_height = self.termination_height
         p.alive_reward_scale = self.alive_reward_scale
         p.max_episode_length = float(self._max_episode_length)
-        p.clip_obs = float(self.clip_obs)
+        p.clip_obs = self._kernel_clip_obs()
         p.power_scale = self.power_scale
         tgt = self.targets[0].tolist()
         inv = self.inv_start_rot[0].tolist()
@@ -114,7 +114,7 @@ class LocomotionTask(RLTask):
             self.potentials.data_ptr(), self.prev_potentials.data_ptr(), self.up_vec.data_ptr(),
             self.heading_vec.data_ptr(), self.actions.data_ptr(), self.episode_stats.data_ptr(), None)
         # CUDA-graph twin: the Philox reset counter lives on the device and is bumped by the step itself
-        self._reset_counter_dev = torch.zeros(1, dtype=torch.int64, device=self._device)
+        self._ensure_reset_counter()
         self._buffers_graph = _lib.OigeTaskBuffers(
             self.obs_buf.data_ptr(), self.rew_buf.data_ptr(), self.reset_buf.data_ptr(), self.progress_buf.data_ptr(),
             self.potentials.data_ptr(), self.prev_potentials.data_ptr(), self.up_vec.data_ptr(),
@@ -138,6 +138,7 @@ class LocomotionTask(RLTask):
                self.progress_buf.data_ptr(), self.actions.data_ptr())
         if cur != self._bound:  # a caller re-assigned a buffer attribute (the reference does in reset())
             self._bind_buffers()
+            self._invalidate_graphs()
 
     def _stream(self) -> int:
         return _lib.current_stream_ptr(self._device)

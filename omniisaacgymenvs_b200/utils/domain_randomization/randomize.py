@@ -138,9 +138,13 @@ class Randomizer():
         self._observations_counter_buffer = self._obs_noise.counter
         # the observation pass clamps to +-clipObservations itself; with noise active the clamp has to come AFTER the
         # noise (vec_env_rlgames.py:42 vs :70-71), so it moves into the noise launch (apply_..., clip=task.clip_obs)
-        p = getattr(task, "_params", None)
-        if p is not None and hasattr(p, "clip_obs"):
-            p.clip_obs = math.inf
+        # (task._kernel_clip_obs() keeps returning +inf from now on, so rebuilt parameter structs stay consistent;
+        # BOTH the fused-step and the hook-by-hook structs are patched: the reference applies the noise first and
+        # clamps once on either path)
+        for name in ("_params", "_params_noinc"):
+            p = getattr(task, name, None)
+            if p is not None and hasattr(p, "clip_obs"):
+                p.clip_obs = math.inf
         self._observations_correlated_noise = self._obs_noise.correlated
 
     def _set_up_actions_randomization(self, task):

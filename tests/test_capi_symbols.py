@@ -21,7 +21,7 @@ def test_library_builds_and_loads():
     assert os.path.exists(path)
     lib = ctypes.CDLL(path)
     lib.oige_abi_version.restype = ctypes.c_int
-    assert lib.oige_abi_version() == 1
+    assert lib.oige_abi_version() == _lib.ABI_VERSION == 2
 
 
 def test_every_declared_symbol_is_exported():

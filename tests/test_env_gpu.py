@@ -35,10 +35,31 @@ def test_env_surface_and_shapes(cuda_lib, robot, obs, act):
     assert p.data_ptr() == v.root_pos.data_ptr(), "clone=False must hand out the live buffer"
 
 
+@pytest.fixture
+def k2_mode(monkeypatch):
+    """Pins the articulation kernel (the library reads OIGE_* once: set, then reload)."""
+    from omniisaacgymenvs_b200 import _lib
+
+    def pin(mode):
+        if mode == "auto":
+            monkeypatch.delenv("OIGE_K2_MODE", raising=False)
+            monkeypatch.delenv("OIGE_K2_EPC", raising=False)
+        else:
+            monkeypatch.setenv("OIGE_K2_MODE", "role")
+            monkeypatch.setenv("OIGE_K2_EPC", "128" if mode == "role128" else "32")
+        _lib.reload_env()
+
+    yield pin
+    monkeypatch.undo()
+    _lib.reload_env()
+
+
+@pytest.mark.parametrize("mode,n", [("auto", 512), ("role", 500), ("role128", 1000), ("role128", 1024)])
 @pytest.mark.parametrize("robot", ["Humanoid", "Ant"])
-def test_fused_step_equals_hook_by_hook_path(cuda_lib, robot):
-    """oige_env_step_f32 (one call) vs pre_physics_step -> world.step x2 -> post_physics_step."""
-    n = 512
+def test_fused_step_equals_hook_by_hook_path(cuda_lib, robot, mode, n, k2_mode):
+    """oige_env_step_f32 (one call; ONE launch of the whole-step kernel K2-F in the role modes, ragged and full
+    tiles) vs pre_physics_step -> world.step x2 -> post_physics_step (K3, the articulation kernel alone, K1)."""
+    k2_mode(mode)
     env_a, task_a = make_env(robot, num_envs=n, seed=3)
     env_b, task_b = make_env(robot, num_envs=n, seed=3)
     task_b.fused_step_enabled = lambda: False  # force the generic path
@@ -333,3 +354,16 @@ def test_random_policy_script_runs(cuda_lib, capsys):
 
     assert random_policy.main(["task=Ant", "num_envs=64", "steps=5"]) == 0
     assert "5 steps of 64 envs" in capsys.readouterr().out
+
+
+def test_whole_step_is_one_launch_from_4096_humanoids(cuda_lib):
+    """clamp + masked reset + substeps + observations / reward / done in ONE kernel launch."""
+    from omniisaacgymenvs_b200 import _lib
+
+    env, task = make_env("Humanoid", num_envs=4096, seed=2)
+    env.reset()
+    a = torch.rand(4096, 21, device=task.device) * 2 - 1
+    n0 = _lib.launch_count()
+    env.step(a)
+    assert _lib.launch_count() - n0 == 1
+    assert _lib.nonfinite_env_count() == 0

@@ -16,12 +16,30 @@ pytestmark = pytest.mark.gpu
 DT = 0.0083
 
 
-@pytest.fixture(autouse=True, params=["warp", "thread", "role"])
+def _set_mode(monkeypatch, mode):
+    """The library reads its OIGE_* knobs once: set them, then ask it to re-read."""
+    from omniisaacgymenvs_b200 import _lib
+
+    if mode.startswith("role"):
+        monkeypatch.setenv("OIGE_K2_MODE", "role")
+        monkeypatch.setenv("OIGE_K2_EPC", "128" if mode == "role128" else "32")
+    else:
+        monkeypatch.setenv("OIGE_K2_MODE", mode)
+        monkeypatch.delenv("OIGE_K2_EPC", raising=False)
+    _lib.reload_env()
+
+
+@pytest.fixture(autouse=True, params=["warp", "thread", "role", "role128"])
 def k2_kernel(request, monkeypatch):
-    """Every test runs against BOTH articulation kernels: warp-per-env (lane = link, shuffles) and
-    thread-per-env (lane = env, local-memory link arrays).  OIGE_K2_MODE overrides the size-based choice."""
-    monkeypatch.setenv("OIGE_K2_MODE", request.param)
-    return request.param
+    """Every test runs against ALL articulation kernels: warp-per-env (lane = link, shuffles), thread-per-env
+    (lane = env, local-memory link arrays) and the role-split whole-step kernel K2-F in physics-only mode, with 32-env
+    and with 128-env CTAs.  OIGE_K2_MODE / OIGE_K2_EPC override the size-based choice."""
+    from omniisaacgymenvs_b200 import _lib
+
+    _set_mode(monkeypatch, request.param)
+    yield request.param
+    monkeypatch.undo()
+    _lib.reload_env()
 
 
 def _err(a, b):
@@ -115,16 +133,19 @@ def test_both_kernels_agree_with_each_other(cuda_lib, monkeypatch):
     """warp-per-env vs thread-per-env on the same state: same model, different summation orders."""
     model, spec = dh.specs("Humanoid")
     st = dh.random_state(model, 256, 11, height=1.3, tilt=0.1)
-    monkeypatch.setenv("OIGE_K2_MODE", "warp")
+    _set_mode(monkeypatch, "warp")
     a = dh.run_gpu(cuda_lib, model, spec, st, 2, DT)
-    monkeypatch.setenv("OIGE_K2_MODE", "thread")
+    _set_mode(monkeypatch, "thread")
     b = dh.run_gpu(cuda_lib, model, spec, st, 2, DT)
     assert _err(a["q"], b["q"]) < 5e-5 and _err(a["pos"], b["pos"]) < 5e-5
     assert (np.abs(a["qd"] - b["qd"]) / np.maximum(1.0, np.abs(a["qd"]))).max() < 5e-3
-    monkeypatch.setenv("OIGE_K2_MODE", "role")  # role-split: the thread-per-env sums, trunk / limbs on separate warps
-    c = dh.run_gpu(cuda_lib, model, spec, st, 2, DT)
-    assert _err(c["q"], b["q"]) < 5e-5 and _err(c["pos"], b["pos"]) < 5e-5
-    assert (np.abs(c["qd"] - b["qd"]) / np.maximum(1.0, np.abs(b["qd"]))).max() < 5e-3
+    for mode in ("role", "role128"):  # role split: trunk / limbs on separate warps, link data in shared memory
+        _set_mode(monkeypatch, mode)
+        c = dh.run_gpu(cuda_lib, model, spec, st, 2, DT)
+        assert _err(c["q"], b["q"]) < 5e-5 and _err(c["pos"], b["pos"]) < 5e-5
+        assert (np.abs(c["qd"] - b["qd"]) / np.maximum(1.0, np.abs(b["qd"]))).max() < 5e-3
+        fs = np.maximum(10.0, np.abs(b["sensors"]))
+        assert (np.abs(c["sensors"] - b["sensors"]) / fs).max() < 5e-3
 
 
 @pytest.mark.parametrize("robot,n", [("Humanoid", 65536), ("Ant", 262144)])
@@ -136,6 +157,8 @@ def test_full_size_rows_are_independent(cuda_lib, robot, n, monkeypatch):
     # the thread-per-env kernel has a many-envs and a single-wave instantiation (different ptxas schedules): pin one,
     # as the library does for the chunks of one step
     monkeypatch.setenv("OIGE_K2_MINB", "4")
+    from omniisaacgymenvs_b200 import _lib
+    _lib.reload_env()
     model, spec = dh.specs(robot)
     st = dh.random_state(model, n, 21, height=model.spawn_height * 0.8, tilt=0.2)  # feet in / near the ground
     full = dh.run_gpu(cuda_lib, model, spec, st, 2, DT)
