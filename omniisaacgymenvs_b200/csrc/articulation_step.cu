@@ -1022,7 +1022,7 @@ namespace {
 size_t role_smem_bytes(const OigeModel* model, int epc, int D, int S) {
     const int OBS = 12 + 3 * D + 6 * S;
     const size_t scratch = (size_t)(epc / 32) * model->group_floats * 32;
-    const size_t tile_in = (size_t)epc * (3 * D + 13);
+    const size_t tile_in = (size_t)epc * (3 * D + 13 + 1);  // q, qd, actions, root state, reset flags
     const size_t tile_out = (size_t)epc * (2 * D + 6 * S + 13) + (size_t)epc * (D + OBS + 6 + 1 + 12) + 128;
     size_t fl = scratch > tile_in ? scratch : tile_in;
     if (tile_out > fl) fl = tile_out;
@@ -1325,7 +1325,6 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
             rm->num_links = L; rm->num_sensors = d->num_sensors; rm->fixed_base = d->fixed_base != 0; rm->nroles = best_r;
             rm->ntrunk = nt; rm->maxc = maxc;
             for (int i = 0; i < kRT; ++i) { rm->tpub[i] = 255; rm->town[i] = 0; }
-            for (int r = 0; r < 4; ++r) { rm->own_t[r] = 255; rm->own_slot[r] = 0; }
             // hand-over slots: one per (role, attach trunk link)
             int slot_of[kMaxRoles][kRT];
             for (int r = 0; r < kMaxRoles; ++r) for (int t = 0; t < kRT; ++t) slot_of[r][t] = -1;
@@ -1348,41 +1347,62 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
             rm->ts_begin[nt] = (unsigned char)pos;
             rm->npub = npub;
             // own inertia of a trunk link goes to the least loaded role that has a slot on it (one link per role)
+            int own_t[kMaxRoles] = {-1, -1, -1, -1};
             for (int t = 0; t < nt; ++t) {
                 int pick = -1;
                 for (int r = 0; r < best_r; ++r)
-                    if (slot_of[r][t] >= 0 && rm->own_t[r] == 255 && (pick < 0 || load[r] < load[pick])) pick = r;
-                if (pick >= 0) { rm->own_t[pick] = (unsigned char)t; rm->own_slot[pick] = (unsigned char)slot_of[pick][t]; rm->town[t] = 1; }
+                    if (slot_of[r][t] >= 0 && own_t[r] < 0 && (pick < 0 || load[r] < load[pick])) pick = r;
+                if (pick >= 0) { own_t[pick] = t; rm->town[t] = 1; }
             }
-            // per-role programs: chains in dealing order, each head -> tip
+            // per-role programs.  Segments in execution order:
+            //   role 0:  trunk kinematics | barrier K | [own inertia of a trunk link] chains ... | barrier H | trunk sweep
+            //   role r:  barrier K | [own inertia of a trunk link] chains ... | barrier H
             int sensor_chains[kMaxRoles] = {0};
             bool slot_written[kRSlots] = {false};
-            for (int r = 0; r < best_r; ++r)
-                if (rm->own_t[r] != 255) slot_written[rm->own_slot[r]] = true;
             bool sensor_seen[OIGE_MAX_SENSORS] = {false};
             for (int r = 0; r < best_r && fits; ++r) {
-                int k = 0;
-                for (int a = 0; a < nh; ++a) {
+                int k = 0, ns = 0;
+                auto add_seg = [&](int kind, int first, int last, int flags, int att, int slot) {
+                    if (ns >= kRSeg) { fits = false; return; }
+                    rm->seg_kind[r][ns] = (unsigned char)kind; rm->seg_first[r][ns] = (unsigned char)first;
+                    rm->seg_last[r][ns] = (unsigned char)last; rm->seg_flag[r][ns] = (unsigned char)flags;
+                    rm->seg_att[r][ns] = (unsigned char)att; rm->seg_slot[r][ns] = (unsigned char)slot;
+                    ++ns;
+                };
+                if (r == 0) add_seg(kSegTrunkKin, 1, nt - 1, kSegBarAfter, 0, 0);
+                const int first_work = ns;
+                if (own_t[r] >= 0) {
+                    const int sl = slot_of[r][own_t[r]];
+                    add_seg(kSegOwn, own_t[r], own_t[r], slot_written[sl] ? 0 : kSegSlotFirst, own_t[r], sl);
+                    slot_written[sl] = true;
+                }
+                int nchains = 0;
+                for (int a = 0; a < nh && fits; ++a) {
                     const int c = order[a];
                     if (owner[c] != r) continue;
+                    ++nchains;
                     const int t = tidx[h->parent[heads[c]]], sl = slot_of[r][t];
                     int sens = -1;
                     for (int s2 = 0; s2 < d->num_sensors; ++s2) if (d->sensor_link[s2] == tip[c]) sens = s2;
                     if (sens >= 0) { ++sensor_chains[r]; sensor_seen[sens] = true; }
                     int links[32], n = 0;
                     for (int cur = tip[c];; cur = h->parent[cur]) { links[n++] = cur; if (cur == heads[c]) break; }
-                    for (int j = n - 1; j >= 0; --j, ++k) {  // head first
-                        unsigned char f = 0;
-                        if (j == n - 1) f |= kPHead;
-                        if (j == 0) f |= kPTip;
-                        if (sens >= 0) f |= kPSensor;
-                        if (j == n - 1 && !slot_written[sl]) { f |= kPSlotFirst; slot_written[sl] = true; }
-                        rm->plink[r][k] = (unsigned char)links[j]; rm->pflag[r][k] = f;
-                        rm->patt[r][k] = (unsigned char)t; rm->pslot[r][k] = (unsigned char)sl;
-                    }
+                    const int k0 = k;
+                    for (int j = n - 1; j >= 0; --j, ++k) rm->plink[r][k] = (unsigned char)links[j];  // head first
+                    int fl = (sens >= 0 ? kSegSensor : 0) | (slot_written[sl] ? 0 : kSegSlotFirst);
+                    slot_written[sl] = true;
+                    add_seg(kSegChain, k0, k - 1, fl, t, sl);
                 }
                 rm->npos[r] = (unsigned char)k;
-                if (sensor_chains[r] > 1) fits = false;  // one sensor wrench is held in registers per role
+                if (nchains == 0 || sensor_chains[r] > 1) fits = false;  // every role works; one sensor wrench per role
+                if (!fits) break;
+                if (r == 0) {
+                    add_seg(kSegTrunkUp, 0, nt - 1, kSegBarBefore, 0, 0);
+                } else {
+                    rm->seg_flag[r][first_work] |= kSegBarBefore;
+                    rm->seg_flag[r][ns - 1] |= kSegBarAfter;
+                }
+                rm->nseg[r] = (unsigned char)ns;
             }
             for (int s2 = 0; s2 < d->num_sensors; ++s2) fits = fits && sensor_seen[s2];  // sensors sit on chain tips
             // scratch layout of a 32-env group (float offsets, x32 lanes)

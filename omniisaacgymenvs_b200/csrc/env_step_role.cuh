@@ -30,7 +30,9 @@ constexpr int kRL = 24;      // links
 constexpr int kRPos = 8;     // chain links per role (>= MAXC)
 constexpr int kRT = 4;       // trunk links incl. the root
 constexpr int kRSlots = 8;   // hand-over slots
-constexpr int kPHead = 1, kPTip = 2, kPSlotFirst = 4, kPSensor = 8;
+constexpr int kRSeg = 8;     // segments per role
+constexpr int kSegTrunkKin = 0, kSegOwn = 1, kSegChain = 2, kSegTrunkUp = 3;
+constexpr int kSegBarBefore = 1, kSegBarAfter = 2, kSegSlotFirst = 4, kSegSensor = 8;
 constexpr int kKin = 19;     // quat 4, p 3, v 6, b 6
 constexpr int kPu = 13;      // s 6, U/d 6, u'''
 constexpr int kHand = 27;    // I^a 21, p^a 6
@@ -53,12 +55,15 @@ struct alignas(16) RoleModel {
     float sph_r[OIGE_MAX_SPHERES];
     unsigned char dof[kRL], jtype[kRL], sph_start[kRL], sph_count[kRL], massless[kRL];
     signed char sensor_of_link[kRL];
-    unsigned char npos[4];
-    unsigned char plink[4][kRPos], pflag[4][kRPos], patt[4][kRPos], pslot[4][kRPos];
-    unsigned char own_t[4], own_slot[4];   // trunk link whose own inertia role r evaluates in S1 (255: none), into which slot
+    unsigned char npos[4], nseg[4];
+    unsigned char plink[4][kRPos];                        // chain links of role r by position (chains concatenated head -> tip)
+    // the role's segments, in execution order (see the kernel): kind, link range (positions for a chain, trunk
+    // indices otherwise), flags, attach trunk link, hand-over slot
+    unsigned char seg_kind[4][kRSeg], seg_first[4][kRSeg], seg_last[4][kRSeg], seg_flag[4][kRSeg];
+    unsigned char seg_att[4][kRSeg], seg_slot[4][kRSeg];
     unsigned char tlink[kRT], town[kRT], tpub[kRT];      // trunk idx -> link, own inertia handed to a role?, xA index (255: none)
     unsigned char ts_begin[kRT + 1], ts_slot[kRSlots];   // hand-over slots attached to trunk link t
-    unsigned char pad[7];
+    unsigned char pad[15];
 };
 static_assert(sizeof(RoleModel) % 16 == 0, "RoleModel must be int4-copyable");
 
@@ -241,58 +246,72 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
         __syncthreads();  // barrier initialised (and the model table staged) before anyone polls
         mbar_wait(&s_bar, 0);
     } else {
-        for (int i = tid; i < cnt * D; i += NT) { s_q[i] = A.q[e0 * D + i]; s_qd[i] = A.qd[e0 * D + i]; s_act[i] = act_src[e0 * D + i]; }
-        for (int i = tid; i < cnt * 3; i += NT) s_pos[i] = A.pos[e0 * 3 + i];
-        for (int i = tid; i < cnt * 4; i += NT) s_quat[i] = A.quat[e0 * 4 + i];
-        for (int i = tid; i < cnt * 6; i += NT) s_vel[i] = A.vel[e0 * 6 + i];
+        _Pragma("unroll 1") for (int i = tid; i < cnt * D; i += NT) { s_q[i] = A.q[e0 * D + i]; s_qd[i] = A.qd[e0 * D + i]; s_act[i] = act_src[e0 * D + i]; }
+        _Pragma("unroll 1") for (int i = tid; i < cnt * 3; i += NT) s_pos[i] = A.pos[e0 * 3 + i];
+        _Pragma("unroll 1") for (int i = tid; i < cnt * 4; i += NT) s_quat[i] = A.quat[e0 * 4 + i];
+        _Pragma("unroll 1") for (int i = tid; i < cnt * 6; i += NT) s_vel[i] = A.vel[e0 * 6 + i];
         __syncthreads();
     }
     pdl_trigger();
-    unsigned long long rcounter = A.counter;
-    bool rflag = false;
     if (A.pro) {
-        rflag = A.reset[env] != 0;  // read by every role BEFORE the barrier below; role 0 clears the flag after it
         // VecEnvRLGames.step's torch.clamp(actions, -clip, clip) (envs/vec_env_rlgames.py:57): the clamped copy the
         // task keeps (locomotion.py:108) goes to actions_out, coalesced; the tile copy feeds the efforts below
         const float c = A.clip;
-        for (int i = tid; i < cnt * D; i += NT) {
+        _Pragma("unroll 1") for (int i = tid; i < cnt * D; i += NT) {
             const float v = s_act[i];
             const float w = v < -c ? -c : (v > c ? c : v);
             s_act[i] = w;
             A.actions_out[e0 * D + i] = w;
         }
-        if (A.counter_dev != nullptr) rcounter = *A.counter_dev;
+        int* s_flag = reinterpret_cast<int*>(s_vel + EPC * 6);
+        _Pragma("unroll 1") for (int i = tid; i < cnt; i += NT) s_flag[i] = A.reset[e0 + i] != 0;
+        __syncthreads();
+        // masked reset_idx (locomotion.py:116-145; same arithmetic as reset_idx.cu) applied to the TILE: one warp per
+        // flagged env, lane = dof -- a random policy flags ~4 % of the envs per step
+        const unsigned long long rcounter = A.counter_dev != nullptr ? *A.counter_dev : A.counter;
+        for (int f = tid >> 5; f < cnt; f += NT / 32) {
+            if (!s_flag[f]) continue;  // warp-uniform
+            const long long genv = e0 + f;
+            if (lane < D) {
+                const uint64_t gid = (uint64_t)(A.env_id_offset + genv);
+                const float up = A.rand_pos ? A.rand_pos[genv * D + lane] : reset_uniform(A.seed, rcounter, gid, lane, 0);
+                const float uv = A.rand_vel ? A.rand_vel[genv * D + lane] : reset_uniform(A.seed, rcounter, gid, lane, 1);
+                const float noise = __fadd_rn(__fmul_rn(0.2f - (-0.2f), up), -0.2f);          // locomotion.py:120
+                float qv = __fadd_rn(A.init_q[genv * D + lane], noise);
+                qv = fmaxf(fminf(qv, P.dof_limits_upper[lane]), P.dof_limits_lower[lane]);    // locomotion.py:121-123
+                s_q[f * D + lane] = qv;
+                s_qd[f * D + lane] = __fadd_rn(__fmul_rn(0.1f - (-0.1f), uv), -0.1f);         // locomotion.py:124
+            }
+            if (lane < 3) s_pos[f * 3 + lane] = A.init_pos[genv * 3 + lane];
+            if (lane < 4) s_quat[f * 4 + lane] = A.init_rot[genv * 4 + lane];
+            if (lane < 6) s_vel[f * 6 + lane] = 0.0f;
+            if (lane == 0) {
+                // potentials = -|| (targets - initial_root_pos)_xy || / dt         (locomotion.py:136-139)
+                const float tx = __fsub_rn(P.targets[0], A.init_pos[genv * 3]);
+                const float ty = __fsub_rn(P.targets[1], A.init_pos[genv * 3 + 1]);
+                const float nrm = sqrtf(fmaf(0.0f, 0.0f, fmaf(ty, ty, __fmul_rn(tx, tx))));
+                const float pp = __fdiv_rn(-nrm, P.dt);
+                A.prev_pot[genv] = pp;
+                A.pot[genv] = pp;
+                A.reset[genv] = 0;     // locomotion.py:142-143
+                A.progress[genv] = 0;
+            }
+        }
         __syncthreads();
     }
-    // masked reset_idx (locomotion.py:116-145), same arithmetic as reset_idx.cu, evaluated by the threads that own
-    // the values
+    // joint state of this role's chain links -> registers (position k in the role's list); the ACTION is kept, the
+    // effort a * gear * power_scale (locomotion.py:109) is formed where it is used
     const int np = M.npos[role];
-    float qr[MAXC], qdr[MAXC], effr[MAXC], tgtr[TGT ? MAXC : 1];
-    float tq0[kRT - 1], tq1[kRT - 1], tq2[kRT - 1], tq3[kRT - 1];  // role 0: trunk q, qd, effort, target on their way to xT
-    auto load_joint = [&](int link, float& qo, float& qdo, float& effo, float& tgo) {
-        const int d = M.dof[link];
-        float qv = s_q[e * D + d], qdv = s_qd[e * D + d];
-        if (rflag) {
-            const uint64_t gid = (uint64_t)(A.env_id_offset + env);
-            const float up = A.rand_pos ? A.rand_pos[env * D + d] : reset_uniform(A.seed, rcounter, gid, d, 0);
-            const float uv = A.rand_vel ? A.rand_vel[env * D + d] : reset_uniform(A.seed, rcounter, gid, d, 1);
-            const float noise = __fadd_rn(__fmul_rn(0.2f - (-0.2f), up), -0.2f);          // locomotion.py:120
-            qv = __fadd_rn(A.init_q[env * D + d], noise);
-            qv = fmaxf(fminf(qv, P.dof_limits_upper[d]), P.dof_limits_lower[d]);          // locomotion.py:121-123
-            qdv = __fadd_rn(__fmul_rn(0.1f - (-0.1f), uv), -0.1f);                        // locomotion.py:124
-        }
-        qo = qv; qdo = qdv;
-        effo = s_act[e * D + d] * P.joint_gears[d] * P.power_scale;                       // locomotion.py:109
-        tgo = (TGT && A.targets != nullptr) ? A.targets[env * D + d] : 0.f;
-    };
+    float qr[MAXC], qdr[MAXC], ar[MAXC], tgtr[TGT ? MAXC : 1];
+    float tq0[kRT - 1], tq1[kRT - 1], tq2[kRT - 1], tq3[kRT - 1];  // role 0: trunk q, qd, action, target on their way to xT
 #pragma unroll
     for (int k = 0; k < MAXC; ++k) {
-        qr[k] = 0.f; qdr[k] = 0.f; effr[k] = 0.f;
+        qr[k] = 0.f; qdr[k] = 0.f; ar[k] = 0.f;
         if (TGT) tgtr[k] = 0.f;
         if (k < np) {
-            float tg;
-            load_joint(M.plink[role][k], qr[k], qdr[k], effr[k], tg);
-            if (TGT) tgtr[k] = tg;
+            const int d = M.dof[M.plink[role][k]];
+            qr[k] = s_q[e * D + d]; qdr[k] = s_qd[e * D + d]; ar[k] = s_act[e * D + d];
+            if (TGT) tgtr[k] = A.targets != nullptr ? A.targets[env * D + d] : 0.f;
         }
     }
     V3 rpos = {0.f, 0.f, 0.f};
@@ -302,30 +321,17 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
 #pragma unroll
         for (int t = 1; t < kRT; ++t) {
             tq0[t - 1] = 0.f; tq1[t - 1] = 0.f; tq2[t - 1] = 0.f; tq3[t - 1] = 0.f;
-            if (t < M.ntrunk) load_joint(M.tlink[t], tq0[t - 1], tq1[t - 1], tq2[t - 1], tq3[t - 1]);
-        }
-        if (rflag) {
-            rpos = {A.init_pos[env * 3], A.init_pos[env * 3 + 1], A.init_pos[env * 3 + 2]};
-            const float4 t = *reinterpret_cast<const float4*>(A.init_rot + env * 4);
-            rquat = {t.x, t.y, t.z, t.w};
-            if (valid) {
-                // potentials = -|| (targets - initial_root_pos)_xy || / dt         (locomotion.py:136-139)
-                const float tx = __fsub_rn(P.targets[0], rpos.x);
-                const float ty = __fsub_rn(P.targets[1], rpos.y);
-                const float nrm = sqrtf(fmaf(0.0f, 0.0f, fmaf(ty, ty, __fmul_rn(tx, tx))));
-                const float pp = __fdiv_rn(-nrm, P.dt);
-                A.prev_pot[env] = pp;
-                A.pot[env] = pp;
-                A.reset[env] = 0;     // locomotion.py:142-143
-                A.progress[env] = 0;
+            if (t < M.ntrunk) {
+                const int d = M.dof[M.tlink[t]];
+                tq0[t - 1] = s_q[e * D + d]; tq1[t - 1] = s_qd[e * D + d]; tq2[t - 1] = s_act[e * D + d];
+                tq3[t - 1] = (TGT && A.targets != nullptr) ? A.targets[env * D + d] : 0.f;
             }
-        } else {
-            rpos = {s_pos[e * 3], s_pos[e * 3 + 1], s_pos[e * 3 + 2]};
-            const float4 t = *reinterpret_cast<const float4*>(s_quat + e * 4);
-            rquat = {t.x, t.y, t.z, t.w};
-            const float* vv = s_vel + e * 6;
-            rvel = {{vv[3], vv[4], vv[5], vv[0], vv[1], vv[2]}};
         }
+        rpos = {s_pos[e * 3], s_pos[e * 3 + 1], s_pos[e * 3 + 2]};
+        const float4 t = *reinterpret_cast<const float4*>(s_quat + e * 4);
+        rquat = {t.x, t.y, t.z, t.w};
+        const float* vv = s_vel + e * 6;
+        rvel = {{vv[3], vv[4], vv[5], vv[0], vv[1], vv[2]}};
     }
     __syncthreads();  // the staging tile is dead from here on: the scratch regions below alias it
 
@@ -333,8 +339,8 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
     float* const G0 = dynsm + (size_t)grp * M.group_floats * 32 + lane;
     float* const xI = G0 + M.oI * 32;   // [nslots][27]   hand-over: I^a, p^a of the chains (+ own inertia of a trunk link)
     float* const xA = G0 + M.oA * 32;   // [npub][6]      a' of the trunk links that chains attach to
-    float* const xK = G0 + M.oK * 32;   // [ntrunk][19]   trunk kinematics; rows t >= 1 become (s, U/d, u''') in S2
-    float* const xT = G0 + M.oT * 32;   // [ntrunk-1][4]  trunk q, qd, effort, target
+    float* const xK = G0 + M.oK * 32;   // [ntrunk][19]   trunk kinematics; rows t >= 1 become (s, U/d, u3) in the trunk sweep
+    float* const xT = G0 + M.oT * 32;   // [ntrunk-1][4]  trunk q, qd, action, target
     float* const xS = G0 + M.oS * 32;   // [nsensors][7]  frame of the sensor links (last substep)
     float* const xM = G0 + M.oM * 32;   // [2]            root height, non-finite flag
     float* const LS = G0 + (M.oL + role * MAXC * kPu) * 32;  // [MAXC][13] link slots of this role
@@ -342,6 +348,7 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
     const bool fixed_base = M.fixed_base != 0;
     const V3 grav = {M.gravity[0], M.gravity[1], M.gravity[2]};
     const bool has_tgt = TGT && A.targets != nullptr;
+    const float power = P.power_scale;
     if (role == 0) {
 #pragma unroll
         for (int t = 1; t < kRT; ++t) {
@@ -357,157 +364,134 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
     float sw[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // sensor wrench of this role's sensor chain
     int sw_idx = -1;
     V6 vatt = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}}, batt = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
+    const int nseg = M.nseg[role];
 
     for (int step = 0; step < A.substeps; ++step) {
         const bool last = (step == A.substeps - 1);
-        // ---- S0 (role 0): trunk kinematics -> xK ------------------------------------------------------------
-        if (role == 0) {
-            KinCtx c;
-            c.q = rquat; c.R = qmat(rquat); c.p = {0.f, 0.f, 0.f}; c.v = rvel;
-            {
-                const V3 wxv = cross(ang(rvel), lin(rvel));
-                c.b = {{0.f, 0.f, 0.f, -wxv.x, -wxv.y, -wxv.z}};
-            }
-            xM[0] = rpos.z;
-            for (int t = 0; t < ntrunk; ++t) {
-                if (t > 0) kin_step(M, M.tlink[t], xT[((t - 1) * 4 + 0) * 32], xT[((t - 1) * 4 + 1) * 32], c);
-                float* k = xK + t * kKin * 32;
-                k[0] = c.q.w; k[32] = c.q.x; k[64] = c.q.y; k[96] = c.q.z;
-                k[4 * 32] = c.p.x; k[5 * 32] = c.p.y; k[6 * 32] = c.p.z;
-#pragma unroll
-                for (int j = 0; j < 6; ++j) { k[(7 + j) * 32] = c.v.a[j]; k[(13 + j) * 32] = c.b.a[j]; }
-            }
-        }
-        group_barrier(bar_id, GT);  // K
-        const float root_z = xM[0];
-
-        // ---- S1: own chains (+ the own inertia of one trunk link, if this role was given one) ---------------
-        if (M.own_t[role] != 255) {
-            const int t = M.own_t[role];
-            const float* k = xK + t * kKin * 32;
-            const M3 R = qmat(Q4{k[0], k[32], k[64], k[96]});
-            const V3 p = {k[4 * 32], k[5 * 32], k[6 * 32]};
+        float root_z = 0.f;
+        S6 carryI;
+        V6 carryP;
+        // ---- S0 / S1 / S2a: the role's SEGMENTS.  One loop body serves the trunk kinematics (role 0), the chains
+        // (kinematics head -> tip, then articulated inertia tip -> head), the own inertia of a trunk link taken off
+        // role 0's hands, and the trunk's bottom-up sweep (role 0): ONE copy of every sweep in the instruction stream
+        // (the first version inlined them two to three times and stalled on instruction fetch, ncu no_instruction 1.5
+        // per issue).
+        for (int sg = 0; sg < nseg; ++sg) {
+            const int kind = M.seg_kind[role][sg], sflag = M.seg_flag[role][sg];
+            const int first = M.seg_first[role][sg], lastl = M.seg_last[role][sg];
+            if (sflag & kSegBarBefore) group_barrier(bar_id, GT);
+            if (kind != kSegTrunkKin) root_z = xM[0];
+            const bool chain = kind == kSegChain;
             V6 v, b;
+            // ---- kinematics sweep: parent -> child -----------------------------------------------------------
+            if (kind == kSegTrunkKin || chain) {
+                KinCtx c;
+                if (chain) {
+                    const float* k = xK + M.seg_att[role][sg] * kKin * 32;
+                    c.q = {k[0], k[32], k[64], k[96]};
+                    c.p = {k[4 * 32], k[5 * 32], k[6 * 32]};
 #pragma unroll
-            for (int j = 0; j < 6; ++j) { v.a[j] = k[(7 + j) * 32]; b.a[j] = k[(13 + j) * 32]; }
-            S6 IA;
-            V6 pA;
-            own_inertia(M, M.tlink[t], R, p, v, b, root_z, dt, grav, IA, pA);
-            float* dst = xI + M.own_slot[role] * kHand * 32;  // first writer of the slot: the chains below add to it
+                    for (int j = 0; j < 6; ++j) { c.v.a[j] = k[(7 + j) * 32]; c.b.a[j] = k[(13 + j) * 32]; }
+                } else {
+                    c.q = rquat; c.p = {0.f, 0.f, 0.f}; c.v = rvel;
+                    const V3 wxv = cross(ang(rvel), lin(rvel));
+                    c.b = {{0.f, 0.f, 0.f, -wxv.x, -wxv.y, -wxv.z}};
+                    xM[0] = rpos.z;
+                    float* k = xK;  // trunk row 0 = the root itself
+                    k[0] = c.q.w; k[32] = c.q.x; k[64] = c.q.y; k[96] = c.q.z;
+                    k[4 * 32] = 0.f; k[5 * 32] = 0.f; k[6 * 32] = 0.f;
 #pragma unroll
-            for (int j = 0; j < 21; ++j) dst[j * 32] = IA.a[j];
-#pragma unroll
-            for (int j = 0; j < 6; ++j) dst[(21 + j) * 32] = pA.a[j];
-        }
-        for (int k0 = 0; k0 < np;) {
-            // kinematics head -> tip; frames into the link slots
-            KinCtx c;
-            {
-                const float* k = xK + M.patt[role][k0] * kKin * 32;
-                c.q = {k[0], k[32], k[64], k[96]};
+                    for (int j = 0; j < 6; ++j) { k[(7 + j) * 32] = c.v.a[j]; k[(13 + j) * 32] = c.b.a[j]; }
+                }
                 c.R = qmat(c.q);
-                c.p = {k[4 * 32], k[5 * 32], k[6 * 32]};
+                for (int i = first; i <= lastl; ++i) {
+                    int link;
+                    float qj, qdj;
+                    if (chain) { link = M.plink[role][i]; qj = rsel(qr, i); qdj = rsel(qdr, i); }
+                    else { link = M.tlink[i]; qj = xT[((i - 1) * 4 + 0) * 32]; qdj = xT[((i - 1) * 4 + 1) * 32]; }
+                    kin_step(M, link, qj, qdj, c);
+                    float* dst = chain ? LS + i * kPu * 32 : xK + i * kKin * 32;
+                    dst[0] = c.q.w; dst[32] = c.q.x; dst[64] = c.q.y; dst[96] = c.q.z;
+                    dst[4 * 32] = c.p.x; dst[5 * 32] = c.p.y; dst[6 * 32] = c.p.z;
+                    if (!chain) {
 #pragma unroll
-                for (int j = 0; j < 6; ++j) { c.v.a[j] = k[(7 + j) * 32]; c.b.a[j] = k[(13 + j) * 32]; }
-            }
-            int k1 = k0;
-            for (;; ++k1) {
-                const int link = M.plink[role][k1];
-                kin_step(M, link, rsel(qr, k1), rsel(qdr, k1), c);
-                float* slot = LS + k1 * kPu * 32;
-                slot[0] = c.q.w; slot[32] = c.q.x; slot[64] = c.q.y; slot[96] = c.q.z;
-                slot[4 * 32] = c.p.x; slot[5 * 32] = c.p.y; slot[6 * 32] = c.p.z;
-                if (M.pflag[role][k1] & kPTip) break;
-            }
-            const int cflag = M.pflag[role][k0];
-            if (last && (cflag & kPSensor)) {  // the foot's frame is needed again after the downward sweep
-                const int link = M.plink[role][k1];
-                float* f = xS + M.sensor_of_link[link] * 7 * 32;
-                f[0] = c.q.w; f[32] = c.q.x; f[64] = c.q.y; f[96] = c.q.z;
-                f[4 * 32] = c.p.x; f[5 * 32] = c.p.y; f[6 * 32] = c.p.z;
-            }
-            // articulated inertia tip -> head in registers; (v, b) are walked back up with it
-            V6 v = c.v, b = c.b;
-            S6 carryI;
-            V6 carryP;
-            for (int kk = k1; kk >= k0; --kk) {
-                const int link = M.plink[role][kk];
-                float* slot = LS + kk * kPu * 32;
-                const M3 R = qmat(Q4{slot[0], slot[32], slot[64], slot[96]});
-                const V3 p = {slot[4 * 32], slot[5 * 32], slot[6 * 32]};
-                S6 IA;
-                V6 pA;
-                own_inertia(M, link, R, p, v, b, root_z, dt, grav, IA, pA);
-                if (kk != k1) {
-#pragma unroll
-                    for (int j = 0; j < 21; ++j) IA.a[j] += carryI.a[j];
-#pragma unroll
-                    for (int j = 0; j < 6; ++j) pA.a[j] += carryP.a[j];
+                        for (int j = 0; j < 6; ++j) { dst[(7 + j) * 32] = c.v.a[j]; dst[(13 + j) * 32] = c.b.a[j]; }
+                    }
                 }
-                joint_reduce(M, link, R, p, v, b, rsel(qr, kk), rsel(qdr, kk), rsel(effr, kk), has_tgt,
-                             TGT ? rsel(tgtr, kk) : 0.f, dt, IA, pA, slot);
-                carryI = IA; carryP = pA;
+                if (chain && last && (sflag & kSegSensor)) {  // the foot's frame is needed again after the downward sweep
+                    float* f = xS + M.sensor_of_link[M.plink[role][lastl]] * 7 * 32;
+                    f[0] = c.q.w; f[32] = c.q.x; f[64] = c.q.y; f[96] = c.q.z;
+                    f[4 * 32] = c.p.x; f[5 * 32] = c.p.y; f[6 * 32] = c.p.z;
+                }
+                v = c.v; b = c.b;  // of the tip: walked back up with the inertia sweep
             }
-            if (last && (cflag & kPSensor)) { vatt = v; batt = b; }  // = the attach link's v, b
-            {   // hand the head's I^a, p^a to the trunk
-                float* dst = xI + M.pslot[role][k0] * kHand * 32;
-                if (cflag & kPSlotFirst) {
+            // ---- articulated-inertia sweep: child -> parent, I^a / p^a carried in registers ---------------------
+            if (kind != kSegTrunkKin) {
+                const bool trunk_up = kind == kSegTrunkUp;
+                for (int i = lastl; i >= first; --i) {
+                    const int link = chain ? M.plink[role][i] : M.tlink[i];
+                    float* src = chain ? LS + i * kPu * 32 : xK + i * kKin * 32;
+                    const M3 R = qmat(Q4{src[0], src[32], src[64], src[96]});
+                    const V3 p = {src[4 * 32], src[5 * 32], src[6 * 32]};
+                    if (!chain) {
 #pragma unroll
-                    for (int j = 0; j < 21; ++j) dst[j * 32] = carryI.a[j];
+                        for (int j = 0; j < 6; ++j) { v.a[j] = src[(7 + j) * 32]; b.a[j] = src[(13 + j) * 32]; }
+                    }
+                    S6 IA;
+                    V6 pA;
+                    if (trunk_up && M.town[i]) {  // a chain role already put this link's own inertia into its slot
 #pragma unroll
-                    for (int j = 0; j < 6; ++j) dst[(21 + j) * 32] = carryP.a[j];
-                } else {
+                        for (int j = 0; j < 21; ++j) IA.a[j] = 0.f;
 #pragma unroll
-                    for (int j = 0; j < 21; ++j) dst[j * 32] += carryI.a[j];
+                        for (int j = 0; j < 6; ++j) pA.a[j] = 0.f;
+                    } else {
+                        own_inertia(M, link, R, p, v, b, root_z, dt, grav, IA, pA);
+                    }
+                    if (i != lastl) {
 #pragma unroll
-                    for (int j = 0; j < 6; ++j) dst[(21 + j) * 32] += carryP.a[j];
+                        for (int j = 0; j < 21; ++j) IA.a[j] += carryI.a[j];
+#pragma unroll
+                        for (int j = 0; j < 6; ++j) pA.a[j] += carryP.a[j];
+                    }
+                    if (trunk_up) {
+                        for (int h = M.ts_begin[i]; h < M.ts_begin[i + 1]; ++h) {
+                            const float* hs = xI + M.ts_slot[h] * kHand * 32;
+#pragma unroll
+                            for (int j = 0; j < 21; ++j) IA.a[j] += hs[j * 32];
+#pragma unroll
+                            for (int j = 0; j < 6; ++j) pA.a[j] += hs[(21 + j) * 32];
+                        }
+                    }
+                    if (chain || (trunk_up && i > 0)) {
+                        float qj, qdj, aj, tj;
+                        if (chain) { qj = rsel(qr, i); qdj = rsel(qdr, i); aj = rsel(ar, i); tj = TGT ? rsel(tgtr, i) : 0.f; }
+                        else { const float* x = xT + (i - 1) * 4 * 32; qj = x[0]; qdj = x[32]; aj = x[64]; tj = x[96]; }
+                        const float eff = aj * P.joint_gears[M.dof[link]] * power;  // locomotion.py:109
+                        joint_reduce(M, link, R, p, v, b, qj, qdj, eff, has_tgt, tj, dt, IA, pA, src);
+                    }
+                    carryI = IA; carryP = pA;
+                }
+                if (!trunk_up) {  // hand the head's I^a, p^a (or a trunk link's own inertia) to the trunk
+                    float* dst = xI + M.seg_slot[role][sg] * kHand * 32;
+                    if (sflag & kSegSlotFirst) {
+#pragma unroll
+                        for (int j = 0; j < 21; ++j) dst[j * 32] = carryI.a[j];
+#pragma unroll
+                        for (int j = 0; j < 6; ++j) dst[(21 + j) * 32] = carryP.a[j];
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 21; ++j) dst[j * 32] += carryI.a[j];
+#pragma unroll
+                        for (int j = 0; j < 6; ++j) dst[(21 + j) * 32] += carryP.a[j];
+                    }
+                    if (chain && last && (sflag & kSegSensor)) { vatt = v; batt = b; }  // = the attach link's v, b
                 }
             }
-            k0 = k1 + 1;
+            if (sflag & kSegBarAfter) group_barrier(bar_id, GT);
         }
-        group_barrier(bar_id, GT);  // H
 
-        // ---- S2 (role 0): trunk tip -> root, root solve, trunk accelerations root -> tip ----------------------
+        // ---- S2b (role 0): root solve, trunk accelerations root -> tip, trunk joints and root integrated ----------
         if (role == 0) {
-            S6 carryI;
-            V6 carryP;
-            for (int t = ntrunk - 1; t >= 0; --t) {
-                const int link = M.tlink[t];
-                float* k = xK + t * kKin * 32;
-                const M3 R = qmat(Q4{k[0], k[32], k[64], k[96]});
-                const V3 p = {k[4 * 32], k[5 * 32], k[6 * 32]};
-                V6 v, b;
-#pragma unroll
-                for (int j = 0; j < 6; ++j) { v.a[j] = k[(7 + j) * 32]; b.a[j] = k[(13 + j) * 32]; }
-                S6 IA;
-                V6 pA;
-                if (M.town[t]) {  // a chain role already put this link's own inertia into its hand-over slot
-#pragma unroll
-                    for (int j = 0; j < 21; ++j) IA.a[j] = 0.f;
-#pragma unroll
-                    for (int j = 0; j < 6; ++j) pA.a[j] = 0.f;
-                } else {
-                    own_inertia(M, link, R, p, v, b, root_z, dt, grav, IA, pA);
-                }
-                if (t != ntrunk - 1) {
-#pragma unroll
-                    for (int j = 0; j < 21; ++j) IA.a[j] += carryI.a[j];
-#pragma unroll
-                    for (int j = 0; j < 6; ++j) pA.a[j] += carryP.a[j];
-                }
-                for (int h = M.ts_begin[t]; h < M.ts_begin[t + 1]; ++h) {
-                    const float* src = xI + M.ts_slot[h] * kHand * 32;
-#pragma unroll
-                    for (int j = 0; j < 21; ++j) IA.a[j] += src[j * 32];
-#pragma unroll
-                    for (int j = 0; j < 6; ++j) pA.a[j] += src[(21 + j) * 32];
-                }
-                if (t > 0) {
-                    const float* x = xT + (t - 1) * 4 * 32;
-                    joint_reduce(M, link, R, p, v, b, x[0], x[32], x[64], has_tgt, x[96], dt, IA, pA, k);
-                }
-                carryI = IA; carryP = pA;
-            }
             V6 a0 = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
             if (!fixed_base) chol6_solve(carryI, carryP, a0);  // a welded base does not accelerate
             V6 ap = a0;  // a' = a - b; b_root = -(0, w x v)
@@ -540,19 +524,20 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
         group_barrier(bar_id, GT);  // A
 
         // ---- S3: accelerations down the own chains, joint integration, foot sensors ---------------------------
-        for (int k0 = 0; k0 < np;) {
-            const int cflag = M.pflag[role][k0];
-            const bool sens_chain = last && (cflag & kPSensor) && A.sens != nullptr;
+        for (int sg = 0; sg < nseg; ++sg) {
+            if (M.seg_kind[role][sg] != kSegChain) continue;
+            const int sflag = M.seg_flag[role][sg];
+            const int first = M.seg_first[role][sg], lastl = M.seg_last[role][sg];
+            const bool sens_chain = last && (sflag & kSegSensor) && A.sens != nullptr;
             V6 ap;
             {
-                const float* src = xA + M.tpub[M.patt[role][k0]] * 6 * 32;
+                const float* src = xA + M.tpub[M.seg_att[role][sg]] * 6 * 32;
 #pragma unroll
                 for (int j = 0; j < 6; ++j) ap.a[j] = src[j * 32];
             }
             V6 v = vatt, b = batt;
-            int k1 = k0;
-            for (;; ++k1) {
-                const float* slot = LS + k1 * kPu * 32;
+            for (int i = first; i <= lastl; ++i) {
+                const float* slot = LS + i * kPu * 32;
                 V6 s;
 #pragma unroll
                 for (int j = 0; j < 6; ++j) s.a[j] = slot[j * 32];
@@ -561,7 +546,7 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
                 for (int j = 0; j < 6; ++j) qdd = fmaf(-slot[(6 + j) * 32], ap.a[j], qdd);
 #pragma unroll
                 for (int j = 0; j < 6; ++j) ap.a[j] = fmaf(s.a[j], qdd, ap.a[j]);
-                const float qd0 = rsel(qdr, k1);
+                const float qd0 = rsel(qdr, i);
                 if (sens_chain) {  // rebuild the start-of-substep v, b down to the foot
 #pragma unroll
                     for (int j = 0; j < 6; ++j) v.a[j] = fmaf(s.a[j], qd0, v.a[j]);
@@ -571,12 +556,11 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
                 }
                 float qd = fmaf(dt, qdd, qd0);
                 qd = fminf(fmaxf(qd, -M.max_qd), M.max_qd);
-                rput(qdr, k1, qd);
-                rput(qr, k1, fmaf(dt, qd, rsel(qr, k1)));
-                if (M.pflag[role][k1] & kPTip) break;
+                rput(qdr, i, qd);
+                rput(qr, i, fmaf(dt, qd, rsel(qr, i)));
             }
             if (sens_chain) {
-                const int link = M.plink[role][k1];
+                const int link = M.plink[role][lastl];
                 sw_idx = M.sensor_of_link[link];
                 const float* f = xS + sw_idx * 7 * 32;
                 const M3 R = qmat(Q4{f[0], f[32], f[64], f[96]});
@@ -584,9 +568,8 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
                 V6 a;
 #pragma unroll
                 for (int j = 0; j < 6; ++j) a.a[j] = ap.a[j] + b.a[j];
-                sensor_wrench(M, link, R, p, v, b, a, root_z, dt, sw);
+                sensor_wrench(M, link, R, p, v, b, a, xM[0], dt, sw);
             }
-            k0 = k1 + 1;
         }
     }
 
@@ -594,7 +577,7 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
     bool bad = false;
 #pragma unroll
     for (int k = 0; k < MAXC; ++k) bad = bad || !(isfinite(qr[k]) && isfinite(qdr[k]));
-    float tq[kRT - 1], tqd[kRT - 1];
+    float tq[kRT - 1], tqd[kRT - 1], ta[kRT - 1];
     if (role == 0) {
         bad = bad || !(isfinite(rpos.x) && isfinite(rpos.y) && isfinite(rpos.z) && isfinite(rquat.w) &&
                        isfinite(rquat.x) && isfinite(rquat.y) && isfinite(rquat.z));
@@ -602,10 +585,11 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
         for (int j = 0; j < 6; ++j) bad = bad || !isfinite(rvel.a[j]);
 #pragma unroll
         for (int t = 1; t < kRT; ++t) {
-            tq[t - 1] = 0.f; tqd[t - 1] = 0.f;
+            tq[t - 1] = 0.f; tqd[t - 1] = 0.f; ta[t - 1] = 0.f;
             if (t < ntrunk) {
                 tq[t - 1] = xT[((t - 1) * 4 + 0) * 32];
                 tqd[t - 1] = xT[((t - 1) * 4 + 1) * 32];
+                ta[t - 1] = xT[((t - 1) * 4 + 2) * 32];
                 bad = bad || !(isfinite(tq[t - 1]) && isfinite(tqd[t - 1]));
             }
         }
@@ -646,6 +630,7 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
                 const int d = M.dof[M.plink[role][k]];
                 o_q[e * D + d] = bad ? 0.f : qr[k];
                 o_qd[e * D + d] = bad ? 0.f : qdr[k];
+                o_act[e * D + d] = ar[k];
             }
         }
         if (role == 0) {
@@ -655,6 +640,7 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
                     const int d = M.dof[M.tlink[t]];
                     o_q[e * D + d] = bad ? 0.f : tq[t - 1];
                     o_qd[e * D + d] = bad ? 0.f : tqd[t - 1];
+                    o_act[e * D + d] = ta[t - 1];
                 }
             }
             o_pos[e * 3] = rpos.x; o_pos[e * 3 + 1] = rpos.y; o_pos[e * 3 + 2] = rpos.z;
@@ -669,7 +655,6 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
         }
     }
     if (A.epi) {
-        for (int i = tid; i < cnt * D; i += NT) o_act[i] = A.actions[e0 * D + i];
         if (tid < 32) {
             s_lo[tid] = tid < D ? P.dof_limits_lower[tid] : 0.0f;
             s_hi[tid] = tid < D ? P.dof_limits_upper[tid] : 0.0f;
@@ -760,7 +745,7 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
         if (P.clip_obs < INFINITY) {  // uniform; the stored rows are clamped after the metrics were evaluated
             __syncthreads();
             const float c = P.clip_obs;
-            for (int i = tid; i < cnt * OBS; i += NT) o_obs[i] = lm::clampf(o_obs[i], c);
+            _Pragma("unroll 1") for (int i = tid; i < cnt * OBS; i += NT) o_obs[i] = lm::clampf(o_obs[i], c);
         }
     }
 
@@ -784,15 +769,15 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
         }
     } else {
         __syncthreads();
-        for (int i = tid; i < cnt * D; i += NT) { A.q[e0 * D + i] = o_q[i]; A.qd[e0 * D + i] = o_qd[i]; }
+        _Pragma("unroll 1") for (int i = tid; i < cnt * D; i += NT) { A.q[e0 * D + i] = o_q[i]; A.qd[e0 * D + i] = o_qd[i]; }
         if (A.sens != nullptr)
-            for (int i = tid; i < cnt * S6n; i += NT) A.sens[e0 * S6n + i] = o_sens[i];
-        for (int i = tid; i < cnt * 3; i += NT) A.pos[e0 * 3 + i] = o_pos[i];
-        for (int i = tid; i < cnt * 4; i += NT) A.quat[e0 * 4 + i] = o_quat[i];
-        for (int i = tid; i < cnt * 6; i += NT) A.vel[e0 * 6 + i] = o_vel[i];
+            _Pragma("unroll 1") for (int i = tid; i < cnt * S6n; i += NT) A.sens[e0 * S6n + i] = o_sens[i];
+        _Pragma("unroll 1") for (int i = tid; i < cnt * 3; i += NT) A.pos[e0 * 3 + i] = o_pos[i];
+        _Pragma("unroll 1") for (int i = tid; i < cnt * 4; i += NT) A.quat[e0 * 4 + i] = o_quat[i];
+        _Pragma("unroll 1") for (int i = tid; i < cnt * 6; i += NT) A.vel[e0 * 6 + i] = o_vel[i];
         if (A.epi) {
-            for (int i = tid; i < cnt * OBS; i += NT) A.obs[e0 * OBS + i] = o_obs[i];
-            for (int i = tid; i < cnt * 3; i += NT) { A.up[e0 * 3 + i] = o_up[i]; A.head[e0 * 3 + i] = o_head[i]; }
+            _Pragma("unroll 1") for (int i = tid; i < cnt * OBS; i += NT) A.obs[e0 * OBS + i] = o_obs[i];
+            _Pragma("unroll 1") for (int i = tid; i < cnt * 3; i += NT) { A.up[e0 * 3 + i] = o_up[i]; A.head[e0 * 3 + i] = o_head[i]; }
         }
     }
     if (tid == 0) {

@@ -363,7 +363,7 @@ def test_whole_step_is_one_launch_from_4096_humanoids(cuda_lib):
     env, task = make_env("Humanoid", num_envs=4096, seed=2)
     env.reset()
     a = torch.rand(4096, 21, device=task.device) * 2 - 1
-    n0 = _lib.launch_count()
+    n0, bad0 = _lib.launch_count(), _lib.nonfinite_env_count()
     env.step(a)
     assert _lib.launch_count() - n0 == 1
-    assert _lib.nonfinite_env_count() == 0
+    assert _lib.nonfinite_env_count() == bad0  # (cumulative per process: other tests blow envs up on purpose)
