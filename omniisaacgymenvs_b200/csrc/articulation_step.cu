@@ -1022,7 +1022,7 @@ namespace {
 size_t role_smem_bytes(const OigeModel* model, int epc, int D, int S) {
     const int OBS = 12 + 3 * D + 6 * S;
     const size_t scratch = (size_t)(epc / 32) * model->group_floats * 32;
-    const size_t tile_in = (size_t)epc * (3 * D + 13 + 1);  // q, qd, actions, root state, reset flags
+    const size_t tile_in = (size_t)epc * (3 * D + 13 + 2);  // q, qd, actions, root state, reset flags (int64)
     const size_t tile_out = (size_t)epc * (2 * D + 6 * S + 13) + (size_t)epc * (D + OBS + 6 + 1 + 12) + 128;
     size_t fl = scratch > tile_in ? scratch : tile_in;
     if (tile_out > fl) fl = tile_out;
@@ -1056,12 +1056,12 @@ int role_dispatch(const OigeModel* model, const OigeTaskParams* P, const FArgs& 
         // staged once per CTA, and four groups is what one wave of 16384 envs needs on 148 SMs)
         const int force = knobs().epc;
         const bool big = force ? force == 128 : (dn + 31) / 32 > 3ll * sm_count();
-        if (big) return role_launch(env_step_role_kernel<6, 3, false, 128, 1>, 0, 3 * 128, 128, model, P, A, stream);
-        return role_launch(env_step_role_kernel<6, 3, false, 32, 3>, 1, 3 * 32, 32, model, P, A, stream);
+        if (big) return role_launch(env_step_role_kernel<6, 3, false, 128, 1, true>, 0, 3 * 128, 128, model, P, A, stream);
+        return role_launch(env_step_role_kernel<6, 3, false, 32, 3, true>, 1, 3 * 32, 32, model, P, A, stream);
     }
     if (model->nroles == 4 && model->maxc == 3) {
-        if (tgt) return role_launch(env_step_role_kernel<3, 4, true, 32, 4>, 2, 4 * 32, 32, model, P, A, stream);
-        return role_launch(env_step_role_kernel<3, 4, false, 32, 4>, 3, 4 * 32, 32, model, P, A, stream);
+        if (tgt) return role_launch(env_step_role_kernel<3, 4, true, 32, 4, false>, 2, 4 * 32, 32, model, P, A, stream);
+        return role_launch(env_step_role_kernel<3, 4, false, 32, 4, false>, 3, 4 * 32, 32, model, P, A, stream);
     }
     return fail(OIGE_E_MODEL, "env_step_role_kernel: no instantiation for %d roles x %d links%s", model->nroles,
                 model->maxc, tgt ? " with position targets" : "");
@@ -1337,23 +1337,51 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
                 }
             }
             rm->nslots = nslots;
-            int pos = 0, npub = 0;
-            for (int t = 0; t < nt; ++t) {
-                rm->ts_begin[t] = (unsigned char)pos;
-                for (int r = 0; r < best_r; ++r)
-                    if (slot_of[r][t] >= 0) rm->ts_slot[pos++] = (unsigned char)slot_of[r][t];
-                if (pos > rm->ts_begin[t]) rm->tpub[t] = (unsigned char)npub++;
+            int npub = 0;
+            for (int t = 0; t < nt; ++t) {  // a' is published for the trunk links that chains attach to
+                bool any = false;
+                for (int r = 0; r < best_r; ++r) any = any || slot_of[r][t] >= 0;
+                if (any) rm->tpub[t] = (unsigned char)npub++;
             }
-            rm->ts_begin[nt] = (unsigned char)pos;
             rm->npub = npub;
-            // own inertia of a trunk link goes to the least loaded role that has a slot on it (one link per role)
+            // The OWN inertia / bias / contacts of a trunk link are taken off role 0's serial trunk sweep: they go to the
+            // least loaded role that has a hand-over slot on the link (one link per role), or -- for a trunk link
+            // without chains -- to a role without such a job, through an extra slot while shared memory allows
+            // (4 groups of a 128-env CTA must fit in 227 KB).  Massless intermediate links have nothing to evaluate.
+            auto is_massless = [&](int i) {
+                bool zero = i > 0 && d->mass[i] == 0.f;
+                for (int k = 0; k < 6; ++k) zero = zero && d->inertia[i][k] == 0.f;
+                for (int s2 = 0; s2 < d->num_spheres; ++s2) zero = zero && d->sphere_link[s2] != i;
+                for (int s2 = 0; s2 < d->num_sensors; ++s2) zero = zero && d->sensor_link[s2] != i;
+                return zero;
+            };
+            const int fixed_floats = npub * 6 + nt * kKin + (nt - 1) * 4 + 2 + best_r * maxc * kPu;
+            const int max_group_floats = (int)((227 * 1024 - sizeof(RoleModel) - 256) / (4 * 32 * sizeof(float)));
             int own_t[kMaxRoles] = {-1, -1, -1, -1};
             for (int t = 0; t < nt; ++t) {
+                if (is_massless(rm->tlink[t])) { rm->town[t] = 1; continue; }
                 int pick = -1;
                 for (int r = 0; r < best_r; ++r)
                     if (slot_of[r][t] >= 0 && own_t[r] < 0 && (pick < 0 || load[r] < load[pick])) pick = r;
                 if (pick >= 0) { own_t[pick] = t; rm->town[t] = 1; }
             }
+            for (int t = 0; t < nt; ++t) {
+                if (rm->town[t]) continue;
+                int pick = -1;
+                for (int r = best_r - 1; r >= 1; --r)  // not role 0: the point is to shorten ITS critical path
+                    if (own_t[r] < 0 && (pick < 0 || load[r] < load[pick])) pick = r;
+                if (pick < 0 || nslots >= kRSlots || fixed_floats + (nslots + 1) * kHand > max_group_floats) continue;
+                slot_of[pick][t] = nslots++;
+                own_t[pick] = t; rm->town[t] = 1;
+            }
+            rm->nslots = nslots;
+            int pos = 0;
+            for (int t = 0; t < nt; ++t) {
+                rm->ts_begin[t] = (unsigned char)pos;
+                for (int r = 0; r < best_r; ++r)
+                    if (slot_of[r][t] >= 0) rm->ts_slot[pos++] = (unsigned char)slot_of[r][t];
+            }
+            rm->ts_begin[nt] = (unsigned char)pos;
             // per-role programs.  Segments in execution order:
             //   role 0:  trunk kinematics | barrier K | [own inertia of a trunk link] chains ... | barrier H | trunk sweep
             //   role r:  barrier K | [own inertia of a trunk link] chains ... | barrier H
@@ -1411,7 +1439,7 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
             rm->oK = rm->oA + npub * 6;
             rm->oT = rm->oK + nt * kKin;
             rm->oS = rm->oT + (nt - 1) * 4;
-            rm->oM = rm->oS + d->num_sensors * 7;
+            rm->oM = rm->oS + (best_r == 3 ? 0 : d->num_sensors * 7);  // the 3-role variants keep the sensor frame in registers
             rm->oL = rm->oM + 2;
             rm->group_floats = rm->oL + best_r * maxc * kPu;
         }

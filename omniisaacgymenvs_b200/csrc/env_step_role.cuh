@@ -194,22 +194,20 @@ __device__ __forceinline__ void joint_reduce(const MT& M, int i, const M3& R, V3
     }
 }
 
-template <int MAXC, int NR, bool TGT, int EPC, int MINB>
+// SREG: the sensor link's frame waits in registers (Humanoid: shared memory is full) or in shared memory (xS; the
+// four-role variants run at 128 registers per thread)
+template <int MAXC, int NR, bool TGT, int EPC, int MINB, bool SREG>
 __global__ void __launch_bounds__(NR * EPC, MINB)
 env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant__ OigeTaskParams P,
                      const __grid_constant__ FArgs A) {
     __shared__ __align__(16) RoleModel M;
     __shared__ __align__(8) uint64_t s_bar;
+    __shared__ unsigned long long s_counter;
     __shared__ float s_stat[(EPC / 32) * 3];
     extern __shared__ __align__(128) float dynsm[];
     constexpr int NT = NR * EPC;
     constexpr int GT = NR * 32;  // threads of a group
     const int tid = threadIdx.x;
-    {
-        const int4* src = reinterpret_cast<const int4*>(gmodel);
-        int4* dst = reinterpret_cast<int4*>(&M);
-        for (int i = tid; i < (int)(sizeof(RoleModel) / 16); i += NT) dst[i] = src[i];
-    }
     const int grp = tid / GT, role = (tid / 32) % NR, lane = tid & 31;
     const int bar_id = 1 + grp;
     const int D = A.D;
@@ -222,36 +220,62 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
     const long long env = e0 + e;
     const float dt = A.dt;
 
-    // ================= stage the tile: q, qd, actions, root state ========================================
+    // ================= stage the tile: q, qd, actions, root state (+ reset flags) ==========================
     float* s_q = dynsm;
     float* s_qd = s_q + EPC * D;
     float* s_act = s_qd + EPC * D;
     float* s_pos = s_act + EPC * D;
     float* s_quat = s_pos + EPC * 3;
     float* s_vel = s_quat + EPC * 4;
+    long long* s_flag = reinterpret_cast<long long*>(s_vel + EPC * 6);  // [EPC] reset_buf rows (fused step only)
     const float* act_src = A.pro ? A.actions_in : A.actions;
-    pdl_wait();  // state / actions may be written by a preceding kernel; the model table is not
-    if (bulk) {
-        if (tid == 0) {
-            mbar_init(&s_bar, 1);
-            mbar_fence_init();
-            mbar_expect_tx(&s_bar, (uint32_t)EPC * (3u * D + 13u) * 4u);
-            bulk_g2s(s_q, A.q + e0 * D, EPC * D * 4, &s_bar);
-            bulk_g2s(s_qd, A.qd + e0 * D, EPC * D * 4, &s_bar);
-            bulk_g2s(s_act, act_src + e0 * D, EPC * D * 4, &s_bar);
-            bulk_g2s(s_pos, A.pos + e0 * 3, EPC * 12, &s_bar);
-            bulk_g2s(s_quat, A.quat + e0 * 4, EPC * 16, &s_bar);
-            bulk_g2s(s_vel, A.vel + e0 * 6, EPC * 24, &s_bar);
+    pdl_wait();  // state / actions may be written by a preceding kernel
+    // The tile's bulk loads are issued FIRST, so that the model-table copy below, the reset counter and the ticket
+    // overlap their DRAM round trip instead of queueing behind it (the step starts with a cold L2 in the benchmark).
+    if (bulk && tid == 0) {
+        mbar_init(&s_bar, 1);
+        mbar_fence_init();
+        mbar_expect_tx(&s_bar, (uint32_t)EPC * ((3u * D + 13u) * 4u + (A.pro ? 8u : 0u)));
+        bulk_g2s(s_q, A.q + e0 * D, EPC * D * 4, &s_bar);
+        bulk_g2s(s_qd, A.qd + e0 * D, EPC * D * 4, &s_bar);
+        bulk_g2s(s_act, act_src + e0 * D, EPC * D * 4, &s_bar);
+        bulk_g2s(s_pos, A.pos + e0 * 3, EPC * 12, &s_bar);
+        bulk_g2s(s_quat, A.quat + e0 * 4, EPC * 16, &s_bar);
+        bulk_g2s(s_vel, A.vel + e0 * 6, EPC * 24, &s_bar);
+        if (A.pro) bulk_g2s(s_flag, A.reset + e0, EPC * 8, &s_bar);
+    }
+    if (tid == 0) {
+        // Philox reset counter of this step.  In a captured (CUDA-graph) step it lives in device memory: every CTA
+        // reads it, THEN takes a ticket; the CTA that draws the last ticket knows everyone has read it and advances it
+        // for the next replay -- here, off the critical path, not at the end of the kernel.
+        unsigned long long c = A.counter;
+        if (A.pro && A.counter_dev != nullptr) {
+            c = *reinterpret_cast<volatile unsigned long long*>(A.counter_dev);
+            if (A.bump) {
+                __threadfence();
+                const unsigned long long t = atomicAdd(A.counter_dev + 1, 1ull);
+                if (t == (unsigned long long)gridDim.x - 1) {
+                    A.counter_dev[1] = 0ull;
+                    A.counter_dev[0] = c + 1ull;
+                }
+            }
         }
-        __syncthreads();  // barrier initialised (and the model table staged) before anyone polls
-        mbar_wait(&s_bar, 0);
-    } else {
+        s_counter = c;
+    }
+    {
+        const int4* src = reinterpret_cast<const int4*>(gmodel);
+        int4* dst = reinterpret_cast<int4*>(&M);
+        for (int i = tid; i < (int)(sizeof(RoleModel) / 16); i += NT) dst[i] = src[i];
+    }
+    if (!bulk) {
         _Pragma("unroll 1") for (int i = tid; i < cnt * D; i += NT) { s_q[i] = A.q[e0 * D + i]; s_qd[i] = A.qd[e0 * D + i]; s_act[i] = act_src[e0 * D + i]; }
         _Pragma("unroll 1") for (int i = tid; i < cnt * 3; i += NT) s_pos[i] = A.pos[e0 * 3 + i];
         _Pragma("unroll 1") for (int i = tid; i < cnt * 4; i += NT) s_quat[i] = A.quat[e0 * 4 + i];
         _Pragma("unroll 1") for (int i = tid; i < cnt * 6; i += NT) s_vel[i] = A.vel[e0 * 6 + i];
-        __syncthreads();
+        if (A.pro) { _Pragma("unroll 1") for (int i = tid; i < cnt; i += NT) s_flag[i] = A.reset[e0 + i]; }
     }
+    __syncthreads();  // model table staged, barrier initialised, counter published
+    if (bulk) mbar_wait(&s_bar, 0);
     pdl_trigger();
     if (A.pro) {
         // VecEnvRLGames.step's torch.clamp(actions, -clip, clip) (envs/vec_env_rlgames.py:57): the clamped copy the
@@ -263,38 +287,42 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
             s_act[i] = w;
             A.actions_out[e0 * D + i] = w;
         }
-        int* s_flag = reinterpret_cast<int*>(s_vel + EPC * 6);
-        _Pragma("unroll 1") for (int i = tid; i < cnt; i += NT) s_flag[i] = A.reset[e0 + i] != 0;
-        __syncthreads();
         // masked reset_idx (locomotion.py:116-145; same arithmetic as reset_idx.cu) applied to the TILE: one warp per
-        // flagged env, lane = dof -- a random policy flags ~4 % of the envs per step
-        const unsigned long long rcounter = A.counter_dev != nullptr ? *A.counter_dev : A.counter;
-        for (int f = tid >> 5; f < cnt; f += NT / 32) {
-            if (!s_flag[f]) continue;  // warp-uniform
-            const long long genv = e0 + f;
-            if (lane < D) {
-                const uint64_t gid = (uint64_t)(A.env_id_offset + genv);
-                const float up = A.rand_pos ? A.rand_pos[genv * D + lane] : reset_uniform(A.seed, rcounter, gid, lane, 0);
-                const float uv = A.rand_vel ? A.rand_vel[genv * D + lane] : reset_uniform(A.seed, rcounter, gid, lane, 1);
-                const float noise = __fadd_rn(__fmul_rn(0.2f - (-0.2f), up), -0.2f);          // locomotion.py:120
-                float qv = __fadd_rn(A.init_q[genv * D + lane], noise);
-                qv = fmaxf(fminf(qv, P.dof_limits_upper[lane]), P.dof_limits_lower[lane]);    // locomotion.py:121-123
-                s_q[f * D + lane] = qv;
-                s_qd[f * D + lane] = __fadd_rn(__fmul_rn(0.1f - (-0.1f), uv), -0.1f);         // locomotion.py:124
-            }
-            if (lane < 3) s_pos[f * 3 + lane] = A.init_pos[genv * 3 + lane];
-            if (lane < 4) s_quat[f * 4 + lane] = A.init_rot[genv * 4 + lane];
-            if (lane < 6) s_vel[f * 6 + lane] = 0.0f;
-            if (lane == 0) {
-                // potentials = -|| (targets - initial_root_pos)_xy || / dt         (locomotion.py:136-139)
-                const float tx = __fsub_rn(P.targets[0], A.init_pos[genv * 3]);
-                const float ty = __fsub_rn(P.targets[1], A.init_pos[genv * 3 + 1]);
-                const float nrm = sqrtf(fmaf(0.0f, 0.0f, fmaf(ty, ty, __fmul_rn(tx, tx))));
-                const float pp = __fdiv_rn(-nrm, P.dt);
-                A.prev_pot[genv] = pp;
-                A.pot[genv] = pp;
-                A.reset[genv] = 0;     // locomotion.py:142-143
-                A.progress[genv] = 0;
+        // flagged env, lane = dof.  A random policy flags ~4 % of the envs per step; every warp ballots the same flags
+        // and takes every NW-th flagged env, so the rows' DRAM round trips (initial state) overlap across the warps.
+        const unsigned long long rcounter = s_counter;
+        int taken = 0;
+        for (int base = 0; base < cnt; base += 32) {
+            const int f0 = base + lane;
+            unsigned m = __ballot_sync(0xffffffffu, f0 < cnt && s_flag[f0] != 0);
+            for (; m; m &= m - 1, ++taken) {
+                if (taken % (NT / 32) != (tid >> 5)) continue;
+                const int f = base + __ffs(m) - 1;
+                const long long genv = e0 + f;
+                if (lane < D) {
+                    const uint64_t gid = (uint64_t)(A.env_id_offset + genv);
+                    const float up = A.rand_pos ? A.rand_pos[genv * D + lane] : reset_uniform(A.seed, rcounter, gid, lane, 0);
+                    const float uv = A.rand_vel ? A.rand_vel[genv * D + lane] : reset_uniform(A.seed, rcounter, gid, lane, 1);
+                    const float noise = __fadd_rn(__fmul_rn(0.2f - (-0.2f), up), -0.2f);          // locomotion.py:120
+                    float qv = __fadd_rn(A.init_q[genv * D + lane], noise);
+                    qv = fmaxf(fminf(qv, P.dof_limits_upper[lane]), P.dof_limits_lower[lane]);    // locomotion.py:121-123
+                    s_q[f * D + lane] = qv;
+                    s_qd[f * D + lane] = __fadd_rn(__fmul_rn(0.1f - (-0.1f), uv), -0.1f);         // locomotion.py:124
+                }
+                if (lane < 3) s_pos[f * 3 + lane] = A.init_pos[genv * 3 + lane];
+                if (lane < 4) s_quat[f * 4 + lane] = A.init_rot[genv * 4 + lane];
+                if (lane < 6) s_vel[f * 6 + lane] = 0.0f;
+                if (lane == 0) {
+                    // potentials = -|| (targets - initial_root_pos)_xy || / dt         (locomotion.py:136-139)
+                    const float tx = __fsub_rn(P.targets[0], A.init_pos[genv * 3]);
+                    const float ty = __fsub_rn(P.targets[1], A.init_pos[genv * 3 + 1]);
+                    const float nrm = sqrtf(fmaf(0.0f, 0.0f, fmaf(ty, ty, __fmul_rn(tx, tx))));
+                    const float pp = __fdiv_rn(-nrm, P.dt);
+                    A.prev_pot[genv] = pp;
+                    A.pot[genv] = pp;
+                    A.reset[genv] = 0;     // locomotion.py:142-143
+                    A.progress[genv] = 0;
+                }
             }
         }
         __syncthreads();
@@ -341,7 +369,7 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
     float* const xA = G0 + M.oA * 32;   // [npub][6]      a' of the trunk links that chains attach to
     float* const xK = G0 + M.oK * 32;   // [ntrunk][19]   trunk kinematics; rows t >= 1 become (s, U/d, u3) in the trunk sweep
     float* const xT = G0 + M.oT * 32;   // [ntrunk-1][4]  trunk q, qd, action, target
-    float* const xS = G0 + M.oS * 32;   // [nsensors][7]  frame of the sensor links (last substep)
+    float* const xS = G0 + M.oS * 32;   // [nsensors][7]  frame of the sensor links (last substep; !SREG)
     float* const xM = G0 + M.oM * 32;   // [2]            root height, non-finite flag
     float* const LS = G0 + (M.oL + role * MAXC * kPu) * 32;  // [MAXC][13] link slots of this role
     const int ntrunk = M.ntrunk;
@@ -364,6 +392,8 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
     float sw[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // sensor wrench of this role's sensor chain
     int sw_idx = -1;
     V6 vatt = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}}, batt = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
+    Q4 sq = {1.f, 0.f, 0.f, 0.f};  // frame of the sensor link at the start of the last substep
+    V3 sp = {0.f, 0.f, 0.f};
     const int nseg = M.nseg[role];
 
     for (int step = 0; step < A.substeps; ++step) {
@@ -419,9 +449,13 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
                     }
                 }
                 if (chain && last && (sflag & kSegSensor)) {  // the foot's frame is needed again after the downward sweep
-                    float* f = xS + M.sensor_of_link[M.plink[role][lastl]] * 7 * 32;
-                    f[0] = c.q.w; f[32] = c.q.x; f[64] = c.q.y; f[96] = c.q.z;
-                    f[4 * 32] = c.p.x; f[5 * 32] = c.p.y; f[6 * 32] = c.p.z;
+                    if (SREG) {
+                        sq = c.q; sp = c.p;  // (registers: they only stay live across barrier waits of the chain roles)
+                    } else {
+                        float* f = xS + M.sensor_of_link[M.plink[role][lastl]] * 7 * 32;
+                        f[0] = c.q.w; f[32] = c.q.x; f[64] = c.q.y; f[96] = c.q.z;
+                        f[4 * 32] = c.p.x; f[5 * 32] = c.p.y; f[6 * 32] = c.p.z;
+                    }
                 }
                 v = c.v; b = c.b;  // of the tip: walked back up with the inertia sweep
             }
@@ -562,9 +596,13 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
             if (sens_chain) {
                 const int link = M.plink[role][lastl];
                 sw_idx = M.sensor_of_link[link];
-                const float* f = xS + sw_idx * 7 * 32;
-                const M3 R = qmat(Q4{f[0], f[32], f[64], f[96]});
-                const V3 p = {f[4 * 32], f[5 * 32], f[6 * 32]};
+                if (!SREG) {
+                    const float* f = xS + sw_idx * 7 * 32;
+                    sq = {f[0], f[32], f[64], f[96]};
+                    sp = {f[4 * 32], f[5 * 32], f[6 * 32]};
+                }
+                const M3 R = qmat(sq);
+                const V3 p = sp;
                 V6 a;
 #pragma unroll
                 for (int j = 0; j < 6; ++j) a.a[j] = ap.a[j] + b.a[j];
@@ -668,6 +706,11 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
     float st_rew = 0.0f, st_done = 0.0f, st_len = 0.0f;
     if (A.epi) {
         const bool closed = P.closed_form_angles != 0;
+        const float clip = P.clip_obs;  // the stored rows are clamped; the metrics see the unclamped values
+        // inputs of the reward / termination thread, requested before the arithmetic below hides their latency
+        float prev_pot_in = 0.f;
+        long long prog_in = 0, reset_in = 0;
+        if (role == 0 && valid) { prev_pot_in = A.pot[env]; prog_in = A.progress[env]; reset_in = A.reset[env]; }
         if (valid) {
             float* row = o_obs + e * OBS;
             for (int r = role; r < 4; r += NR) {  // quarter r of env e: K1's thread (e, r)
@@ -679,9 +722,9 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
                         const float qs = lm::unscale(o_q[e * D + d], s_lo[d], s_hi[d], s_rcp[d]);
                         const float dv = lm::mul(o_qd[e * D + d], P.dof_vel_scale);
                         const float a = o_act[e * D + d];
-                        row[12 + d] = qs;
-                        row[12 + D + d] = dv;
-                        row[12 + 2 * D + S6n + d] = a;
+                        row[12 + d] = lm::clampf(qs, clip);
+                        row[12 + D + d] = lm::clampf(dv, clip);
+                        row[12 + 2 * D + S6n + d] = lm::clampf(a, clip);
                         lm::partial_add(P, part, qs, dv, a, s_ratio[d]);
                     }
                 }
@@ -691,39 +734,48 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
                 s_part[(2 * 4 + r) * EPC + e] = part.elec;
                 for (int k = 0; k < (S6n + 3) / 4; ++k) {
                     const int j = lm::owned_index_rt(S6n, r, k, e);
-                    if (j < S6n) row[12 + 2 * D + j] = lm::mul(o_sens[e * S6n + j], P.contact_force_scale);
+                    if (j < S6n) row[12 + 2 * D + j] = lm::clampf(lm::mul(o_sens[e * S6n + j], P.contact_force_scale), clip);
                 }
                 const float4 q4 = *reinterpret_cast<const float4*>(o_quat + 4 * e);
                 const float rot[4] = {q4.x, q4.y, q4.z, q4.w};
                 float tqq[4];
                 lm::torso_quat(P, rot, tqq);
                 const float px = o_pos[3 * e], py = o_pos[3 * e + 1], pz = o_pos[3 * e + 2];
+                // columns 0 (height), 10 (up projection) and 11 (heading projection) stay unclamped until the reward
+                // thread has read them; every other column is clamped by the thread that wrote it
                 if (r == 0) {
                     lm::root_part0(P, tqq, closed, row, o_up + 3 * e);
+                    row[8] = lm::clampf(row[8], clip);
                 } else if (r == 1) {
                     lm::root_part1(P, tqq, px, py, pz, closed, row);
+                    row[7] = lm::clampf(row[7], clip);
+                    row[9] = lm::clampf(row[9], clip);
                 } else if (r == 2) {
                     lm::root_part2(P, tqq, px, py, row, o_head + 3 * e, o_pot + e);
                 } else {
                     const float lin3[3] = {o_vel[6 * e], o_vel[6 * e + 1], o_vel[6 * e + 2]};
                     const float ang3[3] = {o_vel[6 * e + 3], o_vel[6 * e + 4], o_vel[6 * e + 5]};
                     lm::root_part3(P, tqq, pz, lin3, ang3, row);
+#pragma unroll
+                    for (int j = 1; j < 7; ++j) row[j] = lm::clampf(row[j], clip);
                 }
             }
         }
         __syncthreads();
         if (role == 0 && valid) {  // reward + termination: one thread per env, coalesced [N] accesses
-            const float* row = o_obs + e * OBS;
+            float* row = o_obs + e * OBS;
             float red[3];
 #pragma unroll
             for (int c = 0; c < 3; ++c)
                 red[c] = lm::combine4(s_part[(c * 4 + 0) * EPC + e], s_part[(c * 4 + 1) * EPC + e],
                                       s_part[(c * 4 + 2) * EPC + e], s_part[(c * 4 + 3) * EPC + e]);
-            const float prev = A.pot[env];
+            const float prev = prev_pot_in;
             float total;
             long long prog, rst;
-            lm::reward_done(P, row[0], row[10], row[11], o_pot[e], prev, red, A.progress[env], A.reset[env], total,
-                            prog, rst);
+            lm::reward_done(P, row[0], row[10], row[11], o_pot[e], prev, red, prog_in, reset_in, total, prog, rst);
+            row[0] = lm::clampf(row[0], clip);
+            row[10] = lm::clampf(row[10], clip);
+            row[11] = lm::clampf(row[11], clip);
             A.progress[env] = prog;
             A.reset[env] = rst;
             A.rew[env] = total;
@@ -741,11 +793,6 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
                 st_len += __shfl_xor_sync(0xffffffffu, st_len, o);
             }
             if (lane == 0) { s_stat[grp * 3 + 0] = st_rew; s_stat[grp * 3 + 1] = st_done; s_stat[grp * 3 + 2] = st_len; }
-        }
-        if (P.clip_obs < INFINITY) {  // uniform; the stored rows are clamped after the metrics were evaluated
-            __syncthreads();
-            const float c = P.clip_obs;
-            _Pragma("unroll 1") for (int i = tid; i < cnt * OBS; i += NT) o_obs[i] = lm::clampf(o_obs[i], c);
         }
     }
 
@@ -793,16 +840,6 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
             atomicAdd(slot + 1, d);
             atomicAdd(slot + 2, l);
             atomicAdd(slot + 3, (double)cnt);
-        }
-        if (A.bump && A.counter_dev != nullptr) {
-            // every CTA read the reset counter in its prologue; the last one to get here advances it for the next
-            // replay of a captured step (ticket in counter_dev[1])
-            __threadfence();
-            const unsigned long long t = atomicAdd(A.counter_dev + 1, 1ull);
-            if (t == (unsigned long long)gridDim.x - 1) {
-                A.counter_dev[1] = 0ull;
-                A.counter_dev[0] += 1ull;
-            }
         }
         if (bulk) bulk_wait_read0();  // smem must stay alive until the TMA engine has read it
     }
