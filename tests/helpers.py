@@ -124,27 +124,33 @@ def _circ_diff(a, b):
     return torch.minimum(d, (2 * math.pi - d).abs())
 
 
+REW_ATOL = 1e-6  # measured (tests/k1_deviation.py, profiles/r2_k1_deviation.txt): max |d rew| 1.5e-5 at |rew| ~ 1e2,
+REW_RTOL = 1e-6  # i.e. 2.4e-7 relative -- the per-dof sums are ordered differently from torch's vectorised reduction
+ANGLE_TOL = 1.5e-6  # measured 6.0e-7 (closed-form wrap) / 7.2e-7 (literal chain) on the circle: 1-3 ulp at |x| ~ pi
+
+
 def assert_k1_matches(got, ref, what=""):
-    """The parity bar: reset/progress bit-exact; floats within RTOL (+ATOL floor); angle columns
-    compared on the circle; reward allowed the potentials' measured deviation (the progress term
-    `potentials - prev_potentials` cancels two ~6e4 numbers)."""
+    """The parity bar (north_star: 1e-5 relative in fp32, reset indices bit-exact), with CONSTANT tolerances taken
+    from the measured deviation table: reset/progress/potentials/prev_potentials/height bit-exact; reward within
+    1e-6 + 1e-6*|rew| (10x inside the bar); angle columns within 1.5e-6 on the circle; other floats within 1e-5
+    relative (measured: bit-identical at 4096 envs; the bound covers torch's scalar-tail kernels at ragged N)."""
     assert torch.equal(got["reset_buf"], ref["reset_buf"]), f"{what}: reset_buf not bit-exact"
     assert torch.equal(got["progress_buf"], ref["progress_buf"]), f"{what}: progress_buf not bit-exact"
     assert torch.equal(got["prev_potentials"], ref["prev_potentials"]), f"{what}: prev_potentials must be a copy"
-    torch.testing.assert_close(got["potentials"], ref["potentials"], rtol=RTOL, atol=0.0, msg=f"{what}: potentials")
+    assert torch.equal(got["potentials"], ref["potentials"]), (
+        f"{what}: potentials not bit-exact (max |d| {float((got['potentials'] - ref['potentials']).abs().max())})")
     go, ro = got["obs"], ref["obs"]
     assert torch.equal(go[:, 0], ro[:, 0]), f"{what}: obs[:,0] (height) must be a bit-exact copy"
     ang_cols = [7, 8, 9]
     other = [c for c in range(go.shape[1]) if c not in ang_cols]
     torch.testing.assert_close(go[:, other], ro[:, other], rtol=RTOL, atol=ATOL, msg=f"{what}: obs")
     ad = _circ_diff(go[:, ang_cols], ro[:, ang_cols])
-    assert float(ad.max()) <= 4e-6 + RTOL * math.pi, f"{what}: angle columns differ by {float(ad.max())}"
+    assert float(ad.max()) <= ANGLE_TOL, f"{what}: angle columns differ by {float(ad.max())}"
     torch.testing.assert_close(got["up_vec"], ref["up_vec"], rtol=RTOL, atol=ATOL, msg=f"{what}: up_vec")
     torch.testing.assert_close(got["heading_vec"], ref["heading_vec"], rtol=RTOL, atol=ATOL, msg=f"{what}: heading_vec")
-    pot_dev = (got["potentials"] - ref["potentials"]).abs()
-    tol = ATOL + RTOL * ref["rew"].abs() + 2.0 * pot_dev
+    tol = REW_ATOL + REW_RTOL * ref["rew"].abs()
     bad = (got["rew"] - ref["rew"]).abs() > tol
-    # a reward branch (up>0.93 / ant q>0.99 count) may legitimately flip when its input sits within
+    # a reward branch (up>0.93 / heading>0.8 / ant q>0.99 count) may legitimately flip when its input sits within
     # one ulp of the threshold; such rows must be vanishingly rare
     assert int(bad.sum()) <= max(0, got["rew"].numel() // 100000), (
         f"{what}: reward mismatch on {int(bad.sum())} rows, max err {float((got['rew'] - ref['rew']).abs().max())}")

@@ -128,7 +128,7 @@ def test_k1_clip_obs_clamps_outputs_not_metrics(cuda_lib):
     # reward / reset are computed from the unclamped values, like the reference (the clamp of
     # envs/vec_env_rlgames.py:42 acts on a copy after calculate_metrics)
     assert torch.equal(got["reset_buf"], ref["reset_buf"])
-    torch.testing.assert_close(got["rew"], ref["rew"], rtol=1e-5, atol=2e-2)
+    torch.testing.assert_close(got["rew"], ref["rew"], rtol=helpers.REW_RTOL, atol=helpers.REW_ATOL)
 
 
 def test_k1_progress_increment_flag(cuda_lib):
@@ -208,3 +208,20 @@ def test_k1_fast_division_is_correctly_rounded(cuda_lib, robot):
     assert torch.equal(got["obs"][:, 12 + 2 * d + 6 * spec.num_sensors:], s["actions"])
     assert torch.equal(got["obs"][:, 12 + 2 * d:12 + 2 * d + 6 * spec.num_sensors],
                        s["sensors"].reshape(n, -1) * spec.contact_force_scale)
+
+
+def test_k1_measured_deviation_table_is_inside_the_bar(cuda_lib):
+    """The table DESIGN.md section 4 quotes (tests/k1_deviation.py; 4096 envs x 4 seeds per robot + the goldens):
+    every output except the three angle columns and the reward is BIT-identical to the oracle (itself bit-identical
+    to the verbatim reference functions); angles within 1.5e-6 on the circle; reward within 1e-6 relative."""
+    import k1_deviation as kd
+
+    for cases in (kd.synthetic_cases(), kd.golden_cases()):
+        for robot, rows in kd.measure(cases).items():
+            for name, a in rows.items():
+                if "circle" in name:
+                    assert a.max_abs <= helpers.ANGLE_TOL, (robot, name, a.max_abs)
+                elif name.startswith("rew"):
+                    assert a.max_rel <= 1e-6, (robot, name, a.max_rel)  # relative to max(|rew|, 1)
+                else:
+                    assert a.nbits == 0, (robot, name, a.nbits, a.max_abs)
