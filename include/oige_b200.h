@@ -28,11 +28,12 @@
 extern "C" {
 #endif
 
-#define OIGE_ABI_VERSION 2
+#define OIGE_ABI_VERSION 3
 #define OIGE_MAX_DOF 32      /* one lane per link in the articulation kernel */
 #define OIGE_MAX_LINKS 32
 #define OIGE_MAX_SPHERES 48  /* collision spheres per robot */
 #define OIGE_MAX_SENSORS 4
+#define OIGE_MAX_PAIRS 96    /* self-collision link pairs per robot */
 #define OIGE_STATS_SLOTS 2048  /* episode_stats is striped over slots: same-address fp64 atomics serialise at ~50 ns each in L2 */
 
 #define OIGE_OK 0
@@ -165,8 +166,23 @@ typedef struct OigeModelDesc {
     float friction_viscous;                  /* N s/m regularisation slope of the Coulomb cone */
     float limit_stiffness;                   /* N m/rad beyond a joint limit */
     float limit_damping;
-    float max_joint_velocity;                /* rad/s clamp (docs/transfering_policies_from_isaac_gym.md:71-77) */
-    float angular_damping;                   /* 1/s on the root angular velocity */
+    float max_joint_velocity;                /* JointAPI "Maximum Joint Velocity", rad/s (m/s for a prismatic joint); Isaac Sim
+                                                default 1e6 deg/s (docs/transfering_policies_from_isaac_gym.md:85-87) */
+    float angular_damping;                   /* RigidBodyAPI "Angular Damping", 1/s, on EVERY body: the root's angular
+                                                velocity decays by (1 - dt c) per substep, every other link receives the
+                                                torque -c I_link w_link; Isaac Sim default 0.05 (same doc :71-77) */
+    /* ---- ABI 3 ---- */
+    float max_angular_velocity;              /* RigidBodyAPI "Max Angular Velocity", rad/s (Isaac Sim default 5729.58 deg/s
+                                                = 100 rad/s): clamps |w| of the root body and, in reduced coordinates, each
+                                                hinge's relative angular velocity |qd|; <= 0: unlimited */
+    float max_depenetration_velocity;        /* m/s (cfg/task/Humanoid.yaml:62,90): the penalty springs see at most
+                                                max_depenetration_velocity * dt of penetration per substep; <= 0: unlimited */
+    float self_contact_stiffness;            /* N/m, sphere-sphere penalty between the links of a collision pair */
+    float self_contact_damping;              /* N s/m, only while approaching */
+    int32_t num_collision_pairs;             /* enable_self_collisions (cfg/task/Humanoid.yaml:80): unordered LINK pairs whose
+                                                collision spheres repel each other; 0 = no self-collision (Ant.yaml:82) */
+    int32_t pair_link_a[OIGE_MAX_PAIRS];
+    int32_t pair_link_b[OIGE_MAX_PAIRS];
 } OigeModelDesc;
 
 typedef struct OigeModel OigeModel; /* opaque; holds the immutable device-side model table */

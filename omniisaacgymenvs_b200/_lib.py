@@ -16,8 +16,9 @@ MAX_DOF = 32
 MAX_LINKS = 32
 MAX_SPHERES = 48
 MAX_SENSORS = 4
+MAX_PAIRS = 96
 STATS_SLOTS = 2048
-ABI_VERSION = 2
+ABI_VERSION = 3
 LIMIT_COST_HUMANOID = 0
 LIMIT_COST_ANT = 1
 
@@ -72,6 +73,9 @@ class OigeModelDesc(C.Structure):
         ("gravity", f32 * 3), ("contact_stiffness", f32), ("contact_damping", f32), ("friction_mu", f32),
         ("friction_viscous", f32), ("limit_stiffness", f32), ("limit_damping", f32), ("max_joint_velocity", f32),
         ("angular_damping", f32),
+        ("max_angular_velocity", f32), ("max_depenetration_velocity", f32), ("self_contact_stiffness", f32),
+        ("self_contact_damping", f32), ("num_collision_pairs", i32), ("pair_link_a", i32 * MAX_PAIRS),
+        ("pair_link_b", i32 * MAX_PAIRS),
     ]
 
 

@@ -51,6 +51,7 @@ struct OigeModel {
     int role_ok;          // K2-F applicable: trunk is a path, (roles, chain links per role) is an instantiated combination
     int nroles, maxc;     // roles per 32-env group; link slots per role the kernel is instantiated for (3 or 6)
     int group_floats;     // shared-memory floats (x32 lanes) of one group's scratch
+    int has_sc;           // the model has self-collision pairs: only K2-F integrates it
 };
 
 namespace oige {
@@ -99,6 +100,7 @@ struct DevModel {
     float sph_r[OIGE_MAX_SPHERES];
     float gravity[4];
     float k_c, d_c, mu, c_visc, k_lim, d_lim, max_qd, ang_damp;
+    float max_qd_lin, max_w, pen_cap_v, pad_f;  // prismatic clamp, root |w| clamp, depenetration cap (m/s); 1e30 = off
 };
 static_assert(sizeof(DevModel) % 16 == 0, "DevModel must be int4-copyable");
 
@@ -194,8 +196,10 @@ __device__ __forceinline__ bool contact_eval(const MT& M, int s, const M3& R, V3
     const V3 local = {M.sph_pos[0][s], M.sph_pos[1][s], M.sph_pos[2][s]};
     const float rad = M.sph_r[s];
     const V3 x = p + mulv(R, local);
-    const float pen = rad - (root_z + x.z);
-    if (!(pen > 0.f)) return false;
+    const float pen_raw = rad - (root_z + x.z);
+    if (!(pen_raw > 0.f)) return false;
+    // max_depenetration_velocity (cfg/task/Humanoid.yaml:62,90): the spring sees at most v_dep * dt of penetration
+    const float pen = fminf(pen_raw, M.pen_cap_v * dt);
     c.r = {x.x, x.y, x.z - rad};
     const V3 vp = lin(v) + cross(ang(v), c.r);
     const float vn = vp.z;
@@ -264,6 +268,22 @@ __device__ __forceinline__ void link_inertia_bias(const MT& M, int li, const M3&
     const V3 fg = m * grav;
     const V3 tg = cross(cw, fg);
     pA = mk6(ba - tg, bl - fg);
+    if (li > 0) {
+        // RigidBodyAPI angular damping on every body: the torque -c Ic w about the link's centre of mass (a pure
+        // couple, Ic = R Iloc R^T); the root's own damping is the velocity decay in integrate_root
+        const V3 wl = mulTv(R, w);
+        const float c = M.ang_damp;
+        pA.a[0] = fmaf(c, T[0] * wl.x + T[1] * wl.y + T[2] * wl.z, pA.a[0]);
+        pA.a[1] = fmaf(c, T[3] * wl.x + T[4] * wl.y + T[5] * wl.z, pA.a[1]);
+        pA.a[2] = fmaf(c, T[6] * wl.x + T[7] * wl.y + T[8] * wl.z, pA.a[2]);
+    }
+}
+
+// joint velocity limit: JointAPI max joint velocity; a hinge's relative angular velocity also obeys the body limit
+template <class MT>
+__device__ __forceinline__ float clamp_qd(const MT& M, int li, float qd) {
+    const float m = M.jtype[li] == OIGE_JOINT_PRISMATIC ? M.max_qd_lin : M.max_qd;
+    return fminf(fmaxf(qd, -m), m);
 }
 
 // Adds the linearly-implicit ground contacts of link li: P^T C P to the inertia, -wrench(F0) to the bias.
@@ -395,7 +415,9 @@ __device__ __forceinline__ void integrate_root(const MT& M, const V6& a, float d
     const V3 vdot = lin(a) + cross(w0, v0);  // classical acceleration of the root origin
     float damp = 1.f - dt * M.ang_damp;
     damp = damp < 0.f ? 0.f : damp;
-    const V3 w1 = damp * (w0 + dt * ang(a));
+    V3 w1 = damp * (w0 + dt * ang(a));
+    const float w2 = dot(w1, w1);
+    if (w2 > M.max_w * M.max_w) w1 = (M.max_w * rsqrtf(w2)) * w1;  // RigidBodyAPI max angular velocity of the root body
     const V3 v1 = v0 + dt * vdot;
     rvel = mk6(w1, v1);
     rpos = rpos + dt * v1;
@@ -642,7 +664,7 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
         // ---- integrate (semi-implicit Euler) ----------------------------------------------------------------
         if (is_joint) {
             qd = fmaf(dt, qdd, qd);
-            qd = fminf(fmaxf(qd, -M.max_qd), M.max_qd);
+            qd = clamp_qd(M, li, qd);
             q = fmaf(dt, qd, q);
         }
         if (is_root && !fixed_base) integrate_root(M, a, dt, rpos, rquat, rvel);
@@ -931,7 +953,7 @@ articulation_step_tpe_kernel(const DevModel* __restrict__ gmodel, const __grid_c
             }
             // integrate this joint (semi-implicit Euler); q/qd of link i are not read again this substep
             float qd = fmaf(dt, qdd, qdv[i]);
-            qd = fminf(fmaxf(qd, -M.max_qd), M.max_qd);
+            qd = clamp_qd(M, i, qd);
             qdv[i] = qd;
             qv[i] = fmaf(dt, qd, qv[i]);
             acarry = a;
@@ -1013,6 +1035,10 @@ static bool use_role_split(int64_t n, int num_links) {
 }
 
 bool k2_uses_role_kernel(const OigeModel* model, int64_t decision_n) {
+    if (model->has_sc) {  // self-collision is integrated by K2-F only, at every env count (a forced warp / thread mode fails)
+        const int m = knobs().mode;
+        return model->role_ok && m != 'w' && m != 't';
+    }
     return model->role_ok && use_role_split(decision_n, model->num_links);
 }
 
@@ -1056,19 +1082,23 @@ int role_dispatch(const OigeModel* model, const OigeTaskParams* P, const FArgs& 
         // staged once per CTA, and four groups is what one wave of 16384 envs needs on 148 SMs)
         const int force = knobs().epc;
         const bool big = force ? force == 128 : (dn + 31) / 32 > 3ll * sm_count();
-        if (big) return role_launch(env_step_role_kernel<6, 3, false, 128, 1, true>, 0, 3 * 128, 128, model, P, A, stream);
-        return role_launch(env_step_role_kernel<6, 3, false, 32, 3, true>, 1, 3 * 32, 32, model, P, A, stream);
+        if (model->has_sc) {  // self-collision pairs (Humanoid.yaml:80): the variant with the pair phase
+            if (big) return role_launch(env_step_role_kernel<6, 3, false, 128, 1, true, true>, 4, 3 * 128, 128, model, P, A, stream);
+            return role_launch(env_step_role_kernel<6, 3, false, 32, 3, true, true>, 5, 3 * 32, 32, model, P, A, stream);
+        }
+        if (big) return role_launch(env_step_role_kernel<6, 3, false, 128, 1, true, false>, 0, 3 * 128, 128, model, P, A, stream);
+        return role_launch(env_step_role_kernel<6, 3, false, 32, 3, true, false>, 1, 3 * 32, 32, model, P, A, stream);
     }
-    if (model->nroles == 4 && model->maxc == 3) {
-        if (tgt) return role_launch(env_step_role_kernel<3, 4, true, 32, 4, false>, 2, 4 * 32, 32, model, P, A, stream);
-        return role_launch(env_step_role_kernel<3, 4, false, 32, 4, false>, 3, 4 * 32, 32, model, P, A, stream);
+    if (model->nroles == 4 && model->maxc == 3 && !model->has_sc) {
+        if (tgt) return role_launch(env_step_role_kernel<3, 4, true, 32, 4, false, false>, 2, 4 * 32, 32, model, P, A, stream);
+        return role_launch(env_step_role_kernel<3, 4, false, 32, 4, false, false>, 3, 4 * 32, 32, model, P, A, stream);
     }
     return fail(OIGE_E_MODEL, "env_step_role_kernel: no instantiation for %d roles x %d links%s", model->nroles,
                 model->maxc, tgt ? " with position targets" : "");
 }
 
 bool role_variant_exists(const OigeModel* model, bool tgt) {
-    return (model->nroles == 3 && model->maxc == 6 && !tgt) || (model->nroles == 4 && model->maxc == 3);
+    return (model->nroles == 3 && model->maxc == 6 && !tgt) || (model->nroles == 4 && model->maxc == 3 && !model->has_sc);
 }
 
 inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
@@ -1140,6 +1170,10 @@ int k2_step(const OigeModel* model, const OigeTaskParams* P, const OigeState* st
         if (F.sens == nullptr && F.S > 0) F.use_bulk = F.use_bulk;  // sensors are optional for a physics-only call
         return role_dispatch(model, P, F, stream, dn);
     }
+    if (model->has_sc)
+        return fail(OIGE_E_MODEL, "articulation_step: the model has self-collision pairs, which only the role-split kernel "
+                                  "(K2-F) integrates, and that kernel does not serve this tree%s",
+                    A.targets != nullptr ? " with position targets" : "");
     if (model->tpe_ok && use_thread_per_env(dn)) {
         const int bs = 128;
         const unsigned tb = (unsigned)((n + bs - 1) / bs);
@@ -1278,6 +1312,7 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
                 for (int a = i; a > 0 && !trunk[a]; a = h->parent[a]) trunk[a] = true;
         int tidx[32], nt = 0, nh = 0, heads[32], hlen[32], tip[32];
         bool fits = L <= kRL && d->num_spheres <= OIGE_MAX_SPHERES;
+        const bool has_sc = d->num_collision_pairs > 0;
         for (int i = 0; i < 32; ++i) tidx[i] = -1;
         for (int i = 0; i < L && fits; ++i) {
             if (trunk[i]) {
@@ -1361,7 +1396,7 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
             for (int t = 0; t < nt; ++t) {
                 if (is_massless(rm->tlink[t])) { rm->town[t] = 1; continue; }
                 int pick = -1;
-                for (int r = 0; r < best_r; ++r)
+                for (int r = best_r - 1; r >= 0; --r)  // ties go to the higher role: role 0 carries the trunk sweep already
                     if (slot_of[r][t] >= 0 && own_t[r] < 0 && (pick < 0 || load[r] < load[pick])) pick = r;
                 if (pick >= 0) { own_t[pick] = t; rm->town[t] = 1; }
             }
@@ -1399,31 +1434,47 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
                 };
                 if (r == 0) add_seg(kSegTrunkKin, 1, nt - 1, kSegBarAfter, 0, 0);
                 const int first_work = ns;
-                if (own_t[r] >= 0) {
-                    const int sl = slot_of[r][own_t[r]];
-                    add_seg(kSegOwn, own_t[r], own_t[r], slot_written[sl] ? 0 : kSegSlotFirst, own_t[r], sl);
-                    slot_written[sl] = true;
-                }
-                int nchains = 0;
+                // chains of this role by position (head first)
+                int nchains = 0, ck0[8], ck1[8], cfl[8], catt[8], csl[8];
                 for (int a = 0; a < nh && fits; ++a) {
                     const int c = order[a];
                     if (owner[c] != r) continue;
-                    ++nchains;
-                    const int t = tidx[h->parent[heads[c]]], sl = slot_of[r][t];
+                    if (nchains >= 8) { fits = false; break; }
+                    const int t = tidx[h->parent[heads[c]]];
                     int sens = -1;
                     for (int s2 = 0; s2 < d->num_sensors; ++s2) if (d->sensor_link[s2] == tip[c]) sens = s2;
                     if (sens >= 0) { ++sensor_chains[r]; sensor_seen[sens] = true; }
                     int links[32], n = 0;
                     for (int cur = tip[c];; cur = h->parent[cur]) { links[n++] = cur; if (cur == heads[c]) break; }
-                    const int k0 = k;
+                    ck0[nchains] = k;
                     for (int j = n - 1; j >= 0; --j, ++k) rm->plink[r][k] = (unsigned char)links[j];  // head first
-                    int fl = (sens >= 0 ? kSegSensor : 0) | (slot_written[sl] ? 0 : kSegSlotFirst);
-                    slot_written[sl] = true;
-                    add_seg(kSegChain, k0, k - 1, fl, t, sl);
+                    ck1[nchains] = k - 1; cfl[nchains] = sens >= 0 ? kSegSensor : 0; catt[nchains] = t;
+                    csl[nchains] = slot_of[r][t];
+                    ++nchains;
                 }
                 rm->npos[r] = (unsigned char)k;
                 if (nchains == 0 || sensor_chains[r] > 1) fits = false;  // every role works; one sensor wrench per role
                 if (!fits) break;
+                if (has_sc) {
+                    // self-collision program: every kinematics sweep first (sphere centres and link velocities published
+                    // | barrier C), the pair phase (| barrier P), then the inertia sweeps
+                    for (int c = 0; c < nchains; ++c) add_seg(kSegChain, ck0[c], ck1[c], cfl[c] | kSegKinOnly, catt[c], csl[c]);
+                    if (fits) rm->seg_flag[r][ns - 1] |= kSegBarAfter;
+                    add_seg(kSegPairs, 0, 0, kSegBarAfter, 0, 0);
+                }
+                const int first_up = ns;
+                if (own_t[r] >= 0) {
+                    const int sl = slot_of[r][own_t[r]];
+                    add_seg(kSegOwn, own_t[r], own_t[r], slot_written[sl] ? 0 : kSegSlotFirst, own_t[r], sl);
+                    slot_written[sl] = true;
+                }
+                for (int c = 0; c < nchains; ++c) {
+                    const int fl = cfl[c] | (slot_written[csl[c]] ? 0 : kSegSlotFirst) | (has_sc ? kSegUpOnly : 0);
+                    slot_written[csl[c]] = true;
+                    add_seg(kSegChain, ck0[c], ck1[c], fl, catt[c], csl[c]);
+                }
+                if (!fits) break;
+                (void)first_up;
                 if (r == 0) {
                     add_seg(kSegTrunkUp, 0, nt - 1, kSegBarBefore, 0, 0);
                 } else {
@@ -1435,13 +1486,114 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
             for (int s2 = 0; s2 < d->num_sensors; ++s2) fits = fits && sensor_seen[s2];  // sensors sit on chain tips
             // scratch layout of a 32-env group (float offsets, x32 lanes)
             rm->oI = 0;
-            rm->oA = rm->oI + nslots * kHand;
+            // (with self-collision the hand-over region also holds the sphere centres between the kinematics and the
+            // inertia sweeps: 3 floats per collision sphere)
+            const int handover_floats = has_sc && 3 * d->num_spheres > nslots * kHand ? 3 * d->num_spheres : nslots * kHand;
+            rm->oA = rm->oI + handover_floats;
             rm->oK = rm->oA + npub * 6;
             rm->oT = rm->oK + nt * kKin;
             rm->oS = rm->oT + (nt - 1) * 4;
             rm->oM = rm->oS + (best_r == 3 ? 0 : d->num_sensors * 7);  // the 3-role variants keep the sensor frame in registers
             rm->oL = rm->oM + 2;
             rm->group_floats = rm->oL + best_r * maxc * kPu;
+            // ---- self-collision tables ----
+            rm->has_sc = has_sc ? 1 : 0;
+            if (has_sc && fits) {
+                int owner_of_link[32], sph0[32], sphn[32];
+                for (int i = 0; i < L; ++i) { owner_of_link[i] = tidx[i] >= 0 ? 0 : -1; sphn[i] = 0; sph0[i] = 0; }
+                for (int i = 0; i < L; ++i) {
+                    if (tidx[i] >= 0) { rm->w_idx[i] = (unsigned char)tidx[i]; rm->rec_off[i] = (unsigned short)(rm->oK + tidx[i] * kKin); }
+                }
+                // a trunk link's pairs (and wrench) belong to the role that evaluates its own inertia
+                for (int r = 0; r < best_r; ++r)
+                    if (own_t[r] >= 0) owner_of_link[rm->tlink[own_t[r]]] = r;
+                for (int r = 0; r < best_r; ++r)
+                    for (int k2 = 0; k2 < rm->npos[r]; ++k2) {
+                        const int li = rm->plink[r][k2];
+                        owner_of_link[li] = r;
+                        rm->w_idx[li] = (unsigned char)(kRT + k2);
+                        rm->rec_off[li] = (unsigned short)(rm->oL + (r * maxc + k2) * kPu);
+                    }
+                // spheres in the device order (sorted by link, stable): first sphere / count per link, bounding radius
+                int pos2 = 0;
+                for (int i = 0; i < L; ++i) {
+                    sph0[i] = pos2;
+                    for (int s2 = 0; s2 < d->num_spheres; ++s2) if (d->sphere_link[s2] == i) ++pos2;
+                    sphn[i] = pos2 - sph0[i];
+                }
+                auto sphere_at = [&](int i, int k2, float* c) {  // k2-th sphere of link i in device order
+                    int seen = 0;
+                    for (int s2 = 0; s2 < d->num_spheres; ++s2) {
+                        if (d->sphere_link[s2] != i) continue;
+                        if (seen++ == k2) { for (int q = 0; q < 3; ++q) c[q] = d->sphere_pos[s2][q]; return d->sphere_radius[s2]; }
+                    }
+                    return 0.f;
+                };
+                for (int i = 0; i < L; ++i) {
+                    if (sphn[i] == 0) continue;
+                    float c0[3], c1[3], mid[3];
+                    sphere_at(i, 0, c0); sphere_at(i, sphn[i] - 1, c1);
+                    for (int q = 0; q < 3; ++q) mid[q] = 0.5f * (c0[q] + c1[q]);
+                    float br = 0.f;
+                    for (int k2 = 0; k2 < sphn[i]; ++k2) {
+                        float c[3];
+                        const float rad = sphere_at(i, k2, c);
+                        const float dd = sqrtf((c[0] - mid[0]) * (c[0] - mid[0]) + (c[1] - mid[1]) * (c[1] - mid[1]) +
+                                               (c[2] - mid[2]) * (c[2] - mid[2])) + rad;
+                        if (dd > br) br = dd;
+                    }
+                    rm->brad[i] = br * 1.0001f + 1e-6f;  // (the broad phase must never cut a touching pair)
+                }
+                // directed pairs, grouped by role and sorted by the own link
+                int npairs = 0;
+                for (int r = 0; r < best_r && fits; ++r) {
+                    rm->sc_off[r] = (unsigned char)npairs;
+                    for (int a = 0; a < L && fits; ++a) {
+                        if (owner_of_link[a] != r) continue;
+                        for (int k2 = 0; k2 < d->num_collision_pairs; ++k2) {
+                            int la = d->pair_link_a[k2], lb = d->pair_link_b[k2];
+                            if (la < 0 || la >= L || lb < 0 || lb >= L || la == lb || sphn[la] == 0 || sphn[lb] == 0 ||
+                                owner_of_link[la] < 0 || owner_of_link[lb] < 0) { fits = false; break; }
+                            if (lb == a) { const int t2 = la; la = lb; lb = t2; }
+                            if (la != a) continue;
+                            const bool both = owner_of_link[lb] == r;  // both links are this role's: evaluated once
+                            if (both && lb < la) continue;
+                            if (npairs >= kSCMax || npairs >= 255) { fits = false; break; }
+                            rm->sc_a[npairs] = (unsigned char)la; rm->sc_b[npairs] = (unsigned char)(lb | (both ? 128 : 0));
+                            ++npairs;
+                        }
+                    }
+                }
+                for (int r = best_r; r < 8; ++r) rm->sc_off[r] = (unsigned char)npairs;
+                for (int r = 0; r < best_r; ++r) fits = fits && rm->sc_off[r + 1] - rm->sc_off[r] <= 64;  // candidate bit mask
+                // Bounding centres (3 floats per link with spheres) live in memory that is dead between the kinematics and
+                // the inertia sweeps: floats 7..12 of the records of the role's own massless intermediate links (two
+                // centres each), then the published-acceleration rows and the tail of the sphere-centre region.
+                {
+                    int pool[64], npool = 0, used = 0;
+                    auto is_massless2 = [&](int i) {
+                        bool zero = i > 0 && d->mass[i] == 0.f && sphn[i] == 0;
+                        for (int k2 = 0; k2 < 6; ++k2) zero = zero && d->inertia[i][k2] == 0.f;
+                        for (int s2 = 0; s2 < d->num_sensors; ++s2) zero = zero && d->sensor_link[s2] != i;
+                        return zero;
+                    };
+                    for (int r = 0; r < best_r; ++r)
+                        for (int k2 = 0; k2 < rm->npos[r]; ++k2)
+                            if (is_massless2(rm->plink[r][k2]) && npool + 2 <= 64) {
+                                const int base = rm->oL + (r * maxc + k2) * kPu;
+                                pool[npool++] = base + 7; pool[npool++] = base + 10;
+                            }
+                    for (int q = 0; q + 3 <= npub * 6 && npool < 64; q += 3) pool[npool++] = rm->oA + q;
+                    for (int q = 3 * d->num_spheres; q + 3 <= handover_floats && npool < 64; q += 3) pool[npool++] = rm->oI + q;
+                    for (int i = 0; i < L; ++i) {
+                        if (sphn[i] == 0) continue;
+                        if (used >= npool) { fits = false; break; }
+                        rm->ctr_off[i] = (unsigned short)pool[used++];
+                    }
+                }
+                // the sphere centres live in the hand-over slots' memory during the kinematics / pair phases
+                if (kRT + maxc > 32 || rm->group_floats > max_group_floats) fits = false;
+            }
         }
         role_ok = (fits && h->tpe_ok) ? 1 : 0;
         role_nroles = best_r; role_maxc = maxc;
@@ -1487,7 +1639,11 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
     }
     for (int k = 0; k < 3; ++k) h->gravity[k] = d->gravity[k];
     h->k_c = d->contact_stiffness; h->d_c = d->contact_damping; h->mu = d->friction_mu; h->c_visc = d->friction_viscous;
-    h->k_lim = d->limit_stiffness; h->d_lim = d->limit_damping; h->max_qd = d->max_joint_velocity; h->ang_damp = d->angular_damping;
+    h->k_lim = d->limit_stiffness; h->d_lim = d->limit_damping; h->ang_damp = d->angular_damping;
+    h->max_w = d->max_angular_velocity > 0.f ? d->max_angular_velocity : 1e30f;
+    h->max_qd_lin = d->max_joint_velocity > 0.f ? d->max_joint_velocity : 1e30f;
+    h->max_qd = fminf(h->max_qd_lin, h->max_w);
+    h->pen_cap_v = d->max_depenetration_velocity > 0.f ? d->max_depenetration_velocity : 1e30f;
 
     const int tpe_ok = h->tpe_ok;
     void* dev_role = nullptr;
@@ -1495,6 +1651,8 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
         for (int k = 0; k < 4; ++k) rm->gravity[k] = h->gravity[k];
         rm->k_c = h->k_c; rm->d_c = h->d_c; rm->mu = h->mu; rm->c_visc = h->c_visc; rm->k_lim = h->k_lim;
         rm->d_lim = h->d_lim; rm->max_qd = h->max_qd; rm->ang_damp = h->ang_damp;
+        rm->max_qd_lin = h->max_qd_lin; rm->max_w = h->max_w; rm->pen_cap_v = h->pen_cap_v;
+        rm->k_self = d->self_contact_stiffness; rm->d_self = d->self_contact_damping;
         for (int i = 0; i < L; ++i) {
             for (int k = 0; k < 3; ++k) { rm->jpos[k][i] = h->jpos[k][i]; rm->axis[k][i] = h->axis[k][i]; rm->com[k][i] = h->com[k][i]; }
             for (int k = 0; k < 4; ++k) rm->jquat[k][i] = h->jquat[k][i];
@@ -1534,6 +1692,7 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
     OigeModel* m = new OigeModel();
     m->dev_table = dev; m->dev_role = dev_role; m->num_links = L; m->num_dof = L - 1; m->num_sensors = d->num_sensors;
     m->tpe_ok = tpe_ok; m->role_ok = role_ok; m->nroles = role_nroles; m->maxc = role_maxc; m->group_floats = group_floats;
+    m->has_sc = d->num_collision_pairs > 0 ? 1 : 0;
     return m;
 }
 

@@ -31,8 +31,9 @@ constexpr int kRPos = 8;     // chain links per role (>= MAXC)
 constexpr int kRT = 4;       // trunk links incl. the root
 constexpr int kRSlots = 8;   // hand-over slots
 constexpr int kRSeg = 8;     // segments per role
-constexpr int kSegTrunkKin = 0, kSegOwn = 1, kSegChain = 2, kSegTrunkUp = 3;
-constexpr int kSegBarBefore = 1, kSegBarAfter = 2, kSegSlotFirst = 4, kSegSensor = 8;
+constexpr int kSegTrunkKin = 0, kSegOwn = 1, kSegChain = 2, kSegTrunkUp = 3, kSegPairs = 4;
+constexpr int kSegBarBefore = 1, kSegBarAfter = 2, kSegSlotFirst = 4, kSegSensor = 8, kSegKinOnly = 16, kSegUpOnly = 32;
+constexpr int kSCMax = 144;  // directed self-collision link pairs (Humanoid: 2 x 66)
 constexpr int kKin = 19;     // quat 4, p 3, v 6, b 6
 constexpr int kPu = 13;      // s 6, U/d 6, u'''
 constexpr int kHand = 27;    // I^a 21, p^a 6
@@ -43,6 +44,8 @@ struct alignas(16) RoleModel {
     int oI, oA, oK, oT, oS, oM, oL, maxc;   // float offsets (x32 lanes) of the regions of a group's scratch
     float gravity[4];
     float k_c, d_c, mu, c_visc, k_lim, d_lim, max_qd, ang_damp;
+    float max_qd_lin, max_w, pen_cap_v, k_self, d_self;
+    int has_sc, pad_i[2];
     float jpos[3][kRL];
     float jquat[4][kRL];
     float axis[3][kRL];
@@ -63,7 +66,14 @@ struct alignas(16) RoleModel {
     unsigned char seg_att[4][kRSeg], seg_slot[4][kRSeg];
     unsigned char tlink[kRT], town[kRT], tpub[kRT];      // trunk idx -> link, own inertia handed to a role?, xA index (255: none)
     unsigned char ts_begin[kRT + 1], ts_slot[kRSlots];   // hand-over slots attached to trunk link t
-    unsigned char pad[15];
+    // ---- self-collision (enable_self_collisions): directed link pairs (a = a link of the role, b = its partner) ----
+    unsigned char sc_off[8];                              // role r evaluates pairs [sc_off[r], sc_off[r + 1])
+    unsigned char sc_a[kSCMax], sc_b[kSCMax];
+    unsigned char w_idx[kRL];                             // link -> entry of its role's wrench accumulator
+    unsigned short rec_off[kRL];                          // link -> float offset (x32 lanes) of its (quat, p, v) record
+    float brad[kRL];                                      // bounding radius about the midpoint of its first / last sphere
+    unsigned short ctr_off[kRL];                          // link -> float offset (x32 lanes) of its bounding centre (3 floats)
+    unsigned char pad[7];
 };
 static_assert(sizeof(RoleModel) % 16 == 0, "RoleModel must be int4-copyable");
 
@@ -194,9 +204,100 @@ __device__ __forceinline__ void joint_reduce(const MT& M, int i, const M3& R, V3
     }
 }
 
+// ---- self-collision (enable_self_collisions, cfg/task/Humanoid.yaml:80) -------------------------------------------------
+// Explicit sphere-sphere penalty between the links of a collision pair, evaluated at the state the substep starts from
+// (an implicit pair force would couple two branches of the tree, i.e. close a kinematic loop, and break the O(n)
+// recursion).  Every role evaluates the DIRECTED pairs (a, b) whose link a it owns and keeps only the wrench on a;
+// both directions run the same arithmetic on the same operands (orientation fixed by the sphere numbers), so the two
+// forces are equal and opposite to the bit.  Force along the centre line at the midpoint of the overlap:
+// f = k pen - d vn (damping while approaching only), no friction.
+
+// world centres of link `link`'s collision spheres -> C[sphere][xyz] (stride 32), and the centre of the link's bounding
+// sphere (midpoint of its first and last sphere, radius M.brad) -> ctr[xyz]
+template <class MT>
+__device__ __forceinline__ void publish_spheres(const MT& M, int link, const M3& R, V3 p, float* C, float* ctr) {
+    const int s0 = M.sph_start[link], s1 = s0 + M.sph_count[link];
+    if (s1 == s0) return;
+    V3 first = {0.f, 0.f, 0.f}, x = {0.f, 0.f, 0.f};
+    for (int k = s0; k < s1; ++k) {
+        x = p + mulv(R, V3{M.sph_pos[0][k], M.sph_pos[1][k], M.sph_pos[2][k]});
+        C[(3 * k) * 32] = x.x; C[(3 * k + 1) * 32] = x.y; C[(3 * k + 2) * 32] = x.z;
+        if (k == s0) first = x;
+    }
+    ctr[0] = 0.5f * (first.x + x.x); ctr[32] = 0.5f * (first.y + x.y); ctr[64] = 0.5f * (first.z + x.z);
+}
+__device__ __forceinline__ V3 sphere_centre(const float* C, int k) {
+    return {C[(3 * k) * 32], C[(3 * k + 1) * 32], C[(3 * k + 2) * 32]};
+}
+// One sphere pair in contact: force on link a (and, BOTH: the opposite one on link b, which this role owns too) about O
+// -> W (first touch stores, later ones add).  The orientation is fixed by the sphere numbers, so the roles on either
+// side of a pair compute the same bits.
+template <class MT, int NW>
+__device__ __forceinline__ void sphere_contact(const MT& M, const float* C, const float* G0, int a, int b, int i, int j,
+                                            float dt, bool both, float (&W)[NW][6], unsigned& wmask) {
+    const bool a_lo = i < j;
+    const int lo = a_lo ? i : j, hi = a_lo ? j : i;
+    const V3 clo = sphere_centre(C, lo), chi = sphere_centre(C, hi);
+    const float rlo_ = M.sph_r[lo], rhi_ = M.sph_r[hi];
+    const V3 d = clo - chi;
+    const float d2 = dot(d, d);
+    if (!(d2 > 1e-18f)) return;
+    const float dist = sqrtf(d2), pen = (rlo_ + rhi_) - dist;
+    const V3 n = (1.f / dist) * d;  // from the higher-numbered sphere to the lower one
+    const V3 pc = chi + (rhi_ - 0.5f * pen) * n;
+    const float* rlo = G0 + (int)M.rec_off[a_lo ? a : b] * 32;
+    const float* rhi = G0 + (int)M.rec_off[a_lo ? b : a] * 32;
+    const V3 wlo = {rlo[7 * 32], rlo[8 * 32], rlo[9 * 32]}, ulo = {rlo[10 * 32], rlo[11 * 32], rlo[12 * 32]};
+    const V3 whi = {rhi[7 * 32], rhi[8 * 32], rhi[9 * 32]}, uhi = {rhi[10 * 32], rhi[11 * 32], rhi[12 * 32]};
+    const V3 vrel = (ulo + cross(wlo, pc)) - (uhi + cross(whi, pc));
+    const float vn = dot(vrel, n);
+    const float f = M.k_self * fminf(pen, M.pen_cap_v * dt) - (vn < 0.f ? M.d_self * vn : 0.f);
+    if (!(f > 0.f)) return;
+    const V3 F = (a_lo ? f : -f) * n;  // on link a
+    const V3 tq = cross(pc, F);
+    const float wr[6] = {tq.x, tq.y, tq.z, F.x, F.y, F.z};
+    {
+        const int w = M.w_idx[a];
+        const bool seen = (wmask >> w) & 1u;
+#pragma unroll
+        for (int k = 0; k < 6; ++k) W[w][k] = (seen ? W[w][k] : 0.f) + wr[k];
+        wmask |= 1u << w;
+    }
+    if (both) {
+        const int w = M.w_idx[b];
+        const bool seen = (wmask >> w) & 1u;
+#pragma unroll
+        for (int k = 0; k < 6; ++k) W[w][k] = (seen ? W[w][k] : 0.f) - wr[k];
+        wmask |= 1u << w;
+    }
+}
+// narrow phase of the link pair (a, b) = entry k of the role's list: every sphere of a against every sphere of b.  A hit
+// is only QUEUED here (per-thread list in local memory, touched on contact only): contacts are rare and lane-divergent,
+// so they are evaluated afterwards, all lanes popping their own queue together, instead of one lane at a time in the
+// middle of the test loops.
+constexpr int kSCQueue = 32;
+template <class MT>
+__device__ __forceinline__ void self_contact_tests(const MT& M, const float* C, int a, int b, int k, unsigned (&q)[kSCQueue],
+                                                   int& nq) {
+    const int a0 = M.sph_start[a], a1 = a0 + M.sph_count[a], b0 = M.sph_start[b], b1 = b0 + M.sph_count[b];
+    for (int i = a0; i < a1; ++i) {
+        const V3 ca = sphere_centre(C, i);
+        const float ra = M.sph_r[i];
+        for (int j = b0; j < b1; ++j) {
+            const V3 d = ca - sphere_centre(C, j);
+            const float rr = ra + M.sph_r[j];
+            if (dot(d, d) < rr * rr) {
+                q[nq & (kSCQueue - 1)] = (unsigned)k << 16 | (unsigned)i << 8 | (unsigned)j;
+                ++nq;  // (more than kSCQueue contacts of one role's links in one env: flagged by the caller)
+            }
+        }
+    }
+}
+
 // SREG: the sensor link's frame waits in registers (Humanoid: shared memory is full) or in shared memory (xS; the
 // four-role variants run at 128 registers per thread)
-template <int MAXC, int NR, bool TGT, int EPC, int MINB, bool SREG>
+// SC: the model has self-collision pairs (per substep two more group barriers: sphere centres published | pair forces)
+template <int MAXC, int NR, bool TGT, int EPC, int MINB, bool SREG, bool SC>
 __global__ void __launch_bounds__(NR * EPC, MINB)
 env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant__ OigeTaskParams P,
                      const __grid_constant__ FArgs A) {
@@ -395,12 +496,20 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
     Q4 sq = {1.f, 0.f, 0.f, 0.f};  // frame of the sensor link at the start of the last substep
     V3 sp = {0.f, 0.f, 0.f};
     const int nseg = M.nseg[role];
+    // self-collision: sphere centres live in the hand-over slots' memory (dead until the first chain hands over), the
+    // wrenches on this role's own links in a per-thread array that is only touched when a pair is in contact
+    float* const xC = xI;
+    float W[SC ? kRT + MAXC : 1][6];
+    unsigned wmask = 0u;
+    V6 vkeep = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}}, bkeep = vkeep;  // velocity, velocity-product sum at the tip of the chain swept last
+    int keep_last = -1;
 
     for (int step = 0; step < A.substeps; ++step) {
         const bool last = (step == A.substeps - 1);
         float root_z = 0.f;
         S6 carryI;
         V6 carryP;
+        if (SC) wmask = 0u;
         // ---- S0 / S1 / S2a: the role's SEGMENTS.  One loop body serves the trunk kinematics (role 0), the chains
         // (kinematics head -> tip, then articulated inertia tip -> head), the own inertia of a trunk link taken off
         // role 0's hands, and the trunk's bottom-up sweep (role 0): ONE copy of every sweep in the instruction stream
@@ -410,11 +519,61 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
             const int kind = M.seg_kind[role][sg], sflag = M.seg_flag[role][sg];
             const int first = M.seg_first[role][sg], lastl = M.seg_last[role][sg];
             if (sflag & kSegBarBefore) group_barrier(bar_id, GT);
+            if (SC && kind == kSegPairs) {
+                // ---- pair phase: broad phase on the links' bounding spheres, narrow phase sphere by sphere -------
+                // (a pair whose links both belong to this role is listed once, flagged in bit 7 of sc_b)
+                // Phase 1 (warp-uniform loop over the role's list): bounding-sphere test, one candidate bit per pair.
+                // Phase 2: every lane pops ITS OWN next candidate and runs the sphere-by-sphere test on it -- lanes work on
+                // different pairs at the same time (the scratch is laid out [float][lane], so lane-dependent indices stay
+                // conflict-free), the warp iterates max-over-lanes times instead of once per pair any lane flagged.
+                const int k0 = M.sc_off[role], k1 = M.sc_off[role + 1];
+                unsigned long long cand = 0ull;
+                {
+                    int prev_a = -1;
+                    V3 ma = {0.f, 0.f, 0.f};
+                    float ra = 0.f;
+                    for (int k = k0; k < k1; ++k) {
+                        const int a = M.sc_a[k], b = M.sc_b[k] & 127;
+                        if (a != prev_a) {
+                            const float* c = G0 + (int)M.ctr_off[a] * 32;
+                            ma = {c[0], c[32], c[64]};
+                            ra = M.brad[a];
+                            prev_a = a;
+                        }
+                        const float* c = G0 + (int)M.ctr_off[b] * 32;
+                        const V3 d = {ma.x - c[0], ma.y - c[32], ma.z - c[64]};
+                        const float rr = ra + M.brad[b];
+                        if (dot(d, d) < rr * rr) cand |= 1ull << (k - k0);
+                    }
+                }
+                unsigned cq[kSCQueue];
+                int nq = 0;
+                while (__any_sync(0xffffffffu, cand != 0ull)) {
+                    if (cand != 0ull) {
+                        const int k = k0 + __ffsll((long long)cand) - 1;
+                        cand &= cand - 1ull;
+                        self_contact_tests(M, xC, M.sc_a[k], M.sc_b[k] & 127, k, cq, nq);
+                    }
+                }
+                if (nq > kSCQueue) { xM[32] = 1.f; nq = kSCQueue; }  // cannot happen with <= 48 spheres; parked loudly if it does
+                // Phase 3: the queued contacts, every lane popping its own
+                while (__any_sync(0xffffffffu, nq > 0)) {
+                    if (nq > 0) {
+                        const unsigned e = cq[--nq];
+                        const int k = (int)(e >> 16), bb = M.sc_b[k];
+                        sphere_contact(M, xC, G0, M.sc_a[k], bb & 127, (int)(e >> 8) & 255, (int)e & 255, dt, (bb & 128) != 0, W, wmask);
+                    }
+                }
+                if (sflag & kSegBarAfter) group_barrier(bar_id, GT);
+                continue;
+            }
             if (kind != kSegTrunkKin) root_z = xM[0];
             const bool chain = kind == kSegChain;
+            const bool do_kin = kind == kSegTrunkKin || (chain && !(SC && (sflag & kSegUpOnly)));
+            const bool do_up = kind != kSegTrunkKin && !(SC && (sflag & kSegKinOnly));
             V6 v, b;
             // ---- kinematics sweep: parent -> child -----------------------------------------------------------
-            if (kind == kSegTrunkKin || chain) {
+            if (do_kin) {
                 KinCtx c;
                 if (chain) {
                     const float* k = xK + M.seg_att[role][sg] * kKin * 32;
@@ -434,6 +593,7 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
                     for (int j = 0; j < 6; ++j) { k[(7 + j) * 32] = c.v.a[j]; k[(13 + j) * 32] = c.b.a[j]; }
                 }
                 c.R = qmat(c.q);
+                if (SC && !chain) publish_spheres(M, 0, c.R, c.p, xC, G0 + (int)M.ctr_off[0] * 32);  // the root body's spheres
                 for (int i = first; i <= lastl; ++i) {
                     int link;
                     float qj, qdj;
@@ -443,11 +603,19 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
                     float* dst = chain ? LS + i * kPu * 32 : xK + i * kKin * 32;
                     dst[0] = c.q.w; dst[32] = c.q.x; dst[64] = c.q.y; dst[96] = c.q.z;
                     dst[4 * 32] = c.p.x; dst[5 * 32] = c.p.y; dst[6 * 32] = c.p.z;
+                    // (self-collision reads a body's velocity from its record; a massless intermediate link's floats
+                    // 7..12 may hold the bounding centres of two bodies instead)
+                    if (!chain || (SC && !M.massless[link])) {
+#pragma unroll
+                        for (int j = 0; j < 6; ++j) dst[(7 + j) * 32] = c.v.a[j];
+                    }
                     if (!chain) {
 #pragma unroll
-                        for (int j = 0; j < 6; ++j) { dst[(7 + j) * 32] = c.v.a[j]; dst[(13 + j) * 32] = c.b.a[j]; }
+                        for (int j = 0; j < 6; ++j) dst[(13 + j) * 32] = c.b.a[j];
                     }
+                    if (SC) publish_spheres(M, link, c.R, c.p, xC, G0 + (int)M.ctr_off[link] * 32);
                 }
+                if (SC && chain) { vkeep = c.v; bkeep = c.b; keep_last = lastl; }
                 if (chain && last && (sflag & kSegSensor)) {  // the foot's frame is needed again after the downward sweep
                     if (SREG) {
                         sq = c.q; sp = c.p;  // (registers: they only stay live across barrier waits of the chain roles)
@@ -460,8 +628,33 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
                 v = c.v; b = c.b;  // of the tip: walked back up with the inertia sweep
             }
             // ---- articulated-inertia sweep: child -> parent, I^a / p^a carried in registers ---------------------
-            if (kind != kSegTrunkKin) {
+            if (do_up) {
                 const bool trunk_up = kind == kSegTrunkUp;
+                if (SC && chain) {
+                    // the kinematics ran in an earlier segment: the tip's velocity and velocity-product sum are still in
+                    // registers for the chain swept last, else they are rebuilt from the attach link down the stored frames
+                    if (keep_last == lastl) {
+                        v = vkeep; b = bkeep;
+                    } else {
+                        const float* k = xK + M.seg_att[role][sg] * kKin * 32;
+#pragma unroll
+                        for (int j = 0; j < 6; ++j) { v.a[j] = k[(7 + j) * 32]; b.a[j] = k[(13 + j) * 32]; }
+                        for (int i = first; i <= lastl; ++i) {
+                            const int link = M.plink[role][i];
+                            const float* r2 = LS + i * kPu * 32;
+                            const M3 R = qmat(Q4{r2[0], r2[32], r2[64], r2[96]});
+                            const V3 p = {r2[4 * 32], r2[5 * 32], r2[6 * 32]};
+                            const V3 axis = {M.axis[0][link], M.axis[1][link], M.axis[2][link]};
+                            const V6 sj = joint_subspace(M.jtype[link] == OIGE_JOINT_PRISMATIC, mulv(R, axis), p);
+                            const float qdj = rsel(qdr, i);
+#pragma unroll
+                            for (int j = 0; j < 6; ++j) v.a[j] = fmaf(sj.a[j], qdj, v.a[j]);
+                            const V6 cc = velocity_product(v, sj, qdj);
+#pragma unroll
+                            for (int j = 0; j < 6; ++j) b.a[j] += cc.a[j];
+                        }
+                    }
+                }
                 for (int i = lastl; i >= first; --i) {
                     const int link = chain ? M.plink[role][i] : M.tlink[i];
                     float* src = chain ? LS + i * kPu * 32 : xK + i * kKin * 32;
@@ -480,6 +673,13 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
                         for (int j = 0; j < 6; ++j) pA.a[j] = 0.f;
                     } else {
                         own_inertia(M, link, R, p, v, b, root_z, dt, grav, IA, pA);
+                    }
+                    if (SC) {  // self-collision wrench on this link (held by the role that evaluates its pairs): an external force
+                        const int w = M.w_idx[link];
+                        if ((wmask >> w) & 1u) {
+#pragma unroll
+                            for (int j = 0; j < 6; ++j) pA.a[j] -= W[w][j];
+                        }
                     }
                     if (i != lastl) {
 #pragma unroll
@@ -543,7 +743,7 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
                     for (int j = 0; j < 6; ++j) ap.a[j] = fmaf(k[j * 32], acc, ap.a[j]);
                     float* x = xT + (t - 1) * 4 * 32;
                     float qd = fmaf(dt, acc, x[32]);
-                    qd = fminf(fmaxf(qd, -M.max_qd), M.max_qd);
+                    qd = clamp_qd(M, M.tlink[t], qd);
                     x[32] = qd;
                     x[0] = fmaf(dt, qd, x[0]);
                 }
@@ -561,6 +761,7 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
         for (int sg = 0; sg < nseg; ++sg) {
             if (M.seg_kind[role][sg] != kSegChain) continue;
             const int sflag = M.seg_flag[role][sg];
+            if (SC && (sflag & kSegKinOnly)) continue;  // (a chain appears twice in a self-collision program)
             const int first = M.seg_first[role][sg], lastl = M.seg_last[role][sg];
             const bool sens_chain = last && (sflag & kSegSensor) && A.sens != nullptr;
             V6 ap;
@@ -589,7 +790,7 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
                     for (int j = 0; j < 6; ++j) b.a[j] += cc.a[j];
                 }
                 float qd = fmaf(dt, qdd, qd0);
-                qd = fminf(fmaxf(qd, -M.max_qd), M.max_qd);
+                qd = clamp_qd(M, M.plink[role][i], qd);
                 rput(qdr, i, qd);
                 rput(qr, i, fmaf(dt, qd, rsel(qr, i)));
             }

@@ -117,6 +117,7 @@ HUMANOID = dict(
     density=1000.0,
     spawn_height=1.34,                    # tasks/humanoid.py:61
     sensor_bodies=["right_foot", "left_foot"],
+    self_collision=True,                  # cfg/task/Humanoid.yaml:80 (enable_self_collisions: True; Ant.yaml:82 False)
     # per-DoF order inside a multi-DoF body as the reference lists it (tasks/humanoid.py:82-107:
     # thigh x (45), y (135), z (45)); kinematic chain order stays the MJCF one (x, z, y)
     dof_order_in_body={"right_thigh": ["right_hip_x", "right_hip_y", "right_hip_z"],

@@ -99,8 +99,17 @@ class ArticulationModel:
     friction_viscous: float = 2.0e3
     limit_stiffness: float = 2.0e3
     limit_damping: float = 2.0e1
-    max_joint_velocity: float = 100.0
-    angular_damping: float = 0.0
+    # Isaac Sim USD defaults the reference's assets run with (docs/transfering_policies_from_isaac_gym.md:71-77,85-87):
+    # angular damping 0.05 on every body, max angular velocity 5729.58 deg/s, max joint velocity 1e6 deg/s.  (The Isaac
+    # Gym values of the same table -- 0.0, 64 rad/s, 100 rad/s -- are a `sim.b200` override away.)
+    max_joint_velocity: float = 1.0e6 * math.pi / 180.0
+    angular_damping: float = 0.05
+    max_angular_velocity: float = 5729.58008 * math.pi / 180.0
+    max_depenetration_velocity: float = 10.0   # cfg/task/Humanoid.yaml:62,90
+    self_contact_stiffness: float = 3.0e3      # explicit sphere-sphere penalty (DESIGN.md "self-collision")
+    self_contact_damping: float = 3.0e1
+    enable_self_collisions: bool = False       # cfg/task/Humanoid.yaml:80 (True), Ant.yaml:82 (False)
+    collision_pairs: np.ndarray = field(default_factory=lambda: np.zeros((0, 2), np.int32))  # [P,2] link pairs
     fixed_base: bool = False      # link 0 welded to the world
 
     @property
@@ -236,6 +245,18 @@ def build_model(name: str, **overrides) -> ArticulationModel:
         dof_names=dof_names, dof_body_names=dof_body_names, joint_gears=gears,
         spawn_height=table["spawn_height"], link_names=link_names,
     )
+    # self-collision candidates, PhysX articulation semantics: every pair of BODIES with collision shapes except a body
+    # and its parent (jointed links never collide); expressed on the links that carry the bodies' spheres
+    body_parent = {b["name"]: b["parent"] for b in bodies}
+    with_spheres = [b["name"] for b in bodies if any(int(l) == last_link[b["name"]] for l in sph_link)]
+    pairs = []
+    for ia, a in enumerate(with_spheres):
+        for b in with_spheres[ia + 1:]:
+            if body_parent[a] == b or body_parent[b] == a:
+                continue
+            pairs.append((last_link[a], last_link[b]))
+    model.collision_pairs = np.array(pairs, np.int32).reshape(-1, 2)
+    model.enable_self_collisions = bool(table.get("self_collision", False))
     drive = table.get("drive")
     if drive:  # PD position drive on every joint (tasks/anymal.py:128)
         model.drive_stiffness[1:] = drive["stiffness"]
@@ -292,3 +313,13 @@ def fill_desc(model: ArticulationModel, desc) -> None:
     desc.limit_damping = model.limit_damping
     desc.max_joint_velocity = model.max_joint_velocity
     desc.angular_damping = model.angular_damping
+    desc.max_angular_velocity = model.max_angular_velocity
+    desc.max_depenetration_velocity = model.max_depenetration_velocity
+    desc.self_contact_stiffness = model.self_contact_stiffness
+    desc.self_contact_damping = model.self_contact_damping
+    pairs = model.collision_pairs if model.enable_self_collisions else model.collision_pairs[:0]
+    if len(pairs) > len(desc.pair_link_a):
+        raise ValueError(f"{len(pairs)} self-collision link pairs exceed OIGE_MAX_PAIRS")
+    desc.num_collision_pairs = len(pairs)
+    for k, (a, b) in enumerate(pairs):
+        desc.pair_link_a[k], desc.pair_link_b[k] = int(a), int(b)

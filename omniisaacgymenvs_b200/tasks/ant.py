@@ -31,7 +31,7 @@ class AntLocomotionTask(LocomotionTask):
 
     def get_ant(self):
         self._model = build_model("Ant", spawn_height=float(self._ant_positions[2]),
-                                  **_solver_overrides(self._sim_config))
+                                  **_solver_overrides(self._sim_config, "Ant"))
 
     def get_robot(self):
         return self._ants

@@ -98,7 +98,7 @@ class AnymalTask(RLTask):
         """anymal.py:116-135: the model table carries the drive set by ``set_drive`` (400 / 40 per degree, max force
         1000); the default joint angles come from the YAML in DoF order."""
         self._model = build_model("Anymal", spawn_height=float(self._anymal_translation[2]),
-                                  **_solver_overrides(self._sim_config))
+                                  **_solver_overrides(self._sim_config, "Anymal"))
         self.default_dof_pos = torch.zeros((self.num_envs, 12), dtype=torch.float, device=self.device)
         for i, name in enumerate(self._model.dof_names):
             self.default_dof_pos[:, i] = self.named_default_joint_angles[name]

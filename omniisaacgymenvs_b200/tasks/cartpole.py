@@ -54,7 +54,7 @@ class CartpoleTask(RLTask):
 
     def get_cartpole(self):
         self._model = build_model("Cartpole", spawn_height=float(self._cartpole_positions[2]),
-                                  **_solver_overrides(self._sim_config))
+                                  **_solver_overrides(self._sim_config, "Cartpole"))
 
     def get_robot(self):
         return self._cartpoles

@@ -10,14 +10,26 @@ from omniisaacgymenvs_b200.tasks.base.rl_task import RLTask
 from omniisaacgymenvs_b200.tasks.shared.locomotion import LocomotionTask
 
 
-def _solver_overrides(sim_config) -> dict:
+def _solver_overrides(sim_config, actor: str = None) -> dict:
+    """Model overrides from the task YAML: the reference's own keys (gravity, friction, the `physx` block's
+    max_depenetration_velocity, the per-actor block `sim.<actor>` with enable_self_collisions /
+    max_depenetration_velocity, cfg/task/Humanoid.yaml:34-90) and `sim.b200`, the constants of the stand-in solver."""
     sim = sim_config.task_config.get("sim", {})
-    out = {k: float(v) for k, v in sim.get("b200", {}).items()}
+    out = {}
     if "gravity" in sim:
         out["gravity"] = tuple(float(g) for g in sim["gravity"])
     mat = sim.get("default_physics_material", {})
     if "dynamic_friction" in mat:
         out["friction_mu"] = float(mat["dynamic_friction"])
+    physx = sim.get("physx", {}) or {}
+    if "max_depenetration_velocity" in physx:
+        out["max_depenetration_velocity"] = float(physx["max_depenetration_velocity"])
+    block = (sim.get(actor, {}) or {}) if actor else {}
+    if "max_depenetration_velocity" in block and float(block["max_depenetration_velocity"]) > 0:
+        out["max_depenetration_velocity"] = float(block["max_depenetration_velocity"])  # per-body value wins
+    if "enable_self_collisions" in block:
+        out["enable_self_collisions"] = bool(block["enable_self_collisions"])
+    out.update({k: float(v) for k, v in sim.get("b200", {}).items()})
     return out
 
 
@@ -42,7 +54,7 @@ class HumanoidLocomotionTask(LocomotionTask):
 
     def get_humanoid(self):
         self._model = build_model("Humanoid", spawn_height=float(self._humanoid_positions[2]),
-                                  **_solver_overrides(self._sim_config))
+                                  **_solver_overrides(self._sim_config, "Humanoid"))
 
     def get_robot(self):
         return self._humanoids

@@ -125,6 +125,7 @@ static contact contact_eval(const OigeModelDesc* M, int s, m3 R, v3 p, v3 vlin, 
     double rad = M->sphere_radius[s];
     double pen = rad - x.z;
     if (!(pen > 0)) return c;
+    if (M->max_depenetration_velocity > 0) pen = fmin(pen, (double)M->max_depenetration_velocity * dt);
     c.r = V(x.x, x.y, x.z - rad);
     v3 vp = add(vlin, crs(w, sub(c.r, p)));
     double vn = vp.z;
@@ -199,6 +200,7 @@ static int step_one(const OigeModelDesc* M, double* pos, double* quat, double* v
         v3 a0c = add(ac0[i], add(crs(al0[i], rc), crs(w[i], crs(w[i], rc))));
         v3 fb = scl(m, sub(a0c, g));                         /* linear bias incl. gravity */
         v3 tb = add(mv(Iw, al0[i]), crs(w[i], mv(Iw, w[i]))); /* angular bias */
+        if (i > 0) tb = add(tb, scl((double)M->angular_damping, mv(Iw, w[i]))); /* damping torque -c I w (root: step 7) */
         point_jacobian(M, i, cw, p, axw, &J, nv);
         for (int a = 0; a < nv; ++a) {
             v3 Iwa = mv(Iw, J.jw[a]);
@@ -239,6 +241,37 @@ static int step_one(const OigeModelDesc* M, double* pos, double* quat, double* v
                                      cons[s].C.z * J.jv[a].z * J.jv[b].z;
         }
     }
+    /* 4b. self-collision: explicit sphere-sphere penalty between the links of each collision pair (equal and
+     * opposite forces at the midpoint of the overlap; damping only while approaching; no friction) */
+    for (int k = 0; k < M->num_collision_pairs; ++k) {
+        int la = M->pair_link_a[k], lb = M->pair_link_b[k];
+        for (int sa = 0; sa < M->num_spheres; ++sa) {
+            if (M->sphere_link[sa] != la) continue;
+            v3 ca = add(p[la], mv(R[la], V(M->sphere_pos[sa][0], M->sphere_pos[sa][1], M->sphere_pos[sa][2])));
+            for (int sb = 0; sb < M->num_spheres; ++sb) {
+                if (M->sphere_link[sb] != lb) continue;
+                v3 cb = add(p[lb], mv(R[lb], V(M->sphere_pos[sb][0], M->sphere_pos[sb][1], M->sphere_pos[sb][2])));
+                v3 d = sub(ca, cb);
+                double ra = M->sphere_radius[sa], rb = M->sphere_radius[sb];
+                double dist = sqrt(dt3(d, d)), pen = ra + rb - dist;
+                if (!(pen > 0) || !(dist > 1e-9)) continue;
+                v3 n = scl(1.0 / dist, d); /* from b to a */
+                v3 pc = add(cb, scl(rb - 0.5 * pen, n));
+                v3 va = add(vo[la], crs(w[la], sub(pc, p[la])));
+                v3 vb = add(vo[lb], crs(w[lb], sub(pc, p[lb])));
+                double vn = dt3(sub(va, vb), n);
+                double penc = pen;
+                if (M->max_depenetration_velocity > 0) penc = fmin(penc, (double)M->max_depenetration_velocity * dt);
+                double f = (double)M->self_contact_stiffness * penc - (vn < 0 ? (double)M->self_contact_damping * vn : 0.0);
+                if (!(f > 0)) continue;
+                v3 F = scl(f, n);
+                point_jacobian(M, la, pc, p, axw, &J, nv);
+                for (int a = 0; a < nv; ++a) rhs[a] += dt3(J.jv[a], F);
+                point_jacobian(M, lb, pc, p, axw, &J, nv);
+                for (int a = 0; a < nv; ++a) rhs[a] -= dt3(J.jv[a], F);
+            }
+        }
+    }
     /* 5. solve (a welded base: its six rows/columns become the identity with zero right-hand side) */
     if (M->fixed_base) {
         for (int a = 0; a < 6; ++a) {
@@ -272,7 +305,8 @@ static int step_one(const OigeModelDesc* M, double* pos, double* quat, double* v
     for (int i = 1; i < L; ++i) {
         int d = M->dof_index[i];
         double v = qd[d] + dt * x[6 + i - 1];
-        double mq = M->max_joint_velocity;
+        double mq = M->max_joint_velocity; /* JointAPI limit; a hinge's relative angular velocity also obeys the body limit */
+        if (M->joint_type[i] != OIGE_JOINT_PRISMATIC && M->max_angular_velocity > 0) mq = fmin(mq, (double)M->max_angular_velocity);
         v = fmin(fmax(v, -mq), mq);
         qd[d] = v;
         q[d] += dt * v;
@@ -281,6 +315,10 @@ static int step_one(const OigeModelDesc* M, double* pos, double* quat, double* v
     double damp = 1.0 - dt * (double)M->angular_damping;
     if (damp < 0) damp = 0;
     v3 w1 = scl(damp, add(w[0], scl(dt, V(x[3], x[4], x[5]))));
+    if (M->max_angular_velocity > 0) { /* RigidBodyAPI max angular velocity of the root body */
+        double wn2 = dt3(w1, w1), wm = M->max_angular_velocity;
+        if (wn2 > wm * wm) w1 = scl(wm / sqrt(wn2), w1);
+    }
     v3 v1 = add(vo[0], scl(dt, V(x[0], x[1], x[2])));
     vel[0] = v1.x; vel[1] = v1.y; vel[2] = v1.z; vel[3] = w1.x; vel[4] = w1.y; vel[5] = w1.z;
     pos[0] += dt * v1.x; pos[1] += dt * v1.y; pos[2] += dt * v1.z;

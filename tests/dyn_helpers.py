@@ -83,8 +83,67 @@ def run_oracle(model, spec, st, substeps, dt, calls=1, threads=8):
     return out
 
 
-def specs(robot):
-    return build_model(robot), lo.SPECS[robot]
+def specs(robot, **overrides):
+    """Model + task constants.  Self-collision (Humanoid) is integrated by the role-split kernel only, so the
+    warp-per-env / thread-per-env kernels (OIGE_K2_MODE=warp|thread) are tested on the model without it."""
+    import os
+
+    if os.environ.get("OIGE_K2_MODE", "") in ("warp", "thread"):
+        overrides.setdefault("enable_self_collisions", False)
+    return build_model(robot, **overrides), lo.SPECS[robot]
+
+
+def self_contact_states(m, n, seed, min_depth=0.01, height=50.0, qd_scale=0.3):
+    """Random joint configurations (fp32-exact) in which at least one self-collision sphere pair is in contact."""
+    rng = np.random.default_rng(seed)
+    lim = m.dof_limits().astype(np.float64)
+    out = []
+    while len(out) < n:
+        q = (lim[:, 0] + rng.random(m.num_dof) * (lim[:, 1] - lim[:, 0])).astype(np.float32).astype(np.float64)
+        s = dict(pos=np.array([[0.0, 0.0, height]]), quat=np.array([[1.0, 0, 0, 0]]), q=q[None])
+        if self_contact_depths(m, s).max() > min_depth:
+            out.append(q)
+    q = np.array(out)
+    qd = (qd_scale * rng.normal(size=q.shape)).astype(np.float32).astype(np.float64)
+    return dict(pos=np.tile([[0.0, 0.0, height]], (n, 1)), quat=np.tile([[1.0, 0, 0, 0]], (n, 1)), vel=np.zeros((n, 6)),
+                q=q, qd=qd)
+
+
+def link_frames(model, s, e=0):
+    """(R[L], p[L]) of env e: float64 numpy forward kinematics, hinge + prismatic."""
+    def qmat(q):
+        w, x, y, z = q
+        return np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y)],
+                         [2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x)],
+                         [2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)]])
+
+    L = model.num_links
+    R, p = [None] * L, [None] * L
+    R[0], p[0] = qmat(np.asarray(s["quat"][e], float)), np.array(s["pos"][e], float)
+    for i in range(1, L):
+        pa, d = int(model.parent[i]), int(model.dof_index[i])
+        ax = model.joint_axis[i]
+        Rj = R[pa] @ qmat(model.joint_quat[i])
+        if model.joint_type[i] == 1:
+            R[i] = Rj
+            p[i] = p[pa] + R[pa] @ model.joint_pos[i] + (Rj @ ax) * float(s["q"][e, d])
+        else:
+            th = float(s["q"][e, d])
+            R[i] = Rj @ qmat(np.concatenate([[np.cos(th / 2)], np.sin(th / 2) * ax]))
+            p[i] = p[pa] + R[pa] @ model.joint_pos[i]
+    return R, p
+
+
+def self_contact_depths(model, s, e=0):
+    """Penetration depth (> 0: in contact) of every sphere pair of the model's self-collision link pairs, env e."""
+    R, p = link_frames(model, s, e)
+    c = [p[int(l)] + R[int(l)] @ model.sphere_pos[k] for k, l in enumerate(model.sphere_link)]
+    out = []
+    for la, lb in model.collision_pairs:
+        for a in np.nonzero(model.sphere_link == la)[0]:
+            for b in np.nonzero(model.sphere_link == lb)[0]:
+                out.append(model.sphere_radius[a] + model.sphere_radius[b] - np.linalg.norm(c[a] - c[b]))
+    return np.array(out)
 
 
 def link_coms(model, s):

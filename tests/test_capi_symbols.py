@@ -21,7 +21,7 @@ def test_library_builds_and_loads():
     assert os.path.exists(path)
     lib = ctypes.CDLL(path)
     lib.oige_abi_version.restype = ctypes.c_int
-    assert lib.oige_abi_version() == _lib.ABI_VERSION == 2
+    assert lib.oige_abi_version() == _lib.ABI_VERSION == 3
 
 
 def test_every_declared_symbol_is_exported():
@@ -45,7 +45,8 @@ def test_struct_layouts_match_header_sizes():
     assert ctypes.sizeof(_lib.OigeAnymalParams) == 4 * 4 + 22 * 4 + 3 * 12 * 4
     assert ctypes.sizeof(_lib.OigeAnymalBuffers) == 11 * 8
     L, K, S = _lib.MAX_LINKS, _lib.MAX_SPHERES, _lib.MAX_SENSORS
-    expect = 16 + 3 * L * 4 + L * 4 * (3 + 4 + 3 + 1 + 3 + 6 + 6 + 3) + K * 4 * (1 + 3 + 1) + S * 4 + (3 + 8) * 4
+    expect = (16 + 3 * L * 4 + L * 4 * (3 + 4 + 3 + 1 + 3 + 6 + 6 + 3) + K * 4 * (1 + 3 + 1) + S * 4 + (3 + 8) * 4
+              + (4 + 1) * 4 + 2 * _lib.MAX_PAIRS * 4)  # ABI 3: velocity limits, self-collision pairs
     assert ctypes.sizeof(_lib.OigeModelDesc) == expect
 
 

@@ -12,6 +12,9 @@ def _free(model):
     model.stiffness[:] = 0
     model.limit_lower[:] = -1e9
     model.limit_upper[:] = 1e9
+    model.angular_damping = 0.0          # conservative system: no body damping, no velocity clamps, no limb contacts
+    model.max_angular_velocity = 0.0
+    model.enable_self_collisions = False
     return model
 
 
@@ -91,7 +94,7 @@ def _cartpole_accel(m, x, th, xd, thd, force):
 
 
 def test_cartpole_accelerations_match_the_textbook_equations():
-    m = build_model("Cartpole")
+    m = build_model("Cartpole", angular_damping=0.0)
     assert m.fixed_base and list(m.joint_type) == [0, 1, 0] and m.dof_names == ["cartJoint", "poleJoint"]
     desc = dyn.make_desc(m)
     rng = np.random.default_rng(3)
@@ -110,7 +113,7 @@ def test_cartpole_accelerations_match_the_textbook_equations():
 
 
 def test_cartpole_energy_is_conserved_without_actuation():
-    m = build_model("Cartpole")
+    m = build_model("Cartpole", angular_damping=0.0)
     desc = dyn.make_desc(m)
     base = dict(pos=np.array([[0, 0, 2.0]]), quat=np.array([[1.0, 0, 0, 0]]), vel=np.zeros((1, 6)),
                 q=np.array([[0.3, 0.4]]), qd=np.array([[-0.5, 1.0]]))
@@ -127,7 +130,7 @@ def test_cartpole_energy_is_conserved_without_actuation():
 def test_prismatic_joint_on_a_floating_base_conserves_momentum():
     """A tumbling, free-floating cart-pole (no gravity): linear momentum is exactly conserved by the
     integrator, and the energy drift shrinks with dt -- exercises the Coriolis terms of the slider."""
-    m = build_model("Cartpole", fixed_base=False, gravity=(0.0, 0.0, 0.0))
+    m = build_model("Cartpole", fixed_base=False, gravity=(0.0, 0.0, 0.0), angular_damping=0.0)
     desc = dyn.make_desc(m)
     rng = np.random.default_rng(5)
     base = dict(pos=np.array([[0, 0, 50.0]]), quat=np.array([[1.0, 0, 0, 0]]), vel=rng.normal(size=(1, 6)),
@@ -154,3 +157,55 @@ def test_prismatic_joint_on_a_floating_base_conserves_momentum():
         np.testing.assert_allclose(v_end, v_start, atol=5e-3 * max(1.0, np.abs(v_start).max()) * (dt / 1e-3))
         drift.append(abs(dyn.energy(desc, *[s[k] for k in ("pos", "quat", "vel", "q", "qd")]) - e0) / abs(e0))
     assert drift[1] < drift[0] / 5
+
+
+def _self_contact_states(m, n, seed, min_depth=0.01):
+    import dyn_helpers as dh
+
+    return dh.self_contact_states(m, n, seed, min_depth)
+
+
+def test_self_collision_pairs_follow_the_body_tree():
+    """PhysX semantics: every pair of bodies with shapes except parent / child (cfg/task/Humanoid.yaml:80)."""
+    m = build_model("Humanoid")
+    assert m.enable_self_collisions and len(m.collision_pairs) == 13 * 12 // 2 - 12
+    names = {(m.link_names[a], m.link_names[b]) for a, b in m.collision_pairs}
+    assert ("right_elbow", "left_elbow") in names and ("torso", "right_knee") in names
+    assert ("torso", "abdomen_y") not in names and ("right_hip_y", "right_knee") not in names  # jointed bodies
+    ant = build_model("Ant")
+    assert not ant.enable_self_collisions and dyn.make_desc(ant).num_collision_pairs == 0  # Ant.yaml:82
+    assert dyn.make_desc(m).num_collision_pairs == 66
+    assert dyn.make_desc(build_model("Humanoid", enable_self_collisions=False)).num_collision_pairs == 0
+
+
+def test_self_collision_is_an_internal_force():
+    """Limbs in contact are pushed apart (the joint velocities change at O(dt)) while the centre of mass moves as it
+    does without self-collision (difference O(dt^3)): the pair forces are equal and opposite (no gravity, free flight)."""
+    import dyn_helpers as dh
+
+    kw = dict(gravity=(0.0, 0.0, 0.0), angular_damping=0.0)
+    on, off = build_model("Humanoid", **kw), build_model("Humanoid", enable_self_collisions=False, **kw)
+    base = _self_contact_states(on, 8, 1)
+    D = on.num_dof
+    res = {}
+    for name, m in (("on", on), ("off", off)):
+        s = {k: v.copy() for k, v in base.items()}
+        assert dyn.step(dyn.make_desc(m), s["pos"], s["quat"], s["vel"], s["q"], s["qd"], np.zeros((8, D)), None, 1, 1e-3) == 0
+        res[name] = s
+    assert np.abs(res["on"]["qd"] - res["off"]["qd"]).max(axis=1).min() > 1e-2, "every env had a pair in contact"
+    for e in range(8):
+        com = [dh.link_coms(on, {k: v[e:e + 1] for k, v in res[n_].items()}) for n_ in ("on", "off")]
+        np.testing.assert_allclose(com[0], com[1], atol=1e-7)
+
+
+def test_self_collision_separates_interpenetrating_limbs():
+    """Held only by the joint springs, limbs that start in contact end up (nearly) out of contact."""
+    import dyn_helpers as dh
+
+    m = build_model("Humanoid", gravity=(0.0, 0.0, 0.0))
+    s = _self_contact_states(m, 6, 2, min_depth=0.02)
+    s["qd"][:] = 0.0
+    d0 = np.array([dh.self_contact_depths(m, s, e).max() for e in range(6)])
+    assert dyn.step(dyn.make_desc(m), s["pos"], s["quat"], s["vel"], s["q"], s["qd"], np.zeros((6, m.num_dof)), None, 240, 0.0083) == 0
+    d1 = np.array([dh.self_contact_depths(m, s, e).max() for e in range(6)])
+    assert np.isfinite(s["q"]).all() and (d1 < 0.5 * d0).all(), (d0, d1)

@@ -109,8 +109,9 @@ def test_rollout_64_with_contacts_statistical(cuda_lib, robot):
 
 @pytest.mark.parametrize("robot", ["Humanoid", "Ant"])
 def test_pd_position_drive_matches_oracle(cuda_lib, robot):
-    """PD position-target actuation (set_joint_position_targets): implicit drive, saturating at max force."""
-    model, spec = dh.specs(robot)
+    """PD position-target actuation (set_joint_position_targets): implicit drive, saturating at max force.
+    (A synthetic drive on the Humanoid tree: no self-collision -- K2-F has no position-target variant for 3 roles.)"""
+    model, spec = dh.specs(robot, enable_self_collisions=False)
     model.drive_stiffness[1:] = 60.0
     model.drive_damping[1:] = 3.0
     model.drive_max_force[1:] = 40.0  # some joints saturate with the random targets below
@@ -131,7 +132,7 @@ def test_pd_position_drive_matches_oracle(cuda_lib, robot):
 
 def test_both_kernels_agree_with_each_other(cuda_lib, monkeypatch):
     """warp-per-env vs thread-per-env on the same state: same model, different summation orders."""
-    model, spec = dh.specs("Humanoid")
+    model, spec = dh.specs("Humanoid", enable_self_collisions=False)  # (only K2-F integrates self-collision)
     st = dh.random_state(model, 256, 11, height=1.3, tilt=0.1)
     _set_mode(monkeypatch, "warp")
     a = dh.run_gpu(cuda_lib, model, spec, st, 2, DT)
@@ -402,3 +403,83 @@ def test_model_create_rejects_unknown_joint_type(cuda_lib):
     desc.joint_type[1] = 7
     assert not cuda_lib.oige_model_create(C.byref(desc))
     assert b"malformed" in cuda_lib.oige_last_error()
+
+
+# ---- self-collision (cfg/task/Humanoid.yaml:80 enable_self_collisions: True) ----------------------------------------
+
+def _sc_state(model, n, seed, height=50.0, min_depth=0.01):
+    f32 = lambda a: np.ascontiguousarray(a.astype(np.float32))
+    s = dh.self_contact_states(model, n, seed, min_depth=min_depth, height=height)
+    rng = np.random.default_rng(seed + 1000)
+    return {k: f32(v) for k, v in s.items()} | {"actions": f32(rng.uniform(-1, 1, size=s["q"].shape))}
+
+
+def test_self_collision_single_substep_matches_oracle(cuda_lib, k2_kernel):
+    """Every env starts with at least one sphere pair of non-adjacent bodies in contact; the kernel that integrates
+    self-collision (K2-F) must agree with the float64 oracle, and differ from the run without it."""
+    from omniisaacgymenvs_b200.robots.model import build_model
+
+    model = build_model("Humanoid")
+    spec = dh.lo.SPECS["Humanoid"]
+    st = _sc_state(model, 256, 3)
+    if k2_kernel in ("warp", "thread"):
+        with pytest.raises(RuntimeError, match="self-collision"):
+            dh.run_gpu(cuda_lib, model, spec, st, 1, DT)
+        return
+    g = dh.run_gpu(cuda_lib, model, spec, st, 1, DT)
+    o = dh.run_oracle(model, spec, st, 1, DT)
+    off = dh.run_gpu(cuda_lib, build_model("Humanoid", enable_self_collisions=False), spec, st, 1, DT)
+    assert np.abs(g["qd"] - off["qd"]).max(axis=1).min() > 1e-2, "the pairs must actually push in every env"
+    assert _err(g["q"], o["q"]) < 2e-5 and _err(g["pos"], o["pos"]) < 2e-5 and _quat_err(g["quat"], o["quat"]) < 2e-5
+    assert (np.abs(g["qd"] - o["qd"]) / np.maximum(1.0, np.abs(o["qd"]))).max() < 2e-3
+    assert (np.abs(g["vel"] - o["vel"]) / np.maximum(1.0, np.abs(o["vel"]))).max() < 2e-3
+
+
+def test_self_collision_rollout_separates_limbs_like_the_oracle(cuda_lib, k2_kernel):
+    """32 substeps from interpenetrating limbs (free flight, no actuation): the limbs are pushed apart, the joint
+    trajectories follow the oracle, and the root's momentum change stays at rounding level (internal forces)."""
+    if k2_kernel in ("warp", "thread"):
+        pytest.skip("only K2-F integrates self-collision")
+    from omniisaacgymenvs_b200.robots.model import build_model
+
+    model = build_model("Humanoid", gravity=(0.0, 0.0, 0.0))
+    spec = dh.lo.SPECS["Humanoid"]
+    st = _sc_state(model, 128, 5, min_depth=0.02)
+    st["actions"][:] = 0.0
+    st["qd"][:] = 0.0
+    d0 = np.array([dh.self_contact_depths(model, st, e).max() for e in range(128)])
+    g = dh.run_gpu(cuda_lib, model, spec, st, 32, DT)
+    o = dh.run_oracle(model, spec, st, 32, DT)
+    d1 = np.array([dh.self_contact_depths(model, g, e).max() for e in range(128)])
+    assert np.isfinite(g["q"]).all() and np.median(d1) < 0.5 * np.median(d0), (np.median(d0), np.median(d1))
+    per_env = np.abs(g["q"] - o["q"]).max(axis=1)
+    assert np.median(per_env) < 2e-4 and (per_env < 2e-2).mean() >= 0.97, (np.median(per_env), per_env.max())
+
+
+def test_self_collision_in_the_full_step_keeps_limbs_apart(cuda_lib, k2_kernel):
+    """Random-policy episodes through the public step: with self-collision the deepest limb-limb penetration stays a
+    few centimetres (penalty spring), without it arms and legs pass through the body."""
+    if k2_kernel != "role":
+        pytest.skip("whole-step check, once")
+    import torch
+
+    from omniisaacgymenvs_b200.utils.task_util import make_env
+    from omniisaacgymenvs_b200.robots.model import build_model
+
+    model = build_model("Humanoid")
+    deepest = {}
+    for on in (True, False):
+        env, task = make_env("Humanoid", num_envs=256, overrides={} if on else {"task.sim.Humanoid.enable_self_collisions": False})
+        env.reset()
+        g = torch.Generator(device="cuda").manual_seed(0)
+        worst = 0.0
+        for t in range(60):
+            env.step(torch.rand(256, 21, device="cuda", generator=g) * 2 - 1)
+            if t % 6 == 5:
+                v = task.get_robot()
+                pos, quat = v.get_world_poses(clone=True)
+                s = {"pos": pos.cpu().numpy().astype(np.float64), "quat": quat.cpu().numpy().astype(np.float64),
+                     "q": v.get_joint_positions(clone=True).cpu().numpy().astype(np.float64)}
+                worst = max(worst, max(dh.self_contact_depths(model, s, e).max() for e in range(0, 256, 4)))
+        deepest[on] = worst
+    assert deepest[True] < 0.08 < deepest[False], deepest
