@@ -177,12 +177,17 @@ typedef struct OigeModelDesc {
                                                 hinge's relative angular velocity |qd|; <= 0: unlimited */
     float max_depenetration_velocity;        /* m/s (cfg/task/Humanoid.yaml:62,90): the penalty springs see at most
                                                 max_depenetration_velocity * dt of penetration per substep; <= 0: unlimited */
-    float self_contact_stiffness;            /* N/m, sphere-sphere penalty between the links of a collision pair */
+    float self_contact_stiffness;            /* N/m, capsule-capsule penalty between the links of a collision pair */
     float self_contact_damping;              /* N s/m, only while approaching */
     int32_t num_collision_pairs;             /* enable_self_collisions (cfg/task/Humanoid.yaml:80): unordered LINK pairs whose
                                                 collision spheres repel each other; 0 = no self-collision (Ant.yaml:82) */
     int32_t pair_link_a[OIGE_MAX_PAIRS];
     int32_t pair_link_b[OIGE_MAX_PAIRS];
+    /* self-collision shape of a link: ONE capsule (segment a-b in the link frame, radius); radius <= 0 = none.  Every
+     * link named by a collision pair must have one. */
+    float capsule_a[OIGE_MAX_LINKS][3];
+    float capsule_b[OIGE_MAX_LINKS][3];
+    float capsule_radius[OIGE_MAX_LINKS];
 } OigeModelDesc;
 
 typedef struct OigeModel OigeModel; /* opaque; holds the immutable device-side model table */

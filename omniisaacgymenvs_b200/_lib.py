@@ -76,6 +76,7 @@ class OigeModelDesc(C.Structure):
         ("max_angular_velocity", f32), ("max_depenetration_velocity", f32), ("self_contact_stiffness", f32),
         ("self_contact_damping", f32), ("num_collision_pairs", i32), ("pair_link_a", i32 * MAX_PAIRS),
         ("pair_link_b", i32 * MAX_PAIRS),
+        ("capsule_a", (f32 * 3) * MAX_LINKS), ("capsule_b", (f32 * 3) * MAX_LINKS), ("capsule_radius", f32 * MAX_LINKS),
     ]
 
 

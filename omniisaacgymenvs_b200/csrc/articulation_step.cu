@@ -1486,9 +1486,11 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
             for (int s2 = 0; s2 < d->num_sensors; ++s2) fits = fits && sensor_seen[s2];  // sensors sit on chain tips
             // scratch layout of a 32-env group (float offsets, x32 lanes)
             rm->oI = 0;
-            // (with self-collision the hand-over region also holds the sphere centres between the kinematics and the
-            // inertia sweeps: 3 floats per collision sphere)
-            const int handover_floats = has_sc && 3 * d->num_spheres > nslots * kHand ? 3 * d->num_spheres : nslots * kHand;
+            // (with self-collision the hand-over region also holds the capsule end points between the kinematics and the
+            // inertia sweeps: 6 floats per capsule)
+            int ncaps = 0;
+            for (int i = 0; i < L; ++i) if (d->capsule_radius[i] > 0.f) ++ncaps;
+            const int handover_floats = has_sc && 6 * ncaps > nslots * kHand ? 6 * ncaps : nslots * kHand;
             rm->oA = rm->oI + handover_floats;
             rm->oK = rm->oA + npub * 6;
             rm->oT = rm->oK + nt * kKin;
@@ -1514,35 +1516,21 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
                         rm->w_idx[li] = (unsigned char)(kRT + k2);
                         rm->rec_off[li] = (unsigned short)(rm->oL + (r * maxc + k2) * kPu);
                     }
-                // spheres in the device order (sorted by link, stable): first sphere / count per link, bounding radius
-                int pos2 = 0;
+                // one capsule per link that takes part: slot in the published end points, bounding radius about its midpoint
+                int nc2 = 0;
                 for (int i = 0; i < L; ++i) {
-                    sph0[i] = pos2;
-                    for (int s2 = 0; s2 < d->num_spheres; ++s2) if (d->sphere_link[s2] == i) ++pos2;
-                    sphn[i] = pos2 - sph0[i];
-                }
-                auto sphere_at = [&](int i, int k2, float* c) {  // k2-th sphere of link i in device order
-                    int seen = 0;
-                    for (int s2 = 0; s2 < d->num_spheres; ++s2) {
-                        if (d->sphere_link[s2] != i) continue;
-                        if (seen++ == k2) { for (int q = 0; q < 3; ++q) c[q] = d->sphere_pos[s2][q]; return d->sphere_radius[s2]; }
+                    sphn[i] = d->capsule_radius[i] > 0.f ? 1 : 0;  // "has a self-collision shape"
+                    (void)sph0;
+                    if (!sphn[i]) continue;
+                    rm->cap_idx[i] = (unsigned char)nc2++;
+                    float hl = 0.f;
+                    for (int q = 0; q < 3; ++q) {
+                        rm->cap_a[q][i] = d->capsule_a[i][q]; rm->cap_b[q][i] = d->capsule_b[i][q];
+                        hl += (d->capsule_b[i][q] - d->capsule_a[i][q]) * (d->capsule_b[i][q] - d->capsule_a[i][q]);
                     }
-                    return 0.f;
-                };
-                for (int i = 0; i < L; ++i) {
-                    if (sphn[i] == 0) continue;
-                    float c0[3], c1[3], mid[3];
-                    sphere_at(i, 0, c0); sphere_at(i, sphn[i] - 1, c1);
-                    for (int q = 0; q < 3; ++q) mid[q] = 0.5f * (c0[q] + c1[q]);
-                    float br = 0.f;
-                    for (int k2 = 0; k2 < sphn[i]; ++k2) {
-                        float c[3];
-                        const float rad = sphere_at(i, k2, c);
-                        const float dd = sqrtf((c[0] - mid[0]) * (c[0] - mid[0]) + (c[1] - mid[1]) * (c[1] - mid[1]) +
-                                               (c[2] - mid[2]) * (c[2] - mid[2])) + rad;
-                        if (dd > br) br = dd;
-                    }
-                    rm->brad[i] = br * 1.0001f + 1e-6f;  // (the broad phase must never cut a touching pair)
+                    rm->cap_r[i] = d->capsule_radius[i];
+                    rm->cap_il2[i] = hl > 1e-12f ? 1.f / hl : 0.f;
+                    rm->brad[i] = (0.5f * sqrtf(hl) + d->capsule_radius[i]) * 1.0001f + 1e-6f;  // (never cuts a touching pair)
                 }
                 // directed pairs, grouped by role and sorted by the own link
                 int npairs = 0;
@@ -1573,6 +1561,7 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
                     int pool[64], npool = 0, used = 0;
                     auto is_massless2 = [&](int i) {
                         bool zero = i > 0 && d->mass[i] == 0.f && sphn[i] == 0;
+                        for (int s2 = 0; s2 < d->num_spheres; ++s2) zero = zero && d->sphere_link[s2] != i;
                         for (int k2 = 0; k2 < 6; ++k2) zero = zero && d->inertia[i][k2] == 0.f;
                         for (int s2 = 0; s2 < d->num_sensors; ++s2) zero = zero && d->sensor_link[s2] != i;
                         return zero;
@@ -1584,12 +1573,20 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
                                 pool[npool++] = base + 7; pool[npool++] = base + 10;
                             }
                     for (int q = 0; q + 3 <= npub * 6 && npool < 64; q += 3) pool[npool++] = rm->oA + q;
-                    for (int q = 3 * d->num_spheres; q + 3 <= handover_floats && npool < 64; q += 3) pool[npool++] = rm->oI + q;
+                    for (int q = 6 * ncaps; q + 3 <= handover_floats && npool < 64; q += 3) pool[npool++] = rm->oI + q;
                     for (int i = 0; i < L; ++i) {
                         if (sphn[i] == 0) continue;
                         if (used >= npool) { fits = false; break; }
                         rm->ctr_off[i] = (unsigned short)pool[used++];
                     }
+                }
+                for (int k2 = 0; k2 < npairs; ++k2) {
+                    const int la = rm->sc_a[k2], lb = rm->sc_b[k2] & 127;
+                    const float rr = rm->brad[la] + rm->brad[lb], rr2 = rr * rr;
+                    unsigned bits;
+                    memcpy(&bits, &rr2, sizeof(bits));
+                    rm->sc_rec[k2].x = rm->ctr_off[lb]; rm->sc_rec[k2].y = bits;
+                    rm->sc_ctra[k2] = rm->ctr_off[la];
                 }
                 // the sphere centres live in the hand-over slots' memory during the kinematics / pair phases
                 if (kRT + maxc > 32 || rm->group_floats > max_group_floats) fits = false;

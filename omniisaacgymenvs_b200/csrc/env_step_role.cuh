@@ -73,7 +73,15 @@ struct alignas(16) RoleModel {
     unsigned short rec_off[kRL];                          // link -> float offset (x32 lanes) of its (quat, p, v) record
     float brad[kRL];                                      // bounding radius about the midpoint of its first / last sphere
     unsigned short ctr_off[kRL];                          // link -> float offset (x32 lanes) of its bounding centre (3 floats)
-    unsigned char pad[7];
+    unsigned char cap_idx[kRL];                           // link -> its capsule's slot in the published end points
+    unsigned char pad[15];
+    float cap_a[3][kRL], cap_b[3][kRL], cap_r[kRL];       // self-collision capsule of a link (link frame); r = 0: none
+    float cap_il2[kRL];                                   // 1 / |b - a|^2 (0 for a sphere)
+    // broad-phase record of list entry k: x = float offset of b's bounding centre, y = bits of (brad[a] + brad[b])^2,
+    // z = float offset of a's bounding centre (read when a changes)
+    uint2 sc_rec[kSCMax];
+    unsigned short sc_ctra[kSCMax];
+    unsigned char pad2[(16 - (kSCMax * 2) % 16) % 16];
 };
 static_assert(sizeof(RoleModel) % 16 == 0, "RoleModel must be int4-copyable");
 
@@ -205,48 +213,64 @@ __device__ __forceinline__ void joint_reduce(const MT& M, int i, const M3& R, V3
 }
 
 // ---- self-collision (enable_self_collisions, cfg/task/Humanoid.yaml:80) -------------------------------------------------
-// Explicit sphere-sphere penalty between the links of a collision pair, evaluated at the state the substep starts from
-// (an implicit pair force would couple two branches of the tree, i.e. close a kinematic loop, and break the O(n)
-// recursion).  Every role evaluates the DIRECTED pairs (a, b) whose link a it owns and keeps only the wrench on a;
-// both directions run the same arithmetic on the same operands (orientation fixed by the sphere numbers), so the two
-// forces are equal and opposite to the bit.  Force along the centre line at the midpoint of the overlap:
+// Explicit capsule-capsule penalty between the links of a collision pair (one capsule per body), evaluated at the state
+// the substep starts from (an implicit pair force would couple two branches of the tree, i.e. close a kinematic loop,
+// and break the O(n) recursion).  Every role evaluates the pairs (a, b) whose link a it owns and keeps only the wrench
+// on a (on both, if b is its own too); the two sides of a pair run the same arithmetic on the same operands (segment
+// order fixed by the link numbers), so the two forces are equal and opposite to the bit.  One contact per pair at the
+// closest points of the two segments, force along their connection at the midpoint of the overlap:
 // f = k pen - d vn (damping while approaching only), no friction.
 
-// world centres of link `link`'s collision spheres -> C[sphere][xyz] (stride 32), and the centre of the link's bounding
-// sphere (midpoint of its first and last sphere, radius M.brad) -> ctr[xyz]
+// world end points of link `link`'s capsule -> C[slot][P xyz, Q xyz] (stride 32), its midpoint (centre of the bounding
+// sphere of radius M.brad) -> ctr[xyz]
 template <class MT>
-__device__ __forceinline__ void publish_spheres(const MT& M, int link, const M3& R, V3 p, float* C, float* ctr) {
-    const int s0 = M.sph_start[link], s1 = s0 + M.sph_count[link];
-    if (s1 == s0) return;
-    V3 first = {0.f, 0.f, 0.f}, x = {0.f, 0.f, 0.f};
-    for (int k = s0; k < s1; ++k) {
-        x = p + mulv(R, V3{M.sph_pos[0][k], M.sph_pos[1][k], M.sph_pos[2][k]});
-        C[(3 * k) * 32] = x.x; C[(3 * k + 1) * 32] = x.y; C[(3 * k + 2) * 32] = x.z;
-        if (k == s0) first = x;
-    }
-    ctr[0] = 0.5f * (first.x + x.x); ctr[32] = 0.5f * (first.y + x.y); ctr[64] = 0.5f * (first.z + x.z);
+__device__ __forceinline__ void publish_capsule(const MT& M, int link, const M3& R, V3 p, float* C, float* ctr) {
+    if (!(M.cap_r[link] > 0.f)) return;
+    const V3 P = p + mulv(R, V3{M.cap_a[0][link], M.cap_a[1][link], M.cap_a[2][link]});
+    const V3 Q = p + mulv(R, V3{M.cap_b[0][link], M.cap_b[1][link], M.cap_b[2][link]});
+    float* c = C + (int)M.cap_idx[link] * 6 * 32;
+    c[0] = P.x; c[32] = P.y; c[64] = P.z; c[96] = Q.x; c[128] = Q.y; c[160] = Q.z;
+    ctr[0] = 0.5f * (P.x + Q.x); ctr[32] = 0.5f * (P.y + Q.y); ctr[64] = 0.5f * (P.z + Q.z);
 }
-__device__ __forceinline__ V3 sphere_centre(const float* C, int k) {
-    return {C[(3 * k) * 32], C[(3 * k + 1) * 32], C[(3 * k + 2) * 32]};
+// Closest points of the capsule axes of links lo < hi (Ericson, Real-Time Collision Detection 5.1.9), branch-free.
+// Returns the squared distance; c1 on lo's axis, c2 on hi's.
+template <class MT>
+__device__ __forceinline__ float capsule_closest(const MT& M, const float* C, int lo, int hi, V3& c1, V3& c2) {
+    const float* s1 = C + (int)M.cap_idx[lo] * 6 * 32;
+    const float* s2 = C + (int)M.cap_idx[hi] * 6 * 32;
+    const V3 P1 = {s1[0], s1[32], s1[64]}, Q1 = {s1[96], s1[128], s1[160]};
+    const V3 P2 = {s2[0], s2[32], s2[64]}, Q2 = {s2[96], s2[128], s2[160]};
+    const V3 d1 = Q1 - P1, d2 = Q2 - P2, r = P1 - P2;
+    const float a = dot(d1, d1), e = dot(d2, d2), f = dot(d2, r), c = dot(d1, r), b = dot(d1, d2);
+    const float ia = M.cap_il2[lo], ie = M.cap_il2[hi];  // 1 / length^2: model constants (0: a sphere, a zero-length capsule)
+    const float den = a * e - b * b;
+    float sp = den > 1e-9f * a * e ? __saturatef((b * f - c * e) / den) : 0.f;
+    float tp = (b * sp + f) * ie;
+    if (tp < 0.f || ie == 0.f) sp = __saturatef(-c * ia);
+    else if (tp > 1.f) sp = __saturatef((b - c) * ia);
+    tp = __saturatef(tp);
+    c1 = P1 + sp * d1;
+    c2 = P2 + tp * d2;
+    const V3 d = c1 - c2;
+    return dot(d, d);
 }
-// One sphere pair in contact: force on link a (and, BOTH: the opposite one on link b, which this role owns too) about O
-// -> W (first touch stores, later ones add).  The orientation is fixed by the sphere numbers, so the roles on either
-// side of a pair compute the same bits.
+// The contact of the pair (a, b): force on link a (and, BOTH: the opposite one on link b, which this role owns too)
+// about O -> W (first touch stores, later ones add).
 template <class MT, int NW>
-__device__ __forceinline__ void sphere_contact(const MT& M, const float* C, const float* G0, int a, int b, int i, int j,
-                                            float dt, bool both, float (&W)[NW][6], unsigned& wmask) {
-    const bool a_lo = i < j;
-    const int lo = a_lo ? i : j, hi = a_lo ? j : i;
-    const V3 clo = sphere_centre(C, lo), chi = sphere_centre(C, hi);
-    const float rlo_ = M.sph_r[lo], rhi_ = M.sph_r[hi];
-    const V3 d = clo - chi;
-    const float d2 = dot(d, d);
+__device__ __forceinline__ void capsule_contact(const MT& M, const float* C, const float* G0, int a, int b, float dt,
+                                                bool both, float (&W)[NW][6], unsigned& wmask) {
+    const bool a_lo = a < b;
+    const int lo = a_lo ? a : b, hi = a_lo ? b : a;
+    V3 clo, chi;
+    const float d2 = capsule_closest(M, C, lo, hi, clo, chi);
+    const float rlo_ = M.cap_r[lo], rhi_ = M.cap_r[hi];
     if (!(d2 > 1e-18f)) return;
     const float dist = sqrtf(d2), pen = (rlo_ + rhi_) - dist;
-    const V3 n = (1.f / dist) * d;  // from the higher-numbered sphere to the lower one
+    if (!(pen > 0.f)) return;
+    const V3 n = (1.f / dist) * (clo - chi);  // from the higher-numbered link's capsule to the lower one's
     const V3 pc = chi + (rhi_ - 0.5f * pen) * n;
-    const float* rlo = G0 + (int)M.rec_off[a_lo ? a : b] * 32;
-    const float* rhi = G0 + (int)M.rec_off[a_lo ? b : a] * 32;
+    const float* rlo = G0 + (int)M.rec_off[lo] * 32;
+    const float* rhi = G0 + (int)M.rec_off[hi] * 32;
     const V3 wlo = {rlo[7 * 32], rlo[8 * 32], rlo[9 * 32]}, ulo = {rlo[10 * 32], rlo[11 * 32], rlo[12 * 32]};
     const V3 whi = {rhi[7 * 32], rhi[8 * 32], rhi[9 * 32]}, uhi = {rhi[10 * 32], rhi[11 * 32], rhi[12 * 32]};
     const V3 vrel = (ulo + cross(wlo, pc)) - (uhi + cross(whi, pc));
@@ -269,28 +293,6 @@ __device__ __forceinline__ void sphere_contact(const MT& M, const float* C, cons
 #pragma unroll
         for (int k = 0; k < 6; ++k) W[w][k] = (seen ? W[w][k] : 0.f) - wr[k];
         wmask |= 1u << w;
-    }
-}
-// narrow phase of the link pair (a, b) = entry k of the role's list: every sphere of a against every sphere of b.  A hit
-// is only QUEUED here (per-thread list in local memory, touched on contact only): contacts are rare and lane-divergent,
-// so they are evaluated afterwards, all lanes popping their own queue together, instead of one lane at a time in the
-// middle of the test loops.
-constexpr int kSCQueue = 32;
-template <class MT>
-__device__ __forceinline__ void self_contact_tests(const MT& M, const float* C, int a, int b, int k, unsigned (&q)[kSCQueue],
-                                                   int& nq) {
-    const int a0 = M.sph_start[a], a1 = a0 + M.sph_count[a], b0 = M.sph_start[b], b1 = b0 + M.sph_count[b];
-    for (int i = a0; i < a1; ++i) {
-        const V3 ca = sphere_centre(C, i);
-        const float ra = M.sph_r[i];
-        for (int j = b0; j < b1; ++j) {
-            const V3 d = ca - sphere_centre(C, j);
-            const float rr = ra + M.sph_r[j];
-            if (dot(d, d) < rr * rr) {
-                q[nq & (kSCQueue - 1)] = (unsigned)k << 16 | (unsigned)i << 8 | (unsigned)j;
-                ++nq;  // (more than kSCQueue contacts of one role's links in one env: flagged by the caller)
-            }
-        }
     }
 }
 
@@ -496,7 +498,7 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
     Q4 sq = {1.f, 0.f, 0.f, 0.f};  // frame of the sensor link at the start of the last substep
     V3 sp = {0.f, 0.f, 0.f};
     const int nseg = M.nseg[role];
-    // self-collision: sphere centres live in the hand-over slots' memory (dead until the first chain hands over), the
+    // self-collision: capsule end points live in the hand-over slots' memory (dead until the first chain hands over), the
     // wrenches on this role's own links in a per-thread array that is only touched when a pair is in contact
     float* const xC = xI;
     float W[SC ? kRT + MAXC : 1][6];
@@ -532,36 +534,40 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
                     int prev_a = -1;
                     V3 ma = {0.f, 0.f, 0.f};
                     float ra = 0.f;
+                    (void)ra;
                     for (int k = k0; k < k1; ++k) {
-                        const int a = M.sc_a[k], b = M.sc_b[k] & 127;
-                        if (a != prev_a) {
-                            const float* c = G0 + (int)M.ctr_off[a] * 32;
+                        const uint2 rec = M.sc_rec[k];
+                        const int oa = M.sc_ctra[k];
+                        if (oa != prev_a) {
+                            const float* c = G0 + oa * 32;
                             ma = {c[0], c[32], c[64]};
-                            ra = M.brad[a];
-                            prev_a = a;
+                            prev_a = oa;
                         }
-                        const float* c = G0 + (int)M.ctr_off[b] * 32;
+                        const float* c = G0 + (int)rec.x * 32;
                         const V3 d = {ma.x - c[0], ma.y - c[32], ma.z - c[64]};
-                        const float rr = ra + M.brad[b];
-                        if (dot(d, d) < rr * rr) cand |= 1ull << (k - k0);
+                        if (dot(d, d) < __uint_as_float(rec.y)) cand |= 1ull << (k - k0);
                     }
                 }
-                unsigned cq[kSCQueue];
-                int nq = 0;
+                // Phase 2: every lane pops its own candidates: capsule-capsule distance against the sum of the radii
+                unsigned long long hits = 0ull;
                 while (__any_sync(0xffffffffu, cand != 0ull)) {
                     if (cand != 0ull) {
-                        const int k = k0 + __ffsll((long long)cand) - 1;
+                        const int kb = __ffsll((long long)cand) - 1;
                         cand &= cand - 1ull;
-                        self_contact_tests(M, xC, M.sc_a[k], M.sc_b[k] & 127, k, cq, nq);
+                        const int a = M.sc_a[k0 + kb], b = M.sc_b[k0 + kb] & 127;
+                        V3 c1, c2;
+                        const float d2 = capsule_closest(M, xC, a < b ? a : b, a < b ? b : a, c1, c2);
+                        const float rr = M.cap_r[a] + M.cap_r[b];
+                        if (d2 < rr * rr) hits |= 1ull << kb;
                     }
                 }
-                if (nq > kSCQueue) { xM[32] = 1.f; nq = kSCQueue; }  // cannot happen with <= 48 spheres; parked loudly if it does
-                // Phase 3: the queued contacts, every lane popping its own
-                while (__any_sync(0xffffffffu, nq > 0)) {
-                    if (nq > 0) {
-                        const unsigned e = cq[--nq];
-                        const int k = (int)(e >> 16), bb = M.sc_b[k];
-                        sphere_contact(M, xC, G0, M.sc_a[k], bb & 127, (int)(e >> 8) & 255, (int)e & 255, dt, (bb & 128) != 0, W, wmask);
+                // Phase 3: the pairs in contact (rare, lane-divergent): all lanes pop their own together
+                while (__any_sync(0xffffffffu, hits != 0ull)) {
+                    if (hits != 0ull) {
+                        const int k = k0 + __ffsll((long long)hits) - 1;
+                        hits &= hits - 1ull;
+                        const int bb = M.sc_b[k];
+                        capsule_contact(M, xC, G0, M.sc_a[k], bb & 127, dt, (bb & 128) != 0, W, wmask);
                     }
                 }
                 if (sflag & kSegBarAfter) group_barrier(bar_id, GT);
@@ -593,7 +599,7 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
                     for (int j = 0; j < 6; ++j) { k[(7 + j) * 32] = c.v.a[j]; k[(13 + j) * 32] = c.b.a[j]; }
                 }
                 c.R = qmat(c.q);
-                if (SC && !chain) publish_spheres(M, 0, c.R, c.p, xC, G0 + (int)M.ctr_off[0] * 32);  // the root body's spheres
+                if (SC && !chain) publish_capsule(M, 0, c.R, c.p, xC, G0 + (int)M.ctr_off[0] * 32);  // the root body's capsule
                 for (int i = first; i <= lastl; ++i) {
                     int link;
                     float qj, qdj;
@@ -613,7 +619,7 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
 #pragma unroll
                         for (int j = 0; j < 6; ++j) dst[(13 + j) * 32] = c.b.a[j];
                     }
-                    if (SC) publish_spheres(M, link, c.R, c.p, xC, G0 + (int)M.ctr_off[link] * 32);
+                    if (SC) publish_capsule(M, link, c.R, c.p, xC, G0 + (int)M.ctr_off[link] * 32);
                 }
                 if (SC && chain) { vkeep = c.v; bkeep = c.b; keep_last = lastl; }
                 if (chain && last && (sflag & kSegSensor)) {  // the foot's frame is needed again after the downward sweep

@@ -56,6 +56,8 @@ def _leg(side: str):
             ("capsule", (-0.07, 0.02, 0), (0.14, 0.04, 0), 0.027),
             ("capsule", (-0.07, 0.0, 0), (0.14, -0.02, 0), 0.027),
         ],
+        # self-collision proxy: one capsule along the foot enclosing the two sole capsules
+        sc_capsule=((-0.07, -s * 0.01, 0), (0.14, -s * 0.01, 0), 0.045),
     )
     return thigh, shin, foot
 
@@ -77,6 +79,7 @@ def _arm(side: str):
             ("capsule", (0.01, -s * 0.01, 0.01), (0.17, -s * 0.17, 0.17), 0.031),
             ("sphere", (0.18, -s * 0.18, 0.18), 0.04),  # hand
         ],
+        sc_capsule=((0.01, -s * 0.01, 0.01), (0.18, -s * 0.18, 0.18), 0.04),  # forearm + hand
     )
     return upper, lower
 
@@ -93,6 +96,7 @@ def humanoid_bodies():
             ("capsule", (-0.01, -0.06, -0.12), (-0.01, 0.06, -0.12), 0.06),  # upper_waist
             ("sphere", (0, 0, 0.19), 0.09),  # head
         ],
+        sc_capsule=((-0.01, 0, -0.12), (0, 0, 0.19), 0.11),  # upper waist .. head column
     )
     lower_waist = dict(
         name="lower_waist", parent="torso", pos=(-0.01, 0, -0.26), quat=(1.0, 0, -0.002, 0),

@@ -106,10 +106,14 @@ class ArticulationModel:
     angular_damping: float = 0.05
     max_angular_velocity: float = 5729.58008 * math.pi / 180.0
     max_depenetration_velocity: float = 10.0   # cfg/task/Humanoid.yaml:62,90
-    self_contact_stiffness: float = 3.0e3      # explicit sphere-sphere penalty (DESIGN.md "self-collision")
-    self_contact_damping: float = 3.0e1
+    self_contact_stiffness: float = 1.0e4      # explicit sphere-sphere penalty (DESIGN.md "self-collision")
+    self_contact_damping: float = 5.0e1
     enable_self_collisions: bool = False       # cfg/task/Humanoid.yaml:80 (True), Ant.yaml:82 (False)
     collision_pairs: np.ndarray = field(default_factory=lambda: np.zeros((0, 2), np.int32))  # [P,2] link pairs
+    # self-collision shape of a link: one capsule (segment a-b in the link frame, radius; radius 0 = none)
+    capsule_a: np.ndarray = field(default_factory=lambda: np.zeros((0, 3)))
+    capsule_b: np.ndarray = field(default_factory=lambda: np.zeros((0, 3)))
+    capsule_radius: np.ndarray = field(default_factory=lambda: np.zeros(0))
     fixed_base: bool = False      # link 0 welded to the world
 
     @property
@@ -256,6 +260,23 @@ def build_model(name: str, **overrides) -> ArticulationModel:
                 continue
             pairs.append((last_link[a], last_link[b]))
     model.collision_pairs = np.array(pairs, np.int32).reshape(-1, 2)
+    # one self-collision capsule per body: the table's `sc_capsule` proxy, else the body's single capsule / sphere geom
+    model.capsule_a, model.capsule_b, model.capsule_radius = np.zeros((L, 3)), np.zeros((L, 3)), np.zeros(L)
+    for b in bodies:
+        link, off = last_link[b["name"]], last_anchor[b["name"]]
+        shape = b.get("sc_capsule")
+        solid = [g for g in b["geoms"] if g[0] in ("capsule", "sphere")]
+        if shape is None and len(solid) == 1:
+            g = solid[0]
+            shape = (g[1], g[2], g[3]) if g[0] == "capsule" else (g[1], g[1], g[2])
+        if shape is None:
+            continue  # (a multi-geom body without a proxy takes no part in self-collision)
+        model.capsule_a[link] = np.array(shape[0], float) - off
+        model.capsule_b[link] = np.array(shape[1], float) - off
+        model.capsule_radius[link] = float(shape[2])
+    model.collision_pairs = np.array([pr for pr in model.collision_pairs
+                                      if model.capsule_radius[pr[0]] > 0 and model.capsule_radius[pr[1]] > 0],
+                                     np.int32).reshape(-1, 2)
     model.enable_self_collisions = bool(table.get("self_collision", False))
     drive = table.get("drive")
     if drive:  # PD position drive on every joint (tasks/anymal.py:128)
@@ -323,3 +344,9 @@ def fill_desc(model: ArticulationModel, desc) -> None:
     desc.num_collision_pairs = len(pairs)
     for k, (a, b) in enumerate(pairs):
         desc.pair_link_a[k], desc.pair_link_b[k] = int(a), int(b)
+    for i in range(L):
+        has = len(model.capsule_radius) == L and model.capsule_radius[i] > 0
+        desc.capsule_radius[i] = float(model.capsule_radius[i]) if has else 0.0
+        for k in range(3):
+            desc.capsule_a[i][k] = float(model.capsule_a[i, k]) if has else 0.0
+            desc.capsule_b[i][k] = float(model.capsule_b[i, k]) if has else 0.0

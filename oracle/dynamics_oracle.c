@@ -241,36 +241,49 @@ static int step_one(const OigeModelDesc* M, double* pos, double* quat, double* v
                                      cons[s].C.z * J.jv[a].z * J.jv[b].z;
         }
     }
-    /* 4b. self-collision: explicit sphere-sphere penalty between the links of each collision pair (equal and
-     * opposite forces at the midpoint of the overlap; damping only while approaching; no friction) */
+    /* 4b. self-collision: explicit capsule-capsule penalty between the links of each collision pair.  One contact per
+     * pair at the closest points of the two segments; equal and opposite forces at the midpoint of the overlap; damping
+     * only while approaching; no friction. */
     for (int k = 0; k < M->num_collision_pairs; ++k) {
         int la = M->pair_link_a[k], lb = M->pair_link_b[k];
-        for (int sa = 0; sa < M->num_spheres; ++sa) {
-            if (M->sphere_link[sa] != la) continue;
-            v3 ca = add(p[la], mv(R[la], V(M->sphere_pos[sa][0], M->sphere_pos[sa][1], M->sphere_pos[sa][2])));
-            for (int sb = 0; sb < M->num_spheres; ++sb) {
-                if (M->sphere_link[sb] != lb) continue;
-                v3 cb = add(p[lb], mv(R[lb], V(M->sphere_pos[sb][0], M->sphere_pos[sb][1], M->sphere_pos[sb][2])));
-                v3 d = sub(ca, cb);
-                double ra = M->sphere_radius[sa], rb = M->sphere_radius[sb];
-                double dist = sqrt(dt3(d, d)), pen = ra + rb - dist;
-                if (!(pen > 0) || !(dist > 1e-9)) continue;
-                v3 n = scl(1.0 / dist, d); /* from b to a */
-                v3 pc = add(cb, scl(rb - 0.5 * pen, n));
-                v3 va = add(vo[la], crs(w[la], sub(pc, p[la])));
-                v3 vb = add(vo[lb], crs(w[lb], sub(pc, p[lb])));
-                double vn = dt3(sub(va, vb), n);
-                double penc = pen;
-                if (M->max_depenetration_velocity > 0) penc = fmin(penc, (double)M->max_depenetration_velocity * dt);
-                double f = (double)M->self_contact_stiffness * penc - (vn < 0 ? (double)M->self_contact_damping * vn : 0.0);
-                if (!(f > 0)) continue;
-                v3 F = scl(f, n);
-                point_jacobian(M, la, pc, p, axw, &J, nv);
-                for (int a = 0; a < nv; ++a) rhs[a] += dt3(J.jv[a], F);
-                point_jacobian(M, lb, pc, p, axw, &J, nv);
-                for (int a = 0; a < nv; ++a) rhs[a] -= dt3(J.jv[a], F);
-            }
+        double ra = M->capsule_radius[la], rb = M->capsule_radius[lb];
+        if (!(ra > 0) || !(rb > 0)) continue;
+        v3 P1 = add(p[la], mv(R[la], V(M->capsule_a[la][0], M->capsule_a[la][1], M->capsule_a[la][2])));
+        v3 Q1 = add(p[la], mv(R[la], V(M->capsule_b[la][0], M->capsule_b[la][1], M->capsule_b[la][2])));
+        v3 P2 = add(p[lb], mv(R[lb], V(M->capsule_a[lb][0], M->capsule_a[lb][1], M->capsule_a[lb][2])));
+        v3 Q2 = add(p[lb], mv(R[lb], V(M->capsule_b[lb][0], M->capsule_b[lb][1], M->capsule_b[lb][2])));
+        /* closest points of two segments (Ericson, Real-Time Collision Detection 5.1.9) */
+        v3 d1 = sub(Q1, P1), d2 = sub(Q2, P2), r = sub(P1, P2);
+        double a = dt3(d1, d1), e = dt3(d2, d2), f = dt3(d2, r), c = dt3(d1, r), b = dt3(d1, d2);
+        double sp = 0, tp = 0, eps = 1e-12;
+        if (a <= eps && e <= eps) { sp = tp = 0; }
+        else if (a <= eps) { sp = 0; tp = fmin(fmax(f / e, 0.0), 1.0); }
+        else if (e <= eps) { tp = 0; sp = fmin(fmax(-c / a, 0.0), 1.0); }
+        else {
+            double den = a * e - b * b;
+            sp = den > 1e-9 * a * e ? fmin(fmax((b * f - c * e) / den, 0.0), 1.0) : 0.0;
+            tp = (b * sp + f) / e;
+            if (tp < 0) { tp = 0; sp = fmin(fmax(-c / a, 0.0), 1.0); }
+            else if (tp > 1) { tp = 1; sp = fmin(fmax((b - c) / a, 0.0), 1.0); }
         }
+        v3 c1 = add(P1, scl(sp, d1)), c2 = add(P2, scl(tp, d2));
+        v3 d = sub(c1, c2);
+        double dist = sqrt(dt3(d, d)), pen = ra + rb - dist;
+        if (!(pen > 0) || !(dist > 1e-9)) continue;
+        v3 n = scl(1.0 / dist, d); /* from b to a */
+        v3 pc = add(c2, scl(rb - 0.5 * pen, n));
+        v3 va = add(vo[la], crs(w[la], sub(pc, p[la])));
+        v3 vb = add(vo[lb], crs(w[lb], sub(pc, p[lb])));
+        double vn = dt3(sub(va, vb), n);
+        double penc = pen;
+        if (M->max_depenetration_velocity > 0) penc = fmin(penc, (double)M->max_depenetration_velocity * dt);
+        double fm = (double)M->self_contact_stiffness * penc - (vn < 0 ? (double)M->self_contact_damping * vn : 0.0);
+        if (!(fm > 0)) continue;
+        v3 F = scl(fm, n);
+        point_jacobian(M, la, pc, p, axw, &J, nv);
+        for (int q2 = 0; q2 < nv; ++q2) rhs[q2] += dt3(J.jv[q2], F);
+        point_jacobian(M, lb, pc, p, axw, &J, nv);
+        for (int q2 = 0; q2 < nv; ++q2) rhs[q2] -= dt3(J.jv[q2], F);
     }
     /* 5. solve (a welded base: its six rows/columns become the identity with zero right-hand side) */
     if (M->fixed_base) {

@@ -134,15 +134,35 @@ def link_frames(model, s, e=0):
     return R, p
 
 
+def _segment_distance(P1, Q1, P2, Q2):
+    d1, d2, r = Q1 - P1, Q2 - P2, P1 - P2
+    a, e, f, c, b = d1 @ d1, d2 @ d2, d2 @ r, d1 @ r, d1 @ d2
+    if a <= 1e-12 and e <= 1e-12:
+        s = t = 0.0
+    elif a <= 1e-12:
+        s, t = 0.0, min(max(f / e, 0.0), 1.0)
+    elif e <= 1e-12:
+        t, s = 0.0, min(max(-c / a, 0.0), 1.0)
+    else:
+        den = a * e - b * b
+        s = min(max((b * f - c * e) / den, 0.0), 1.0) if den > 1e-9 * a * e else 0.0
+        t = (b * s + f) / e
+        if t < 0:
+            t, s = 0.0, min(max(-c / a, 0.0), 1.0)
+        elif t > 1:
+            t, s = 1.0, min(max((b - c) / a, 0.0), 1.0)
+    return float(np.linalg.norm((P1 + s * d1) - (P2 + t * d2)))
+
+
 def self_contact_depths(model, s, e=0):
-    """Penetration depth (> 0: in contact) of every sphere pair of the model's self-collision link pairs, env e."""
+    """Penetration depth (> 0: in contact) of the capsules of every self-collision link pair of the model, env e."""
     R, p = link_frames(model, s, e)
-    c = [p[int(l)] + R[int(l)] @ model.sphere_pos[k] for k, l in enumerate(model.sphere_link)]
     out = []
     for la, lb in model.collision_pairs:
-        for a in np.nonzero(model.sphere_link == la)[0]:
-            for b in np.nonzero(model.sphere_link == lb)[0]:
-                out.append(model.sphere_radius[a] + model.sphere_radius[b] - np.linalg.norm(c[a] - c[b]))
+        la, lb = int(la), int(lb)
+        P1, Q1 = p[la] + R[la] @ model.capsule_a[la], p[la] + R[la] @ model.capsule_b[la]
+        P2, Q2 = p[lb] + R[lb] @ model.capsule_a[lb], p[lb] + R[lb] @ model.capsule_b[lb]
+        out.append(model.capsule_radius[la] + model.capsule_radius[lb] - _segment_distance(P1, Q1, P2, Q2))
     return np.array(out)
 
 

@@ -46,7 +46,7 @@ def test_struct_layouts_match_header_sizes():
     assert ctypes.sizeof(_lib.OigeAnymalBuffers) == 11 * 8
     L, K, S = _lib.MAX_LINKS, _lib.MAX_SPHERES, _lib.MAX_SENSORS
     expect = (16 + 3 * L * 4 + L * 4 * (3 + 4 + 3 + 1 + 3 + 6 + 6 + 3) + K * 4 * (1 + 3 + 1) + S * 4 + (3 + 8) * 4
-              + (4 + 1) * 4 + 2 * _lib.MAX_PAIRS * 4)  # ABI 3: velocity limits, self-collision pairs
+              + (4 + 1) * 4 + 2 * _lib.MAX_PAIRS * 4 + L * 7 * 4)  # ABI 3: velocity limits, self-collision pairs / capsules
     assert ctypes.sizeof(_lib.OigeModelDesc) == expect
 
 
