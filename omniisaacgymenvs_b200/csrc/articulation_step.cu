@@ -33,6 +33,7 @@
 // Tensor cores are not used: the per-env matrices are 6x6 and the work is a latency-bound tree
 // recursion, not a dense contraction.
 #include <math.h>
+#include <stdio.h>
 #include <stdlib.h>
 
 #include <atomic>
@@ -1210,6 +1211,17 @@ int k2_step(const OigeModel* model, const OigeTaskParams* P, const OigeState* st
     return check_launch("articulation_step_kernel");
 }
 
+#ifdef OIGE_STAMPS
+// diagnostic build only (tools/k2f_stamps.py): the (tag, clock64) pairs of group 0 of CTA 0 of the last K2-F launch
+extern "C" int oige_debug_read_stamps(long long* out) {
+    return (int)cudaMemcpyFromSymbol(out, g_stamps, sizeof(long long) * 4 * 128 * 2);
+}
+extern "C" int oige_debug_clear_stamps(void) {
+    static long long zero[4 * 128 * 2];
+    return (int)cudaMemcpyToSymbol(g_stamps, zero, sizeof(zero));
+}
+#endif
+
 uint64_t k2_nonfinite_count() {
     unsigned long long v = 0;
     if (cudaMemcpyFromSymbol(&v, g_nonfinite_envs, sizeof(v)) != cudaSuccess) { cudaGetLastError(); return 0; }
@@ -1390,7 +1402,7 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
                 for (int s2 = 0; s2 < d->num_sensors; ++s2) zero = zero && d->sensor_link[s2] != i;
                 return zero;
             };
-            const int fixed_floats = npub * 6 + nt * kKin + (nt - 1) * 4 + 2 + best_r * maxc * kPu;
+            const int fixed_floats = npub * 6 + nt * kKin + (nt - 1) * 4 + 2 + (has_sc ? best_r : 0) + best_r * maxc * kPu;
             const int max_group_floats = (int)((227 * 1024 - sizeof(RoleModel) - 256) / (4 * 32 * sizeof(float)));
             int own_t[kMaxRoles] = {-1, -1, -1, -1};
             for (int t = 0; t < nt; ++t) {
@@ -1421,6 +1433,7 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
             //   role 0:  trunk kinematics | barrier K | [own inertia of a trunk link] chains ... | barrier H | trunk sweep
             //   role r:  barrier K | [own inertia of a trunk link] chains ... | barrier H
             int sensor_chains[kMaxRoles] = {0};
+            int hb_roles[kRT] = {0, 0, 0, 0};
             bool slot_written[kRSlots] = {false};
             bool sensor_seen[OIGE_MAX_SENSORS] = {false};
             for (int r = 0; r < best_r && fits; ++r) {
@@ -1476,12 +1489,28 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
                 if (!fits) break;
                 (void)first_up;
                 if (r == 0) {
-                    add_seg(kSegTrunkUp, 0, nt - 1, kSegBarBefore, 0, 0);
+                    add_seg(kSegTrunkUp, 0, nt - 1, 0, 0, 0);  // (waits per trunk link, see hb_id)
                 } else {
                     rm->seg_flag[r][first_work] |= kSegBarBefore;
-                    rm->seg_flag[r][ns - 1] |= kSegBarAfter;
+                    // after its last sweep into a slot on trunk link t the role ARRIVES at t's hand-over barrier
+                    for (int t = 0; t < nt; ++t) {
+                        int lastseg = -1;
+                        for (int q = first_up; q < ns; ++q)
+                            if ((rm->seg_kind[r][q] == kSegChain || rm->seg_kind[r][q] == kSegOwn) && rm->seg_att[r][q] == t) lastseg = q;
+                        if (lastseg >= 0) { rm->seg_flag[r][lastseg] |= kSegArrive; hb_roles[t] |= 1 << r; }
+                    }
                 }
                 rm->nseg[r] = (unsigned char)ns;
+            }
+            {   // hand-over barriers: one per trunk link that other roles hand over to (two ids per group)
+                int nb = 0;
+                for (int t = 0; t < nt && fits; ++t) {
+                    if (!hb_roles[t]) continue;
+                    if (++nb > 2) { fits = false; break; }
+                    int cnt = 1;
+                    for (int r = 1; r < best_r; ++r) cnt += (hb_roles[t] >> r) & 1;
+                    rm->hb_id[t] = (unsigned char)nb; rm->hb_cnt[t] = (unsigned char)(32 * cnt);
+                }
             }
             for (int s2 = 0; s2 < d->num_sensors; ++s2) fits = fits && sensor_seen[s2];  // sensors sit on chain tips
             // scratch layout of a 32-env group (float offsets, x32 lanes)
@@ -1496,7 +1525,8 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
             rm->oT = rm->oK + nt * kKin;
             rm->oS = rm->oT + (nt - 1) * 4;
             rm->oM = rm->oS + (best_r == 3 ? 0 : d->num_sensors * 7);  // the 3-role variants keep the sensor frame in registers
-            rm->oL = rm->oM + 2;
+            rm->oH = rm->oM + 2;                       // one hit word per role (self-collision)
+            rm->oL = rm->oH + (has_sc ? best_r : 0);
             rm->group_floats = rm->oL + best_r * maxc * kPu;
             // ---- self-collision tables ----
             rm->has_sc = has_sc ? 1 : 0;
@@ -1532,7 +1562,78 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
                     rm->cap_il2[i] = hl > 1e-12f ? 1.f / hl : 0.f;
                     rm->brad[i] = (0.5f * sqrtf(hl) + d->capsule_radius[i]) * 1.0001f + 1e-6f;  // (never cuts a touching pair)
                 }
-                // directed pairs, grouped by role and sorted by the own link
+                // Every pair goes into the list of ONE role: the owner of both links, else one of the two owners, dealt so
+                // that the roles' expected NARROW-phase work is even (the phases are separated by group barriers, the
+                // slowest role sets the pace).  A pair whose capsules are near each other at the rest pose (q = 0) is a
+                // narrow-phase candidate most of the time (the two thighs, a thigh and the lower waist, ...) and weighs
+                // kNearWeight, any other pair kFarWeight (its broad-phase test plus an occasional narrow test).  A list
+                // holds at most 32 entries (one candidate bit each).  Lists are sorted by the first link.
+                double Rw[32][9], pw[32][3];
+                for (int i = 0; i < L; ++i) {
+                    double Rl[9];
+                    {
+                        const double w = i == 0 ? 1.0 : d->joint_quat[i][0], x = i == 0 ? 0.0 : d->joint_quat[i][1];
+                        const double y = i == 0 ? 0.0 : d->joint_quat[i][2], z = i == 0 ? 0.0 : d->joint_quat[i][3];
+                        const double m[9] = {1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y),
+                                             2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x),
+                                             2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)};
+                        memcpy(Rl, m, sizeof(m));
+                    }
+                    if (i == 0) {
+                        memcpy(Rw[0], Rl, sizeof(Rl));
+                        pw[0][0] = pw[0][1] = pw[0][2] = 0.0;
+                        continue;
+                    }
+                    const int pa = h->parent[i];
+                    for (int r2 = 0; r2 < 3; ++r2) {
+                        pw[i][r2] = pw[pa][r2];
+                        for (int c2 = 0; c2 < 3; ++c2) {
+                            pw[i][r2] += Rw[pa][3 * r2 + c2] * d->joint_pos[i][c2];
+                            Rw[i][3 * r2 + c2] = 0.0;
+                            for (int k2 = 0; k2 < 3; ++k2) Rw[i][3 * r2 + c2] += Rw[pa][3 * r2 + k2] * Rl[3 * k2 + c2];
+                        }
+                    }
+                }
+                auto rest_gap = [&](int la, int lb) {  // distance between the two capsule surfaces at the rest pose (sampled)
+                    double best = 1e30;
+                    for (int ia = 0; ia <= 8; ++ia)
+                        for (int ib = 0; ib <= 8; ++ib) {
+                            double dd = 0.0;
+                            for (int r2 = 0; r2 < 3; ++r2) {
+                                double xa = pw[la][r2], xb = pw[lb][r2];
+                                for (int c2 = 0; c2 < 3; ++c2) {
+                                    xa += Rw[la][3 * r2 + c2] * (d->capsule_a[la][c2] + (d->capsule_b[la][c2] - d->capsule_a[la][c2]) * ia / 8.0);
+                                    xb += Rw[lb][3 * r2 + c2] * (d->capsule_a[lb][c2] + (d->capsule_b[lb][c2] - d->capsule_a[lb][c2]) * ib / 8.0);
+                                }
+                                dd += (xa - xb) * (xa - xb);
+                            }
+                            if (dd < best) best = dd;
+                        }
+                    return sqrt(best) - d->capsule_radius[la] - d->capsule_radius[lb];
+                };
+                const double kNearGap = 0.12, kNearWeight = 9.0, kFarWeight = 2.0;
+                int pair_role[OIGE_MAX_PAIRS], sc_count[kMaxRoles] = {0, 0, 0, 0};
+                double sc_load[kMaxRoles] = {0.0, 0.0, 0.0, 0.0};
+                double pair_w[OIGE_MAX_PAIRS];
+                for (int k2 = 0; k2 < d->num_collision_pairs && fits; ++k2) {
+                    const int la = d->pair_link_a[k2], lb = d->pair_link_b[k2];
+                    if (la < 0 || la >= L || lb < 0 || lb >= L || la == lb || sphn[la] == 0 || sphn[lb] == 0 ||
+                        owner_of_link[la] < 0 || owner_of_link[lb] < 0) { fits = false; break; }
+                    pair_w[k2] = rest_gap(la, lb) < kNearGap ? kNearWeight : kFarWeight;
+                    pair_role[k2] = -1;
+                    if (owner_of_link[la] == owner_of_link[lb]) {
+                        pair_role[k2] = owner_of_link[la]; sc_load[pair_role[k2]] += pair_w[k2]; ++sc_count[pair_role[k2]];
+                    }
+                }
+                for (int pass = 0; pass < 2 && fits; ++pass)  // heavy pairs first, each to the lighter of its two owners
+                    for (int k2 = 0; k2 < d->num_collision_pairs; ++k2) {
+                        if (pair_role[k2] >= 0 || (pass == 0) != (pair_w[k2] > kFarWeight)) continue;
+                        const int ra = owner_of_link[d->pair_link_a[k2]], rb = owner_of_link[d->pair_link_b[k2]];
+                        int pick = sc_load[ra] < sc_load[rb] || (sc_load[ra] == sc_load[rb] && ra > rb) ? ra : rb;
+                        if (sc_count[pick] >= 32) pick = pick == ra ? rb : ra;
+                        pair_role[k2] = pick;
+                        sc_load[pick] += pair_w[k2]; ++sc_count[pick];
+                    }
                 int npairs = 0;
                 for (int r = 0; r < best_r && fits; ++r) {
                     rm->sc_off[r] = (unsigned char)npairs;
@@ -1540,20 +1641,33 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
                         if (owner_of_link[a] != r) continue;
                         for (int k2 = 0; k2 < d->num_collision_pairs; ++k2) {
                             int la = d->pair_link_a[k2], lb = d->pair_link_b[k2];
-                            if (la < 0 || la >= L || lb < 0 || lb >= L || la == lb || sphn[la] == 0 || sphn[lb] == 0 ||
-                                owner_of_link[la] < 0 || owner_of_link[lb] < 0) { fits = false; break; }
-                            if (lb == a) { const int t2 = la; la = lb; lb = t2; }
+                            if (pair_role[k2] != r) continue;
+                            const bool both = owner_of_link[la] == r && owner_of_link[lb] == r;
+                            if (both && lb < la) { const int t2 = la; la = lb; lb = t2; }  // first link = the lower one
+                            if (!both && owner_of_link[la] != r) { const int t2 = la; la = lb; lb = t2; }
                             if (la != a) continue;
-                            const bool both = owner_of_link[lb] == r;  // both links are this role's: evaluated once
-                            if (both && lb < la) continue;
-                            if (npairs >= kSCMax || npairs >= 255) { fits = false; break; }
+                            if (npairs >= kSCMax) { fits = false; break; }
                             rm->sc_a[npairs] = (unsigned char)la; rm->sc_b[npairs] = (unsigned char)(lb | (both ? 128 : 0));
                             ++npairs;
                         }
                     }
                 }
                 for (int r = best_r; r < 8; ++r) rm->sc_off[r] = (unsigned char)npairs;
-                for (int r = 0; r < best_r; ++r) fits = fits && rm->sc_off[r + 1] - rm->sc_off[r] <= 64;  // candidate bit mask
+                for (int r = 0; r < best_r; ++r) fits = fits && rm->sc_off[r + 1] - rm->sc_off[r] <= 32;  // candidate bit mask
+                fits = fits && npairs == d->num_collision_pairs && best_r <= 4;
+                for (int r = 0; r < best_r && fits; ++r)
+                    for (int k2 = rm->sc_off[r]; k2 < rm->sc_off[r + 1]; ++k2) {
+                        const int ob = owner_of_link[rm->sc_b[k2] & 127];
+                        if (ob != r) rm->sc_to[r][ob] |= 1u << (k2 - rm->sc_off[r]);
+                    }
+                if (getenv("OIGE_DUMP_ROLES") != nullptr) {
+                    for (int r = 0; r < best_r; ++r) {
+                        fprintf(stderr, "[oige] self-collision list of role %d (load %.0f):", r, sc_load[r]);
+                        for (int k2 = rm->sc_off[r]; k2 < rm->sc_off[r + 1]; ++k2)
+                            fprintf(stderr, " %d-%d%s", rm->sc_a[k2], rm->sc_b[k2] & 127, (rm->sc_b[k2] & 128) ? "*" : "");
+                        fprintf(stderr, "\n");
+                    }
+                }
                 // Bounding centres (3 floats per link with spheres) live in memory that is dead between the kinematics and
                 // the inertia sweeps: floats 7..12 of the records of the role's own massless intermediate links (two
                 // centres each), then the published-acceleration rows and the tail of the sphere-centre region.
@@ -1580,13 +1694,22 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
                         rm->ctr_off[i] = (unsigned short)pool[used++];
                     }
                 }
-                for (int k2 = 0; k2 < npairs; ++k2) {
+                for (int k2 = 0; k2 < npairs && fits; ++k2) {
                     const int la = rm->sc_a[k2], lb = rm->sc_b[k2] & 127;
                     const float rr = rm->brad[la] + rm->brad[lb], rr2 = rr * rr;
                     unsigned bits;
                     memcpy(&bits, &rr2, sizeof(bits));
-                    rm->sc_rec[k2].x = rm->ctr_off[lb]; rm->sc_rec[k2].y = bits;
-                    rm->sc_ctra[k2] = rm->ctr_off[la];
+                    const unsigned oca = (unsigned)rm->ctr_off[la] * 128u, ocb = (unsigned)rm->ctr_off[lb] * 128u;
+                    if (oca > 0xffffu || ocb > 0xffffu) { fits = false; break; }
+                    rm->sc_brd[k2].x = oca << 16 | ocb; rm->sc_brd[k2].y = bits;
+                    const int lo = la < lb ? la : lb, hi = la < lb ? lb : la;
+                    const unsigned olo = (unsigned)rm->cap_idx[lo] * 6u * 128u, ohi = (unsigned)rm->cap_idx[hi] * 6u * 128u;
+                    if (olo > 0xffffu || ohi > 0xffffu) { fits = false; break; }
+                    const float cr = rm->cap_r[la] + rm->cap_r[lb], cr2 = cr * cr;
+                    rm->sc_nar[k2].x = olo << 16 | ohi;
+                    memcpy(&rm->sc_nar[k2].y, &rm->cap_il2[lo], 4);
+                    memcpy(&rm->sc_nar[k2].z, &rm->cap_il2[hi], 4);
+                    memcpy(&rm->sc_nar[k2].w, &cr2, 4);
                 }
                 // the sphere centres live in the hand-over slots' memory during the kinematics / pair phases
                 if (kRT + maxc > 32 || rm->group_floats > max_group_floats) fits = false;

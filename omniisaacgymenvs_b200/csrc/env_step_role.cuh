@@ -33,7 +33,8 @@ constexpr int kRSlots = 8;   // hand-over slots
 constexpr int kRSeg = 8;     // segments per role
 constexpr int kSegTrunkKin = 0, kSegOwn = 1, kSegChain = 2, kSegTrunkUp = 3, kSegPairs = 4;
 constexpr int kSegBarBefore = 1, kSegBarAfter = 2, kSegSlotFirst = 4, kSegSensor = 8, kSegKinOnly = 16, kSegUpOnly = 32;
-constexpr int kSCMax = 144;  // directed self-collision link pairs (Humanoid: 2 x 66)
+constexpr int kSegArrive = 64;  // after the sweep: arrive at the hand-over barrier of the segment's attach trunk link
+constexpr int kSCMax = 96;   // self-collision link pairs (Humanoid: 66), each listed ONCE, with the role that evaluates it
 constexpr int kKin = 19;     // quat 4, p 3, v 6, b 6
 constexpr int kPu = 13;      // s 6, U/d 6, u'''
 constexpr int kHand = 27;    // I^a 21, p^a 6
@@ -66,22 +67,30 @@ struct alignas(16) RoleModel {
     unsigned char seg_att[4][kRSeg], seg_slot[4][kRSeg];
     unsigned char tlink[kRT], town[kRT], tpub[kRT];      // trunk idx -> link, own inertia handed to a role?, xA index (255: none)
     unsigned char ts_begin[kRT + 1], ts_slot[kRSlots];   // hand-over slots attached to trunk link t
-    // ---- self-collision (enable_self_collisions): directed link pairs (a = a link of the role, b = its partner) ----
-    unsigned char sc_off[8];                              // role r evaluates pairs [sc_off[r], sc_off[r + 1])
-    unsigned char sc_a[kSCMax], sc_b[kSCMax];
+    // ---- self-collision (enable_self_collisions): every link pair is listed once, in the list of ONE of the two roles
+    // that own its links (a = a link of that role, b = its partner); the other role learns of a contact through the
+    // evaluating role's hit word (xH) ----
+    unsigned char sc_off[8];                              // role r evaluates entries [sc_off[r], sc_off[r + 1]) (<= 32)
+    unsigned char sc_a[kSCMax], sc_b[kSCMax];             // (bit 7 of sc_b: both links belong to the evaluating role)
     unsigned char w_idx[kRL];                             // link -> entry of its role's wrench accumulator
     unsigned short rec_off[kRL];                          // link -> float offset (x32 lanes) of its (quat, p, v) record
-    float brad[kRL];                                      // bounding radius about the midpoint of its first / last sphere
+    float brad[kRL];                                      // bounding radius about the midpoint of its capsule axis
     unsigned short ctr_off[kRL];                          // link -> float offset (x32 lanes) of its bounding centre (3 floats)
     unsigned char cap_idx[kRL];                           // link -> its capsule's slot in the published end points
-    unsigned char pad[15];
+    // hand-over barriers: role 0 waits at trunk link t only for the roles with a slot on t (hb_id[t]: 0 none, else the
+    // barrier's offset from the group's first id; hb_cnt[t]: threads taking part, role 0's warp included)
+    unsigned char hb_id[kRT], hb_cnt[kRT];
+    unsigned char pad[7];
+    int oH, pad_h[3];                                     // float offset (x32 lanes) of the roles' hit words
     float cap_a[3][kRL], cap_b[3][kRL], cap_r[kRL];       // self-collision capsule of a link (link frame); r = 0: none
     float cap_il2[kRL];                                   // 1 / |b - a|^2 (0 for a sphere)
-    // broad-phase record of list entry k: x = float offset of b's bounding centre, y = bits of (brad[a] + brad[b])^2,
-    // z = float offset of a's bounding centre (read when a changes)
-    uint2 sc_rec[kSCMax];
-    unsigned short sc_ctra[kSCMax];
-    unsigned char pad2[(16 - (kSCMax * 2) % 16) % 16];
+    // broad phase of entry k: x = byte offset (lane 0) of a's bounding centre << 16 | b's, y = bits of
+    // (brad[a] + brad[b])^2; zero-filled past the last entry (a threshold of 0 never passes), 4 entries of slack
+    uint2 sc_brd[kSCMax + 4];
+    // narrow phase of entry k, links in canonical order lo < hi: x = byte offset of lo's capsule end points << 16 | hi's,
+    // y, z = bits of 1 / length^2 of lo's, hi's axis, w = bits of (r_lo + r_hi)^2
+    uint4 sc_nar[kSCMax];
+    unsigned sc_to[4][4];                                 // [src role][dst role]: entries of src's list whose partner link is dst's
 };
 static_assert(sizeof(RoleModel) % 16 == 0, "RoleModel must be int4-copyable");
 
@@ -109,8 +118,26 @@ struct FArgs {
 
 __device__ unsigned long long g_nonfinite_envs = 0;  // envs parked by the non-finite guard since load (diagnostic)
 
+// Phase timing (diagnostic build only, -DOIGE_STAMPS -> tools/k2f_stamps.py): (tag, clock64) pairs of group 0 of CTA 0.
+#ifdef OIGE_STAMPS
+__device__ long long g_stamps[4][128][2];
+#define STAMP(tag)                                                                                         \
+    do {                                                                                                   \
+        if (blockIdx.x == 0 && grp == 0 && lane == 0 && stamp_i < 128) {                                   \
+            g_stamps[role][stamp_i][0] = (tag);                                                            \
+            g_stamps[role][stamp_i][1] = clock64();                                                        \
+            ++stamp_i;                                                                                     \
+        }                                                                                                  \
+    } while (0)
+#else
+#define STAMP(tag) do { } while (0)
+#endif
+
 __device__ __forceinline__ void group_barrier(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+__device__ __forceinline__ void group_arrive(int id, int nthreads) {  // producer side: does not wait
+    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
 // register arrays with a run-time index: select chains keep them in registers (no local memory)
@@ -215,10 +242,11 @@ __device__ __forceinline__ void joint_reduce(const MT& M, int i, const M3& R, V3
 // ---- self-collision (enable_self_collisions, cfg/task/Humanoid.yaml:80) -------------------------------------------------
 // Explicit capsule-capsule penalty between the links of a collision pair (one capsule per body), evaluated at the state
 // the substep starts from (an implicit pair force would couple two branches of the tree, i.e. close a kinematic loop,
-// and break the O(n) recursion).  Every role evaluates the pairs (a, b) whose link a it owns and keeps only the wrench
-// on a (on both, if b is its own too); the two sides of a pair run the same arithmetic on the same operands (segment
-// order fixed by the link numbers), so the two forces are equal and opposite to the bit.  One contact per pair at the
-// closest points of the two segments, force along their connection at the midpoint of the overlap:
+// and break the O(n) recursion).  Every pair is TESTED once, by the role whose list holds it (broad phase on the bounding
+// spheres, narrow phase capsule against capsule); the pairs found in contact are published as one hit word per role, and
+// each of the two roles that own a link of such a pair evaluates the contact for ITS link -- the same arithmetic on the
+// same operands (segment order fixed by the link numbers), so the two forces are equal and opposite to the bit.  One
+// contact per pair at the closest points of the two segments, force along their connection at the midpoint of the overlap:
 // f = k pen - d vn (damping while approaching only), no friction.
 
 // world end points of link `link`'s capsule -> C[slot][P xyz, Q xyz] (stride 32), its midpoint (centre of the bounding
@@ -232,17 +260,17 @@ __device__ __forceinline__ void publish_capsule(const MT& M, int link, const M3&
     c[0] = P.x; c[32] = P.y; c[64] = P.z; c[96] = Q.x; c[128] = Q.y; c[160] = Q.z;
     ctr[0] = 0.5f * (P.x + Q.x); ctr[32] = 0.5f * (P.y + Q.y); ctr[64] = 0.5f * (P.z + Q.z);
 }
-// Closest points of the capsule axes of links lo < hi (Ericson, Real-Time Collision Detection 5.1.9), branch-free.
-// Returns the squared distance; c1 on lo's axis, c2 on hi's.
-template <class MT>
-__device__ __forceinline__ float capsule_closest(const MT& M, const float* C, int lo, int hi, V3& c1, V3& c2) {
-    const float* s1 = C + (int)M.cap_idx[lo] * 6 * 32;
-    const float* s2 = C + (int)M.cap_idx[hi] * 6 * 32;
+// Closest points of the capsule axes of a pair, links in canonical order lo < hi (Ericson, Real-Time Collision Detection
+// 5.1.9), branch-free.  `nar` = the pair's narrow-phase record (RoleModel::sc_nar), Cb = this lane's column of the
+// published end points.  Returns the squared distance; c1 on lo's axis, c2 on hi's.
+__device__ __forceinline__ float capsule_closest(const char* Cb, uint4 nar, V3& c1, V3& c2) {
+    const float* s1 = reinterpret_cast<const float*>(Cb + (nar.x >> 16));
+    const float* s2 = reinterpret_cast<const float*>(Cb + (nar.x & 0xffffu));
     const V3 P1 = {s1[0], s1[32], s1[64]}, Q1 = {s1[96], s1[128], s1[160]};
     const V3 P2 = {s2[0], s2[32], s2[64]}, Q2 = {s2[96], s2[128], s2[160]};
     const V3 d1 = Q1 - P1, d2 = Q2 - P2, r = P1 - P2;
     const float a = dot(d1, d1), e = dot(d2, d2), f = dot(d2, r), c = dot(d1, r), b = dot(d1, d2);
-    const float ia = M.cap_il2[lo], ie = M.cap_il2[hi];  // 1 / length^2: model constants (0: a sphere, a zero-length capsule)
+    const float ia = __uint_as_float(nar.y), ie = __uint_as_float(nar.z);  // 1 / length^2: 0 for a sphere (zero-length axis)
     const float den = a * e - b * b;
     float sp = den > 1e-9f * a * e ? __saturatef((b * f - c * e) / den) : 0.f;
     float tp = (b * sp + f) * ie;
@@ -254,15 +282,15 @@ __device__ __forceinline__ float capsule_closest(const MT& M, const float* C, in
     const V3 d = c1 - c2;
     return dot(d, d);
 }
-// The contact of the pair (a, b): force on link a (and, BOTH: the opposite one on link b, which this role owns too)
-// about O -> W (first touch stores, later ones add).
+// The contact of the pair (a, b), list entry `nar`: force on link a (and, BOTH: the opposite one on link b, which this
+// role owns too) about O -> W (first touch stores, later ones add).
 template <class MT, int NW>
-__device__ __forceinline__ void capsule_contact(const MT& M, const float* C, const float* G0, int a, int b, float dt,
-                                                bool both, float (&W)[NW][6], unsigned& wmask) {
+__device__ __forceinline__ void capsule_contact(const MT& M, const char* Cb, const float* G0, uint4 nar, int a, int b,
+                                                float dt, bool both, float (&W)[NW][6], unsigned& wmask) {
     const bool a_lo = a < b;
     const int lo = a_lo ? a : b, hi = a_lo ? b : a;
     V3 clo, chi;
-    const float d2 = capsule_closest(M, C, lo, hi, clo, chi);
+    const float d2 = capsule_closest(Cb, nar, clo, chi);
     const float rlo_ = M.cap_r[lo], rhi_ = M.cap_r[hi];
     if (!(d2 > 1e-18f)) return;
     const float dist = sqrtf(d2), pen = (rlo_ + rhi_) - dist;
@@ -280,18 +308,27 @@ __device__ __forceinline__ void capsule_contact(const MT& M, const float* C, con
     const V3 F = (a_lo ? f : -f) * n;  // on link a
     const V3 tq = cross(pc, F);
     const float wr[6] = {tq.x, tq.y, tq.z, F.x, F.y, F.z};
+    // (W lives in local memory, and the L1 left beside 220 KB of shared memory is small: a first touch must not load)
     {
         const int w = M.w_idx[a];
-        const bool seen = (wmask >> w) & 1u;
+        if ((wmask >> w) & 1u) {
 #pragma unroll
-        for (int k = 0; k < 6; ++k) W[w][k] = (seen ? W[w][k] : 0.f) + wr[k];
+            for (int k = 0; k < 6; ++k) W[w][k] += wr[k];
+        } else {
+#pragma unroll
+            for (int k = 0; k < 6; ++k) W[w][k] = wr[k];
+        }
         wmask |= 1u << w;
     }
     if (both) {
         const int w = M.w_idx[b];
-        const bool seen = (wmask >> w) & 1u;
+        if ((wmask >> w) & 1u) {
 #pragma unroll
-        for (int k = 0; k < 6; ++k) W[w][k] = (seen ? W[w][k] : 0.f) - wr[k];
+            for (int k = 0; k < 6; ++k) W[w][k] -= wr[k];
+        } else {
+#pragma unroll
+            for (int k = 0; k < 6; ++k) W[w][k] = -wr[k];
+        }
         wmask |= 1u << w;
     }
 }
@@ -312,7 +349,7 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
     constexpr int GT = NR * 32;  // threads of a group
     const int tid = threadIdx.x;
     const int grp = tid / GT, role = (tid / 32) % NR, lane = tid & 31;
-    const int bar_id = 1 + grp;
+    const int bar_id = 1 + grp * 3;  // + 1, + 2: the group's hand-over barriers
     const int D = A.D;
     const long long e0 = (long long)blockIdx.x * EPC;
     const int cnt = (int)((A.n - e0) < (long long)EPC ? (A.n - e0) : (long long)EPC);
@@ -506,8 +543,13 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
     V6 vkeep = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}}, bkeep = vkeep;  // velocity, velocity-product sum at the tip of the chain swept last
     int keep_last = -1;
 
+#ifdef OIGE_STAMPS
+    int stamp_i = 0;
+#endif
+    STAMP(1);
     for (int step = 0; step < A.substeps; ++step) {
         const bool last = (step == A.substeps - 1);
+        STAMP(10);
         float root_z = 0.f;
         S6 carryI;
         V6 carryP;
@@ -520,57 +562,102 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
         for (int sg = 0; sg < nseg; ++sg) {
             const int kind = M.seg_kind[role][sg], sflag = M.seg_flag[role][sg];
             const int first = M.seg_first[role][sg], lastl = M.seg_last[role][sg];
-            if (sflag & kSegBarBefore) group_barrier(bar_id, GT);
+            STAMP(20 + sg);
+            if (sflag & kSegBarBefore) { group_barrier(bar_id, GT); STAMP(30 + sg); }
             if (SC && kind == kSegPairs) {
-                // ---- pair phase: broad phase on the links' bounding spheres, narrow phase sphere by sphere -------
-                // (a pair whose links both belong to this role is listed once, flagged in bit 7 of sc_b)
-                // Phase 1 (warp-uniform loop over the role's list): bounding-sphere test, one candidate bit per pair.
-                // Phase 2: every lane pops ITS OWN next candidate and runs the sphere-by-sphere test on it -- lanes work on
-                // different pairs at the same time (the scratch is laid out [float][lane], so lane-dependent indices stay
-                // conflict-free), the warp iterates max-over-lanes times instead of once per pair any lane flagged.
-                const int k0 = M.sc_off[role], k1 = M.sc_off[role + 1];
-                unsigned long long cand = 0ull;
+                // ---- pair phase (every link pair is in exactly one role's list) ---------------------------------
+                // 1. broad phase, warp-uniform loop over the role's list, grouped by the first link: bounding spheres
+                //    about the capsule midpoints, one candidate bit per entry.
+                // 2. narrow phase: every lane pops ITS OWN next candidate and runs the capsule-capsule distance on it
+                //    -- lanes work on different pairs at the same time (the scratch is laid out [float][lane], so
+                //    lane-dependent indices stay conflict-free); the warp iterates max-over-lanes times.  The pairs in
+                //    contact go to the role's hit word xH[role].                                    | barrier
+                // 3. contacts (rare, lane-divergent): the role's own hits, then the hits of the other roles' entries
+                //    whose partner link is this role's (sc_to) -- the wrench on the OWN link is kept.
+                const int k0 = M.sc_off[role];
+                const char* const Gb = reinterpret_cast<const char*>(G0);
+                const char* const Cb = reinterpret_cast<const char*>(xC);
+                unsigned cand = 0u;
                 {
-                    int prev_a = -1;
-                    V3 ma = {0.f, 0.f, 0.f};
-                    float ra = 0.f;
-                    (void)ra;
-                    for (int k = k0; k < k1; ++k) {
-                        const uint2 rec = M.sc_rec[k];
-                        const int oa = M.sc_ctra[k];
-                        if (oa != prev_a) {
-                            const float* c = G0 + oa * 32;
-                            ma = {c[0], c[32], c[64]};
-                            prev_a = oa;
+                    // four entries per trip, loads first: the tests are independent, their latencies overlap (a trip may
+                    // run into the next role's entries or the zero fill; those bits are masked off)
+                    const int nk = M.sc_off[role + 1] - k0;
+                    for (int k = 0; k < nk; k += 4) {
+                        uint2 rec[4];
+                        float ax[4], ay[4], az[4], bx[4], by[4], bz[4];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) rec[u] = M.sc_brd[k0 + k + u];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const float* ca = reinterpret_cast<const float*>(Gb + (rec[u].x >> 16));
+                            const float* cb = reinterpret_cast<const float*>(Gb + (rec[u].x & 0xffffu));
+                            ax[u] = ca[0]; ay[u] = ca[32]; az[u] = ca[64];
+                            bx[u] = cb[0]; by[u] = cb[32]; bz[u] = cb[64];
                         }
-                        const float* c = G0 + (int)rec.x * 32;
-                        const V3 d = {ma.x - c[0], ma.y - c[32], ma.z - c[64]};
-                        if (dot(d, d) < __uint_as_float(rec.y)) cand |= 1ull << (k - k0);
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const float dx = ax[u] - bx[u], dy = ay[u] - by[u], dz = az[u] - bz[u];
+                            if (fmaf(dz, dz, fmaf(dy, dy, dx * dx)) < __uint_as_float(rec[u].y)) cand |= 1u << (k + u);
+                        }
+                    }
+                    cand &= nk >= 32 ? 0xffffffffu : (1u << nk) - 1u;
+                }
+                STAMP(40);
+                // two candidates per trip (the two distance computations are independent dependency chains)
+                unsigned hits = 0u;
+                while (__any_sync(0xffffffffu, cand != 0u)) {
+                    if (cand != 0u) {
+                        const int kb1 = __ffs((int)cand) - 1;
+                        cand &= cand - 1u;
+                        const int kb2 = cand != 0u ? __ffs((int)cand) - 1 : kb1;
+                        cand &= cand - 1u;  // (0 stays 0)
+                        const uint4 nar1 = M.sc_nar[k0 + kb1], nar2 = M.sc_nar[k0 + kb2];
+                        V3 c1, c2, c3, c4;
+                        const float da = capsule_closest(Cb, nar1, c1, c2), db = capsule_closest(Cb, nar2, c3, c4);
+                        if (da < __uint_as_float(nar1.w)) hits |= 1u << kb1;
+                        if (db < __uint_as_float(nar2.w)) hits |= 1u << kb2;
                     }
                 }
-                // Phase 2: every lane pops its own candidates: capsule-capsule distance against the sum of the radii
-                unsigned long long hits = 0ull;
-                while (__any_sync(0xffffffffu, cand != 0ull)) {
-                    if (cand != 0ull) {
-                        const int kb = __ffsll((long long)cand) - 1;
-                        cand &= cand - 1ull;
-                        const int a = M.sc_a[k0 + kb], b = M.sc_b[k0 + kb] & 127;
-                        V3 c1, c2;
-                        const float d2 = capsule_closest(M, xC, a < b ? a : b, a < b ? b : a, c1, c2);
-                        const float rr = M.cap_r[a] + M.cap_r[b];
-                        if (d2 < rr * rr) hits |= 1ull << kb;
+                G0[(M.oH + role) * 32] = __uint_as_float(hits);
+                STAMP(41);
+                group_barrier(bar_id, GT);
+                STAMP(42);
+                // one pop loop over the own hits and the other roles' hits on this role's links (the warp iterates
+                // max-over-lanes of the lane's TOTAL, not once per source list)
+                unsigned hsrc[NR];
+                hsrc[0] = hits;
+#pragma unroll
+                for (int dr = 1; dr < NR; ++dr) {
+                    const int src = role + dr < NR ? role + dr : role + dr - NR;
+                    hsrc[dr] = __float_as_uint(G0[(M.oH + src) * 32]) & M.sc_to[src][role];
+                }
+                for (;;) {
+                    unsigned any = 0u;
+#pragma unroll
+                    for (int dr = 0; dr < NR; ++dr) any |= hsrc[dr];
+                    if (!__any_sync(0xffffffffu, any != 0u)) break;
+                    if (any != 0u) {
+                        int dsel = 0;
+#pragma unroll
+                        for (int dr = NR - 1; dr >= 1; --dr) dsel = hsrc[dr] != 0u ? dr : dsel;
+                        dsel = hsrc[0] != 0u ? 0 : dsel;
+                        unsigned h = hsrc[0];
+#pragma unroll
+                        for (int dr = 1; dr < NR; ++dr) h = dsel == dr ? hsrc[dr] : h;
+                        const int src = role + dsel < NR ? role + dsel : role + dsel - NR;
+                        const int k = M.sc_off[src] + __ffs((int)h) - 1;
+                        h &= h - 1u;
+#pragma unroll
+                        for (int dr = 0; dr < NR; ++dr) hsrc[dr] = dsel == dr ? h : hsrc[dr];
+                        const int la = M.sc_a[k], lb = M.sc_b[k];
+                        // (a foreign entry: this role's link is the entry's partner b)
+                        capsule_contact(M, Cb, G0, M.sc_nar[k], dsel == 0 ? la : (lb & 127), dsel == 0 ? (lb & 127) : la, dt,
+                                        dsel == 0 && (lb & 128) != 0, W, wmask);
                     }
                 }
-                // Phase 3: the pairs in contact (rare, lane-divergent): all lanes pop their own together
-                while (__any_sync(0xffffffffu, hits != 0ull)) {
-                    if (hits != 0ull) {
-                        const int k = k0 + __ffsll((long long)hits) - 1;
-                        hits &= hits - 1ull;
-                        const int bb = M.sc_b[k];
-                        capsule_contact(M, xC, G0, M.sc_a[k], bb & 127, dt, (bb & 128) != 0, W, wmask);
-                    }
-                }
+                STAMP(43);
                 if (sflag & kSegBarAfter) group_barrier(bar_id, GT);
+                STAMP(44);
                 continue;
             }
             if (kind != kSegTrunkKin) root_z = xM[0];
@@ -633,6 +720,7 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
                 }
                 v = c.v; b = c.b;  // of the tip: walked back up with the inertia sweep
             }
+            STAMP(50 + sg);
             // ---- articulated-inertia sweep: child -> parent, I^a / p^a carried in registers ---------------------
             if (do_up) {
                 const bool trunk_up = kind == kSegTrunkUp;
@@ -694,6 +782,8 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
                         for (int j = 0; j < 6; ++j) pA.a[j] += carryP.a[j];
                     }
                     if (trunk_up) {
+                        // the chains (and own inertias) handed over at this trunk link: wait for THEIR roles only
+                        if (M.hb_id[i]) group_barrier(bar_id + M.hb_id[i], M.hb_cnt[i]);
                         for (int h = M.ts_begin[i]; h < M.ts_begin[i + 1]; ++h) {
                             const float* hs = xI + M.ts_slot[h] * kHand * 32;
 #pragma unroll
@@ -727,7 +817,13 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
                     if (chain && last && (sflag & kSegSensor)) { vatt = v; batt = b; }  // = the attach link's v, b
                 }
             }
-            if (sflag & kSegBarAfter) group_barrier(bar_id, GT);
+            STAMP(60 + sg);
+            if (sflag & kSegArrive) {
+                const int t = M.seg_att[role][sg];
+                __threadfence_block();
+                group_arrive(bar_id + M.hb_id[t], M.hb_cnt[t]);
+            }
+            if (sflag & kSegBarAfter) { group_barrier(bar_id, GT); STAMP(70 + sg); }
         }
 
         // ---- S2b (role 0): root solve, trunk accelerations root -> tip, trunk joints and root integrated ----------
@@ -761,7 +857,9 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
             }
             if (!fixed_base) integrate_root(M, a0, dt, rpos, rquat, rvel);
         }
+        STAMP(80);
         group_barrier(bar_id, GT);  // A
+        STAMP(81);
 
         // ---- S3: accelerations down the own chains, joint integration, foot sensors ---------------------------
         for (int sg = 0; sg < nseg; ++sg) {
@@ -818,6 +916,7 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
         }
     }
 
+    STAMP(90);
     // ================= non-finite guard (agreed across the roles of an env) ================================
     bool bad = false;
 #pragma unroll
@@ -1034,6 +1133,7 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
             _Pragma("unroll 1") for (int i = tid; i < cnt * 3; i += NT) { A.up[e0 * 3 + i] = o_up[i]; A.head[e0 * 3 + i] = o_head[i]; }
         }
     }
+    STAMP(99);
     if (tid == 0) {
         if (A.epi && A.stats != nullptr) {
             double r = 0.0, d = 0.0, l = 0.0;
