@@ -5,15 +5,22 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--envs-per-gpu E]
 
 A "step" is one VecEnvRLGames.step of every environment: clamp actions, device-side reset of
-flagged envs (K3), controlFrequencyInv=2 articulation substeps (K2), fused obs/reward/termination
-(K1).  One process per GPU; environments are partitioned by index, no per-step collective; NCCL
-all-reduces the episode statistics every 16 steps on a side stream.
+flagged envs, controlFrequencyInv=2 articulation substeps (self-collision on, as in the reference's
+Humanoid.yaml), observations / reward / termination -- ONE launch of the whole-step kernel K2-F
+(`env_step_role_kernel`) per step.  One process per GPU; environments are partitioned by index, no
+per-step collective; NCCL all-reduces the episode statistics every 16 steps on a side stream.
 
 Printed JSON (rank 0, one line): the driver contract keys plus
-  roofline      K1 at 1,048,576 envs (772 MB per launch > 126 MB L2), algorithmic bytes / CUDA-event time
+  roofline      the dominant kernel (K2-F, the whole step) against the HBM roofline, measured live; it is issue /
+                latency-bound, so `issue` (warp-instructions per launch from the committed ncu capture / live time
+                against the SMs' issue peak) is the figure that explains it
+  roofline_k1   the stand-alone obs/reward pass K1 at 1,048,576 envs (772 MB per launch > 126 MB L2) and at the
+                benchmark's own env count
+  sustained     the same CUDA-graph step looped for >= 2 s with its own clock record (a loaded-GPU twin of `value`)
+  no_self_collision  `value`'s twin with enable_self_collisions off (the round-1 mechanical system)
   cpu_baseline  the oracle (torch CPU obs/reward + float64 OpenMP dynamics) on a bounded sample, rank 0, N=1
   e2e           the same step through `step_host` (pinned HOST buffers, H2D + D2H inside the timed region)
-  step_breakdown per-kernel device time of one step (hook-by-hook path), for the kernel-share check
+  step_breakdown per-kernel device time of the staged (hook-by-hook) K3 / K2 / K1 path, for reference
 `--impl reference` times the CPU oracle port alone (PhysX / Isaac Sim are not installable: see DESIGN.md).
 """
 import argparse
@@ -36,6 +43,40 @@ ROOFLINE_ENVS = 1 << 20
 # dram__bytes_read.sum + dram__bytes_write.sum of one K1 launch at 1,048,576 envs, from the ncu --set full
 # capture summarised in profiles/r1_ncu_full.txt (390.1 MB + 367.4 MB); algorithmic bytes are 809.5 MB
 K1_TRAFFIC_BYTES_1M = 757.6e6
+K1_TRAFFIC_SOURCE = "profiles/r1_ncu_full.txt"
+# The dominant kernel, K2-F at 16384 Humanoid envs with self-collision: figures of the committed ncu --set full capture
+# (one launch = one whole env step).  Read from profiles/ at run time when the file travels with the repo.
+K2F_NCU_FILE = "profiles/r2_ncu_k2f_sc_16384.txt"
+K2F_NCU_DEFAULTS = {"warp_inst": 40.0e6, "issue_util_pct": 42.7, "dram_bytes": 10.3e6, "time_us": 102.6}
+
+
+def read_k2f_ncu():
+    """smsp__inst_executed.sum, issue utilisation, DRAM bytes and duration of the committed K2-F capture."""
+    out = dict(K2F_NCU_DEFAULTS)
+    out["source"] = "bench.py constants"
+    path = os.path.join(ROOT, K2F_NCU_FILE)
+    keys = {"smsp__inst_executed.sum": "warp_inst", "smsp__issue_active.avg.pct_of_peak_sustained_active": "issue_util_pct",
+            "gpu__time_duration.sum": "time_us"}
+    try:
+        rd = wr = None
+        with open(path) as f:
+            for ln in f:
+                p = ln.split()
+                if len(p) < 2:
+                    continue
+                scale = {"Mbyte": 1e6, "Kbyte": 1e3, "Gbyte": 1e9, "byte": 1.0}.get(p[2] if len(p) > 2 else "", 1.0)
+                if p[0] in keys:
+                    out[keys[p[0]]] = float(p[1].replace(",", ""))
+                elif p[0] == "dram__bytes_read.sum":
+                    rd = float(p[1].replace(",", "")) * scale
+                elif p[0] == "dram__bytes_write.sum":
+                    wr = float(p[1].replace(",", "")) * scale
+        if rd is not None and wr is not None:
+            out["dram_bytes"] = rd + wr
+        out["source"] = K2F_NCU_FILE
+    except Exception:
+        pass
+    return out
 
 
 def read_peaks():
@@ -57,6 +98,7 @@ class ClockSampler:
     def __init__(self, index: int):
         self.index, self.samples, self._stop, self._t = index, [], threading.Event(), None
         self.sm_max = None
+        self.interval = 0.002  # s between NVML samples (raised around the host-buffer loop: one polling thread per rank)
         self._nvml = None
         try:
             import pynvml
@@ -94,7 +136,7 @@ class ClockSampler:
                 self._sample_nvml() if self._nvml is not None else self._sample_smi()
             except Exception:
                 pass
-            self._stop.wait(0.002 if self._nvml is not None else 0.1)
+            self._stop.wait(self.interval if self._nvml is not None else max(self.interval, 0.1))
 
     def __enter__(self):
         self._t = threading.Thread(target=self._run, daemon=True)
@@ -202,8 +244,9 @@ def run_reference_arm(args):
 # ------------------------------------------------------------------------------------------------
 # our arm
 # ------------------------------------------------------------------------------------------------
-def k1_roofline(torch, device, n_envs, iters=20, warmup=5):
-    """Achieved bandwidth of K1 at n_envs (state + outputs > L2) via CUDA events on the launch stream."""
+def k1_roofline(torch, device, n_envs, iters=20, warmup=5, flush=None):
+    """Achieved bandwidth of K1 at n_envs via CUDA events on the launch stream (state + outputs > L2 at 1 Mi envs;
+    at smaller counts `flush` -- a buffer larger than L2 -- is rewritten between launches, outside the event pairs)."""
     import ctypes as C
 
     from omniisaacgymenvs_b200 import _lib
@@ -234,6 +277,8 @@ def k1_roofline(torch, device, n_envs, iters=20, warmup=5):
     torch.cuda.synchronize(device)
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(iters)]
     for a, b in evs:
+        if flush is not None:
+            flush.zero_()
         a.record(); launch(); b.record()
     torch.cuda.synchronize(device)
     ms = [a.elapsed_time(b) for a, b in evs]
@@ -272,6 +317,19 @@ def step_breakdown(torch, env, task, actions, iters=10):
         acc["articulation_ms"] += ev[1].elapsed_time(ev[2]) / iters
         acc["obs_reward_ms"] += ev[2].elapsed_time(ev[3]) / iters
     return acc
+
+
+def timed_steps(torch, env, acts, flush, K, device):
+    """K steps, per-step CUDA-event pairs, L2 flushed between steps outside the pairs; returns total device ms."""
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    for i in range(K):
+        flush.zero_()
+        a, b = evs[i]
+        a.record()
+        env.step(acts[i % len(acts)])
+        b.record()
+    torch.cuda.synchronize(device)
+    return sum(a.elapsed_time(b) for a, b in evs)
 
 
 def run_ours(args):
@@ -367,41 +425,109 @@ def run_ours(args):
             env.enable_cuda_graph_host(a, obs_h, rew_h, rst_h)
     for i in range(3):
         env.step_host(a_host[i % 4], obs_h, rew_h, rst_h)
+    clocks.interval = 0.1  # one NVML polling thread per rank: keep it off the host cores while the copies are timed
     barrier()
     t0 = time.perf_counter()
     for i in range(K):
         env.step_host(a_host[i % 4], obs_h, rew_h, rst_h)
         torch.cuda.synchronize(device)  # the caller reads obs/rew/reset every step
-    if dist is not None:
-        dist.barrier()
-    e2e_s = time.perf_counter() - t0
-    clocks.__exit__()
+    e2e_s = time.perf_counter() - t0  # this rank's own loop; the slowest rank sets the job's rate (max over ranks)
     e2e_value = world * n * K / max_over_ranks(e2e_s, device)
+    clocks.interval = 0.002
     h2d = n * D * 4
     d2h = n * task.num_observations * 4 + n * 4 + n * 8
+
+    # ---- sustained: the same CUDA-graph step looped for >= 2 s (hot L2, no flush), with its own clock record ----
+    env.disable_cuda_graph_host()
+    if not args.no_cuda_graph:
+        env.enable_cuda_graph()
+    for _ in range(W):
+        env.step(acts[0])
+    barrier()
+    sus_lo = clocks.mark()
+    s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sus_steps, t0 = 0, time.perf_counter()
+    s0.record()
+    while time.perf_counter() - t0 < args.sustained_s:
+        for i in range(256):
+            env.step(acts[i % len(acts)])
+        sus_steps += 256
+        torch.cuda.synchronize(device)  # bounds the launch queue; ~25 ms of work per sync
+    s1.record()
+    torch.cuda.synchronize(device)
+    sus_ms = max_over_ranks(s0.elapsed_time(s1), device)
+    sus_hi = clocks.mark()
+    sustained = {"value": world * n * sus_steps / (sus_ms / 1e3), "unit": "env-steps/s", "steps": sus_steps,
+                 "seconds": sus_ms / 1e3, "us_per_step": 1e3 * sus_ms / max(sus_steps, 1), "l2": "hot (no flush)",
+                 "clocks": clocks.summary(sus_lo, sus_hi)}
+    clocks.__exit__()
 
     line = None
     if rank == 0:
         breakdown = step_breakdown(torch, env, task, acts[0])
         del env, task
         torch.cuda.empty_cache()
+        # `value`'s twin without self-collision (the mechanical system of round 1)
+        nosc = None
+        if not args.no_extras:
+            with contextlib.redirect_stdout(sys.stderr):
+                env2, task2 = make_env(ROBOT, num_envs=n, device_id=local_rank, seed=42, env_id_offset=rank * n,
+                                       global_num_envs=world * n,
+                                       overrides={"task.sim.Humanoid.enable_self_collisions": False})
+                env2.reset()
+                if not args.no_cuda_graph:
+                    env2.enable_cuda_graph()
+            for _ in range(W):
+                env2.step(acts[0])
+            torch.cuda.synchronize(device)
+            ms2 = timed_steps(torch, env2, acts, flush, 20, device)
+            nosc = {"value": n * 20 / (ms2 / 1e3), "unit": "env-steps/s (this rank)", "ms_per_step": ms2 / 20, "steps": 20}
+            del env2, task2
+            torch.cuda.empty_cache()
         peak, peak_src = read_peaks()
-        roof = None
-        cpu = None
-        if world == 1 or True:
+        ncu = read_k2f_ncu()
+        step_s = ms_per_step * 1e-3
+        sm_mhz = clocks.summary(clk_lo, clk_hi)["sm_mhz"] or clocks.sm_max or 1965.0
+        n_sm = torch.cuda.get_device_properties(device).multi_processor_count
+        issue_peak = n_sm * 4 * sm_mhz * 1e6  # one warp-instruction per scheduler per cycle, 4 schedulers per SM
+        scale = n / 16384.0  # the capture is of a 16384-env launch
+        achieved = STEP_BYTES[ROBOT] * n / step_s / 1e9
+        roof = {"bound": "hbm", "kernel": "env_step_role_kernel<6,3,false,128,1,true,true> (K2-F: the whole env step in one launch)",
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": ncu["dram_bytes"] * scale, "traffic_source": ncu["source"], "peak_source": peak_src,
+                "envs": n, "bytes_per_env": STEP_BYTES[ROBOT], "avg_ms": ms_per_step,
+                "limiter": "issue / dependency latency, not HBM: see `issue`",
+                "note": "algorithmic bytes = state in + state, observations, reward, flags out (944 B per env-step) over the "
+                        "device time of the step; the kernel keeps everything else on chip (ncu DRAM traffic ~ the "
+                        "algorithmic bytes, no spill traffic)"}
+        issue = {"warp_inst_per_launch": ncu["warp_inst"] * scale, "source": ncu["source"],
+                 "achieved_ginst_s": ncu["warp_inst"] * scale / step_s / 1e9, "peak_ginst_s": issue_peak / 1e9,
+                 "frac": ncu["warp_inst"] * scale / step_s / issue_peak, "ncu_issue_util_pct": ncu["issue_util_pct"],
+                 "ncu_time_us": ncu["time_us"], "sm_mhz": sm_mhz,
+                 "note": "warp-instructions of the committed ncu capture / live device time of the step, against "
+                         "SMs x 4 schedulers x SM clock; the step time includes the graph's hand-off copies"}
+        roof_k1 = None
+        if not args.no_extras:
             k1_ms, k1_best = k1_roofline(torch, device, ROOFLINE_ENVS)
-            achieved = K1_BYTES[ROBOT] * ROOFLINE_ENVS / (k1_ms * 1e-3) / 1e9
-            roof = {"bound": "hbm", "kernel": "obs_reward_reset_kernel<21,2,32>", "achieved": achieved, "peak": peak,
-                    "unit": "GB/s", "frac": achieved / peak, "traffic": K1_TRAFFIC_BYTES_1M if ROOFLINE_ENVS == (1 << 20) else None, "peak_source": peak_src,
-                    "envs": ROOFLINE_ENVS, "bytes_per_env": K1_BYTES[ROBOT], "avg_ms": k1_ms, "best_ms": k1_best,
-                    "note": "K1 timed alone at 1,048,576 envs (772 MB/launch > L2); the full step is dominated by "
-                            "K2 which is issue/latency-bound (no HBM or tensor roofline applies), see step_breakdown"}
+            a1 = K1_BYTES[ROBOT] * ROOFLINE_ENVS / (k1_ms * 1e-3) / 1e9
+            k1s_ms, k1s_best = k1_roofline(torch, device, n, flush=flush)
+            a2 = K1_BYTES[ROBOT] * n / (k1s_ms * 1e-3) / 1e9
+            roof_k1 = {"bound": "hbm", "kernel": "obs_reward_reset_kernel<21,2,32> (stand-alone obs/reward/reset pass; inside "
+                                                  "the fused step its arithmetic runs in K2-F's epilogue)",
+                       "achieved": a1, "peak": peak, "unit": "GB/s", "frac": a1 / peak, "envs": ROOFLINE_ENVS,
+                       "bytes_per_env": K1_BYTES[ROBOT], "avg_ms": k1_ms, "best_ms": k1_best,
+                       "traffic": K1_TRAFFIC_BYTES_1M, "traffic_source": K1_TRAFFIC_SOURCE,
+                       "at_bench_envs": {"envs": n, "achieved": a2, "frac": a2 / peak, "avg_ms": k1s_ms, "best_ms": k1s_best,
+                                         "l2": "flushed between launches"}}
+        cpu = None
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
             rate, cms = cpu_env_step_rate(args.cpu_sample_envs, 30, 2, threads)
+            rate1, _ = cpu_env_step_rate(2048, 5, 1, 1)
             cpu = {"value": rate, "unit": "env-steps/s", "cores": threads, "kind": "port",
+                   "value_1thread": rate1, "sample_1thread": "2048 envs x 5 full env steps, 1 thread",
                    "sample": f"{args.cpu_sample_envs} envs x 30 full env steps on the host cores "
-                             "(float64 OpenMP dynamics oracle, 2 substeps, + torch CPU obs/reward/reset oracle)"}
+                             "(float64 OpenMP dynamics oracle incl. self-collision, 2 substeps, + torch CPU obs/reward/reset oracle)"}
         line = {
             "metric": "humanoid_env_steps_per_sec", "value": value, "unit": "env-steps/s", "n_gpus": world,
             "steps": K, "warmup": W, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
@@ -409,13 +535,19 @@ def run_ours(args):
             "config": {"workload": f"Humanoid full env step (K3 reset + 2x K2 articulation substeps + K1 obs/reward/reset), "
                                    f"{n} envs/GPU (BASELINE.json configs[2])",
                        "envs_per_gpu": n, "global_envs": world * n, "parallelism": f"env-index sharding x{world}",
+                       "kernels": "one launch per step: K2-F env_step_role_kernel (reset + clamp, 2 substeps, obs/reward/done fused)",
+                       "self_collision": True,
                        "l2": "flushed between steps (256 MiB memset outside the per-step CUDA-event pairs)",
                        "actions": "uniform random policy, device-resident",
-                       "cuda_graph": not args.no_cuda_graph},
+                       "cuda_graph": not args.no_cuda_graph,
+                       "physics_parity": "vs PhysX UNPINNED: PhysX 5 is closed and absent; the articulation step is this repo's "
+                                         "own solver, checked against its float64 oracle and model-level invariants (DESIGN.md section 4)"},
             "clocks": clocks.summary(clk_lo, clk_hi),
-            "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+            "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "timing": "per-rank wall clock around K host-buffer steps (one stream sync per step), max over ranks"},
             "gpu_launches": int(launches),
-            "roofline": roof, "cpu_baseline": cpu, "step_breakdown": breakdown,
+            "roofline": roof, "issue": issue, "roofline_k1": roof_k1, "sustained": sustained, "no_self_collision": nosc,
+            "cpu_baseline": cpu, "step_breakdown": breakdown,
             "wall_s_timed_region": t_wall,
             "episode_stats": episode_stats,
         }
@@ -437,6 +569,8 @@ def main():
     ap.add_argument("--cpu-sample-envs", type=int, default=ENVS_PER_GPU)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-cuda-graph", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the K1 roofline and no-self-collision side measurements")
+    ap.add_argument("--sustained-s", type=float, default=2.0, help="length of the sustained (loaded-GPU) loop")
     args = ap.parse_args()
     # stdout carries exactly ONE JSON line: libraries that write to the C-level stdout (NCCL prints its version
     # banner there) are sent to stderr by pointing fd 1 at fd 2 and giving Python's sys.stdout the original fd

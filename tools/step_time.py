@@ -1,14 +1,17 @@
-"""Whole-step timing (GPU box): eager vs CUDA-graph VecEnvRLGames.step at several env counts."""
+"""Whole-step timing (GPU box): eager vs CUDA-graph VecEnvRLGames.step at several env counts.
+argv[1] = "nosc": Humanoid with enable_self_collisions off (the reference default is on, Humanoid.yaml:80)."""
 import os, sys, statistics, io, contextlib
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
 import torch
 from omniisaacgymenvs_b200.utils.task_util import make_env
-for robot in ("Humanoid", "Ant"):
+NOSC = len(sys.argv) > 1 and sys.argv[1] == "nosc"
+for robot in (("Humanoid",) if NOSC else ("Humanoid", "Ant")):
     for n in (1024, 4096, 16384, 65536):
         out = [f"{robot} n={n:6d}"]
         for graph in (False, True):
             with contextlib.redirect_stdout(io.StringIO()):
-                env, task = make_env(robot, num_envs=n); env.reset()
+                env, task = make_env(robot, num_envs=n, overrides={"task.sim.Humanoid.enable_self_collisions": False} if NOSC else None)
+                env.reset()
             if graph: env.enable_cuda_graph()
             dev = torch.device(task.device)
             acts = [torch.rand(n, task.num_actions, device=dev) * 2 - 1 for _ in range(8)]
