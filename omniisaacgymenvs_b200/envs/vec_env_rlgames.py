@@ -112,12 +112,16 @@ class VecEnvRLGames(VecEnvBase):
             task._reset_counter += 1  # host mirror of the device-side counter
             self.sim_frame_count += task.control_frequency_inv
             self._world.current_time_step_index += task.control_frequency_inv
+            if hasattr(task, "poll_episode_extras"):
+                task.poll_episode_extras()
             return self._g_out[0], self._g_out[1], self._g_out[2], task.extras.copy()
         if getattr(task, "supports_fused_step", False) and task.fused_step_enabled():
             actions = actions.to(task.device)
             self._fused_step_with_noise(actions, self._world.get_physics_dt())
             self.sim_frame_count += task.control_frequency_inv
             self._world.current_time_step_index += task.control_frequency_inv
+            if hasattr(task, "poll_episode_extras"):
+                task.poll_episode_extras()
             self._obs, self._rew, self._resets, self._extras = task.obs_buf, task.rew_buf, task.reset_buf, task.extras
         else:
             actions = torch.clamp(actions, -task.clip_actions, task.clip_actions).to(task.device).clone()

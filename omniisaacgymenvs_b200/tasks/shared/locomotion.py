@@ -294,6 +294,37 @@ class LocomotionTask(RLTask):
             int(self.control_frequency_inv), float(physics_dt), self._stream())
         _lib.check(rc, "oige_env_step_host_f32")
 
+    def poll_episode_extras(self, every: int = 16) -> None:
+        """Puts the episode statistics where the reference's observer looks (``infos["episode"]``,
+        utils/rlgames/rlgames_utils.py:51-62,67-91) WITHOUT a per-step sync: every ``every`` steps the striped
+        accumulators are summed on the device and copied to pinned host memory asynchronously; the copy enqueued
+        ``every`` steps earlier has long arrived by then and is published as the window's mean return / mean length /
+        episode count.  ``extras["episode"]`` is present only in the step that publishes a window (the observer
+        appends whatever it finds, so a stale entry would be counted again)."""
+        self.extras.pop("episode", None)
+        self._ep_step = getattr(self, "_ep_step", 0) + 1
+        if self._ep_step % max(int(every), 1):
+            return
+        dev = torch.device(self._device)
+        if not hasattr(self, "_ep_host"):
+            self._ep_host = torch.zeros(4, dtype=torch.float64).pin_memory()
+            self._ep_prev = torch.zeros(4, dtype=torch.float64)
+            self._ep_event = None
+        if self._ep_event is not None:
+            self._ep_event.synchronize()  # recorded `every` steps ago: returns at once
+            tot = self._ep_host.clone()
+            win = tot - self._ep_prev
+            if bool((win < 0).any()):  # the accumulators were read-and-reset in between (read_episode_stats)
+                win = tot
+            self._ep_prev = tot
+            if float(win[1]) > 0:
+                self.extras["episode"] = {"mean_return": torch.tensor(float(win[0] / win[1])),
+                                          "mean_length": torch.tensor(float(win[2] / win[1])),
+                                          "count": torch.tensor(float(win[1]))}
+        self._ep_host.copy_(self.episode_stats.sum(dim=0), non_blocking=True)
+        self._ep_event = torch.cuda.Event()
+        self._ep_event.record(torch.cuda.current_stream(dev))
+
     def read_episode_stats(self, reset: bool = True) -> torch.Tensor:
         """[4] float64 on the device: sum(reward), #episodes finished, sum(length at finish), #env-steps."""
         s = self.episode_stats.sum(dim=0)

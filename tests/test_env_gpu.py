@@ -319,7 +319,7 @@ def test_rlgames_adapter_protocol(cuda_lib):
     a2c play_steps drives them: get_env_info, reset, step, process_infos, after_print_stats."""
     from omniisaacgymenvs_b200.utils.rlgames.rlgames_utils import RLGPUAlgoObserver, RLGPUEnv
 
-    env, task = make_env("Ant", num_envs=128)
+    env, task = make_env("Ant", num_envs=128, overrides={"task.env.episodeLength": 8})
     vec = RLGPUEnv("rlgpu", 128, env_creator=lambda **kw: env)
     info = vec.get_env_info()
     assert info["action_space"].shape == (8,) and info["observation_space"].shape == (60,) and "state_space" not in info
@@ -339,6 +339,17 @@ def test_rlgames_adapter_protocol(cuda_lib):
 
     ob = RLGPUAlgoObserver()
     ob.after_init(Algo)
+    # the task's own episode statistics reach the observer through infos["episode"] (every 16 steps, no sync)
+    seen = 0
+    for _ in range(64):
+        o, r, d, infos = vec.step(torch.rand(128, 8, device=task.device) * 2 - 1)
+        if "episode" in infos:
+            seen += 1
+            assert 1.0 <= float(infos["episode"]["mean_length"]) <= 8.0 and float(infos["episode"]["count"]) >= 128
+        ob.process_infos(infos, d.nonzero())
+    assert seen >= 2 and len(ob.ep_infos) == seen
+    ob.after_print_stats(frame=64 * 128, epoch_num=0, total_time=0.1)
+    assert {"Episode/mean_return", "Episode/mean_length", "Episode/count"} <= {k for k, _, _ in Algo.writer.rows}
     for _ in range(3):
         o, r, d, infos = vec.step(torch.rand(128, 8, device=task.device) * 2 - 1)
         infos = dict(infos, episode={"len": task.progress_buf.float().mean()}, lr=3e-4)
