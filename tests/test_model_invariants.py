@@ -126,7 +126,7 @@ def test_random_policy_episode_length_bands(cuda_lib):
     random-policy episodes are 20-40 steps long); the Ant survives several times longer."""
     from omniisaacgymenvs_b200.utils.task_util import make_env
 
-    mean_len = {}
+    mean_len, rate = {}, {}
     for robot, n_act in (("Humanoid", 21), ("Ant", 8)):
         env, task = make_env(robot, num_envs=2048, seed=1)
         env.reset()
@@ -134,7 +134,7 @@ def test_random_policy_episode_length_bands(cuda_lib):
         for _ in range(400):
             env.step(torch.rand(2048, n_act, device=task.device) * 2 - 1)
         st = task.read_episode_stats().cpu().numpy()
-        assert st[1] > 2048, "episodes must finish in the window"
-        mean_len[robot] = st[2] / st[1]
-    assert 12.0 < mean_len["Humanoid"] < 60.0, mean_len
-    assert mean_len["Ant"] > 1.5 * mean_len["Humanoid"], mean_len
+        rate[robot] = st[1] / st[3]  # episodes finished per env-step
+        mean_len[robot] = st[2] / max(st[1], 1.0)
+    assert rate["Humanoid"] > 1.0 / 60.0 and 12.0 < mean_len["Humanoid"] < 60.0, (mean_len, rate)
+    assert rate["Ant"] < rate["Humanoid"] / 1.5, (mean_len, rate)  # the four-legged Ant rarely tips below 0.31 m
