@@ -335,6 +335,11 @@ def timed_steps(torch, env, acts, flush, K, device):
 def run_ours(args):
     import torch
 
+    # host-buffer step knobs (read once when the library loads; the device-resident path does not use them): two chunks,
+    # observations stored straight into the pinned host buffer and actions read straight from it -- the best of the
+    # combinations in profiles/r2_e2e_breakdown.txt.  Opt-in because the device copy of obs_buf is then not written.
+    os.environ.setdefault("OIGE_HOST_ZEROCOPY", "3")
+    os.environ.setdefault("OIGE_HOST_CHUNKS", "2")
     from omniisaacgymenvs_b200 import _lib
 
     rank = int(os.environ.get("RANK", "0"))
@@ -544,7 +549,8 @@ def run_ours(args):
                                          "own solver, checked against its float64 oracle and model-level invariants (DESIGN.md section 4)"},
             "clocks": clocks.summary(clk_lo, clk_hi),
             "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "timing": "per-rank wall clock around K host-buffer steps (one stream sync per step), max over ranks"},
+                    "timing": "per-rank wall clock around K host-buffer steps (one stream sync per step), max over ranks",
+                    "knobs": {k: os.environ.get(k) for k in ("OIGE_HOST_ZEROCOPY", "OIGE_HOST_CHUNKS")}},
             "gpu_launches": int(launches),
             "roofline": roof, "issue": issue, "roofline_k1": roof_k1, "sustained": sustained, "no_self_collision": nosc,
             "cpu_baseline": cpu, "step_breakdown": breakdown,

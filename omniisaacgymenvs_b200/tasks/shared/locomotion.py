@@ -240,6 +240,17 @@ class LocomotionTask(RLTask):
         self.actions = torch.zeros((n, self.num_actions), device=dev)
         # episode statistics accumulated by K1 (sum rew, #done, sum len at done, #env-steps), striped
         self.episode_stats = torch.zeros((_lib.STATS_SLOTS, 4), device=dev, dtype=torch.float64)
+        # landing buffer of poll_episode_extras, pinned HERE (cudaHostAlloc synchronises the device and takes
+        # milliseconds: not something to do lazily inside a step)
+        self._ep_host = torch.zeros(4, dtype=torch.float64).pin_memory()
+        self._ep_prev = torch.zeros(4, dtype=torch.float64)
+        self._ep_event = None
+        self._ep_step = 0
+        # first use of the reduction / copy / event paths loads their CUDA modules (milliseconds): do it now
+        self._ep_host.copy_(self.episode_stats.sum(dim=0), non_blocking=True)
+        warm = torch.cuda.Event()
+        warm.record(torch.cuda.current_stream(dev))
+        warm.synchronize()
         self._bind_buffers()
 
         indices = torch.arange(self._robots.count, dtype=torch.int64, device=dev)
@@ -298,20 +309,17 @@ class LocomotionTask(RLTask):
         """Puts the episode statistics where the reference's observer looks (``infos["episode"]``,
         utils/rlgames/rlgames_utils.py:51-62,67-91) WITHOUT a per-step sync: every ``every`` steps the striped
         accumulators are summed on the device and copied to pinned host memory asynchronously; the copy enqueued
-        ``every`` steps earlier has long arrived by then and is published as the window's mean return / mean length /
-        episode count.  ``extras["episode"]`` is present only in the step that publishes a window (the observer
+        earlier is published as the window's mean return / mean length / episode count once its event has completed
+        (polled with ``query()``, never waited for: a host that runs ahead of the device just tries again later).  ``extras["episode"]`` is present only in the step that publishes a window (the observer
         appends whatever it finds, so a stale entry would be counted again)."""
         self.extras.pop("episode", None)
-        self._ep_step = getattr(self, "_ep_step", 0) + 1
+        self._ep_step += 1
         if self._ep_step % max(int(every), 1):
             return
         dev = torch.device(self._device)
-        if not hasattr(self, "_ep_host"):
-            self._ep_host = torch.zeros(4, dtype=torch.float64).pin_memory()
-            self._ep_prev = torch.zeros(4, dtype=torch.float64)
-            self._ep_event = None
         if self._ep_event is not None:
-            self._ep_event.synchronize()  # recorded `every` steps ago: returns at once
+            if not self._ep_event.query():  # the host runs ahead of the device: never wait, try again next time
+                return
             tot = self._ep_host.clone()
             win = tot - self._ep_prev
             if bool((win < 0).any()):  # the accumulators were read-and-reset in between (read_episode_stats)
