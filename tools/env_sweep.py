@@ -33,6 +33,7 @@ def main():
     ap.add_argument("--rollouts", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--eager", action="store_true", help="time the 3-launch eager step instead of the CUDA graph")
+    ap.add_argument("--no-self-collision", action="store_true", help="Humanoid with enable_self_collisions off")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0")); local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -51,7 +52,9 @@ def main():
         for total in (int(c) for c in args.counts.split(",")):
             lo, n = shard_range(total, rank, world)
             with contextlib.redirect_stdout(io.StringIO()):
-                env, task = make_env(task_name, num_envs=n, device_id=local, seed=42, env_id_offset=lo, global_num_envs=total)
+                ov = {"task.sim.Humanoid.enable_self_collisions": False} if (args.no_self_collision and task_name == "Humanoid") else None
+                env, task = make_env(task_name, num_envs=n, device_id=local, seed=42, env_id_offset=lo, global_num_envs=total,
+                                     overrides=ov)
                 env.reset()
                 if not args.eager:
                     env.enable_cuda_graph()
