@@ -1040,7 +1040,13 @@ bool k2_uses_role_kernel(const OigeModel* model, int64_t decision_n) {
         const int m = knobs().mode;
         return model->role_ok && m != 'w' && m != 't';
     }
-    return model->role_ok && use_role_split(decision_n, model->num_links);
+    if (!(model->role_ok && use_role_split(decision_n, model->num_links))) return false;
+    // The four-role variants (Ant, Anymal: 128-thread CTAs of 32 envs at 128 registers, four per SM) hold 128 envs per SM
+    // and wave; from the third wave on the thread-per-env path K3 -> K2-T -> K1 (512+ envs per SM) has the higher
+    // throughput for these small trees (profiles/r2_env_sweep_1gpu.txt: Ant 65536 envs 154 vs 129 us per step).  The
+    // Humanoid's three-role variant wins at every count (317 vs 280 M env-steps/s at 1 Mi envs).
+    if (model->nroles == 4 && knobs().mode != 'r' && decision_n > 2ll * 4 * 32 * sm_count()) return false;
+    return true;
 }
 
 namespace {
