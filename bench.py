@@ -229,8 +229,10 @@ def run_reference_arm(args):
         "impl": "reference", "metric": "humanoid_env_steps_per_sec", "value": rate, "unit": "env-steps/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"Humanoid full env step, {ENVS_PER_GPU} envs/GPU (BASELINE.json configs[2])",
-                   "sample_envs_per_step": sample_envs},
+        "config": {"workload": f"Humanoid full env step (K3 reset + 2x K2 articulation substeps + K1 obs/reward/reset), "
+                               f"{args.envs_per_gpu} envs/GPU (BASELINE.json configs[2])",
+                   "envs_per_gpu": args.envs_per_gpu, "sample_envs_per_step": sample_envs, "self_collision": True,
+                   "arm": "CPU oracle port (float64 OpenMP dynamics incl. self-collision + torch obs/reward/reset), all host cores"},
         "cpu_baseline": {"value": rate, "unit": "env-steps/s", "cores": threads, "kind": "port",
                          "sample": f"{sample_envs} envs x {args.steps} full env steps (2 dynamics substeps + obs/reward/reset); "
                                    "PhysX/Isaac Sim not installable, float64 OpenMP oracle + torch CPU oracle stand in"},
