@@ -138,3 +138,19 @@ def test_random_policy_episode_length_bands(cuda_lib):
         mean_len[robot] = st[2] / max(st[1], 1.0)
     assert rate["Humanoid"] > 1.0 / 60.0 and 12.0 < mean_len["Humanoid"] < 60.0, (mean_len, rate)
     assert rate["Ant"] < rate["Humanoid"] / 1.5, (mean_len, rate)  # the four-legged Ant rarely tips below 0.31 m
+
+
+@pytest.mark.gpu
+def test_ppo_return_rises_on_the_ant(cuda_lib):
+    """Behaviour-level plausibility: a minimal PPO through VecEnvRLGames.step learns to move the Ant --
+    the mean reward per step rises from about zero to above 1 within 60 iterations (1 M env-steps)."""
+    import os
+    import sys
+
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    import ppo_smoke
+
+    curve = ppo_smoke.run("Ant", iterations=60, num_envs=1024, verbose=False)
+    first = sum(c[0] for c in curve[:5]) / 5
+    last = sum(c[0] for c in curve[-10:]) / 10
+    assert last > 1.0 and last > first + 0.5, (first, last)
