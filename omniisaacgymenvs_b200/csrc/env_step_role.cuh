@@ -1019,7 +1019,11 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
         if (role == 0 && valid) { prev_pot_in = A.pot[env]; prog_in = A.progress[env]; reset_in = A.reset[env]; }
         if (valid) {
             float* row = o_obs + e * OBS;
-            for (int r = role; r < 4; r += NR) {  // quarter r of env e: K1's thread (e, r)
+            // quarter r of env e = K1's thread (e, r).  Quarters are dealt so that role 0, which also evaluates the reward
+            // below, gets the light one (2: heading, potentials) and the last role the two around it (0: roll / up, 3:
+            // local velocities); who evaluates a quarter does not change a bit of the result.
+#pragma unroll 1
+            for (int r = NR - 1 - role; r < 4; r += NR) {
                 lm::Partial part;
                 lm::partial_init(part);
                 for (int k = 0; k < (D + 3) / 4; ++k) {
