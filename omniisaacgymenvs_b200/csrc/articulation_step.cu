@@ -1475,7 +1475,7 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
                 if (nchains == 0 || sensor_chains[r] > 1) fits = false;  // every role works; one sensor wrench per role
                 if (!fits) break;
                 if (has_sc) {
-                    // self-collision program: every kinematics sweep first (sphere centres and link velocities published
+                    // self-collision program: every kinematics sweep first (capsule end points and link velocities published
                     // | barrier C), the pair phase (| barrier P), then the inertia sweeps
                     for (int c = 0; c < nchains; ++c) add_seg(kSegChain, ck0[c], ck1[c], cfl[c] | kSegKinOnly, catt[c], csl[c]);
                     if (fits) rm->seg_flag[r][ns - 1] |= kSegBarAfter;
@@ -1537,8 +1537,8 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
             // ---- self-collision tables ----
             rm->has_sc = has_sc ? 1 : 0;
             if (has_sc && fits) {
-                int owner_of_link[32], sph0[32], sphn[32];
-                for (int i = 0; i < L; ++i) { owner_of_link[i] = tidx[i] >= 0 ? 0 : -1; sphn[i] = 0; sph0[i] = 0; }
+                int owner_of_link[32], sphn[32];
+                for (int i = 0; i < L; ++i) { owner_of_link[i] = tidx[i] >= 0 ? 0 : -1; sphn[i] = 0; }
                 for (int i = 0; i < L; ++i) {
                     if (tidx[i] >= 0) { rm->w_idx[i] = (unsigned char)tidx[i]; rm->rec_off[i] = (unsigned short)(rm->oK + tidx[i] * kKin); }
                 }
@@ -1556,7 +1556,6 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
                 int nc2 = 0;
                 for (int i = 0; i < L; ++i) {
                     sphn[i] = d->capsule_radius[i] > 0.f ? 1 : 0;  // "has a self-collision shape"
-                    (void)sph0;
                     if (!sphn[i]) continue;
                     rm->cap_idx[i] = (unsigned char)nc2++;
                     float hl = 0.f;
@@ -1717,7 +1716,7 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
                     memcpy(&rm->sc_nar[k2].z, &rm->cap_il2[hi], 4);
                     memcpy(&rm->sc_nar[k2].w, &cr2, 4);
                 }
-                // the sphere centres live in the hand-over slots' memory during the kinematics / pair phases
+                // the capsule end points live in the hand-over slots' memory during the kinematics / pair phases
                 if (kRT + maxc > 32 || rm->group_floats > max_group_floats) fits = false;
             }
         }

@@ -9,12 +9,14 @@
 //
 // Mapping.  lane = env, warp = ROLE, a GROUP = 32 envs x `nroles` warps, a CTA = EPC/32 groups.  The tree is cut on the
 // host into a TRUNK (root + every link with a branching link at or below it; must be a path) and the plain CHAINS
-// hanging off it, dealt to the roles; role 0 also owns the trunk.  Per substep (three named barriers per group):
+// hanging off it, dealt to the roles; role 0 also owns the trunk.  Per substep (named barriers of the group; the
+// self-collision variant adds the pair phase between the kinematics and the inertia sweeps, see below):
 //   S0  role 0: kinematics of the trunk -> shared memory (xK)                                        | barrier K
 //   S1  every role, chain by chain: kinematics head -> tip (frames into the chain's link slots), then the articulated
 //       inertia tip -> head in registers; each link leaves (s, U/d, u''') in its slot; the head's I^a, p^a are added to
 //       the role's hand-over slot (xI).  A role with a slot on trunk link t may also take t's OWN inertia / bias /
-//       contacts off role 0's hands.                                                                  | barrier H
+//       contacts off role 0's hands.                  | barriers H_t: one per trunk link t with hand-over slots -- role 0
+//       waits at t only for the roles that hand over at t, which arrive (bar.arrive) and go on to barrier A
 //   S2  role 0: trunk tip -> root (own inertia + hand-over slots + carry), 6x6 Cholesky at the root, trunk accelerations
 //       root -> tip, trunk joints and root integrated, accelerations of the attach links published (xA) | barrier A
 //   S3  every role: accelerations down its chains -- 13 FMAs per link: qdd = u''' - (U/d).a', a' += s qdd -- and joint
@@ -335,7 +337,7 @@ __device__ __forceinline__ void capsule_contact(const MT& M, const char* Cb, con
 
 // SREG: the sensor link's frame waits in registers (Humanoid: shared memory is full) or in shared memory (xS; the
 // four-role variants run at 128 registers per thread)
-// SC: the model has self-collision pairs (per substep two more group barriers: sphere centres published | pair forces)
+// SC: the model has self-collision pairs (per substep three more group barriers: capsules published | hit words | pair forces)
 template <int MAXC, int NR, bool TGT, int EPC, int MINB, bool SREG, bool SC>
 __global__ void __launch_bounds__(NR * EPC, MINB)
 env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant__ OigeTaskParams P,

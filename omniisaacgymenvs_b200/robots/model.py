@@ -106,7 +106,7 @@ class ArticulationModel:
     angular_damping: float = 0.05
     max_angular_velocity: float = 5729.58008 * math.pi / 180.0
     max_depenetration_velocity: float = 10.0   # cfg/task/Humanoid.yaml:62,90
-    self_contact_stiffness: float = 1.0e4      # explicit sphere-sphere penalty (DESIGN.md "self-collision")
+    self_contact_stiffness: float = 1.0e4      # explicit capsule-capsule penalty (DESIGN.md "Self-collision")
     self_contact_damping: float = 5.0e1
     enable_self_collisions: bool = False       # cfg/task/Humanoid.yaml:80 (True), Ant.yaml:82 (False)
     collision_pairs: np.ndarray = field(default_factory=lambda: np.zeros((0, 2), np.int32))  # [P,2] link pairs
