@@ -116,6 +116,29 @@ __device__ __forceinline__ V3 cross(V3 a, V3 b) {
 __device__ __forceinline__ float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 
 struct Q4 { float w, x, y, z; };
+// sin / cos of a joint HALF angle.  Joint limits keep |x| below ~1.4 rad (the knee: 160 deg / 2), where two short Taylor
+// chains (x^13, x^12: truncation < 2e-8 at |x| = 1.75, i.e. below half an ulp of the result) replace sincosf's range
+// reduction -- it heads the dependency chain of every link's kinematics.  Anything larger takes sincosf.
+__device__ __forceinline__ void sincos_half_angle(float x, float* s, float* c) {
+    if (fabsf(x) > 1.75f) {
+        sincosf(x, s, c);
+        return;
+    }
+    const float x2 = x * x;
+    float ps = fmaf(x2, 1.6059044e-10f, -2.5052108e-8f);
+    ps = fmaf(ps, x2, 2.7557319e-6f);
+    ps = fmaf(ps, x2, -1.9841270e-4f);
+    ps = fmaf(ps, x2, 8.3333333e-3f);
+    ps = fmaf(ps, x2, -1.6666667e-1f);
+    *s = fmaf(ps * x2, x, x);
+    float pc = fmaf(x2, 2.0876757e-9f, -2.7557319e-7f);
+    pc = fmaf(pc, x2, 2.4801587e-5f);
+    pc = fmaf(pc, x2, -1.3888889e-3f);
+    pc = fmaf(pc, x2, 4.1666667e-2f);
+    pc = fmaf(pc, x2, -0.5f);
+    *c = fmaf(pc, x2, 1.f);
+}
+
 __device__ __forceinline__ Q4 qmul(Q4 a, Q4 b) {
     return {a.w * b.w - a.x * b.x - a.y * b.y - a.z * b.z, a.w * b.x + a.x * b.w + a.y * b.z - a.z * b.y,
             a.w * b.y - a.x * b.z + a.y * b.w + a.z * b.x, a.w * b.z + a.x * b.y - a.y * b.x + a.z * b.w};
@@ -509,7 +532,7 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
             Q4 ql = {1.f, 0.f, 0.f, 0.f};
             if (is_joint) {
                 float sh, ch;
-                sincosf(prismatic ? 0.f : 0.5f * q, &sh, &ch);
+                sincos_half_angle(prismatic ? 0.f : 0.5f * q, &sh, &ch);
                 ql = qmul(jquat, Q4{ch, sh * axis.x, sh * axis.y, sh * axis.z});
                 p = jpos;
             }
@@ -795,7 +818,7 @@ articulation_step_tpe_kernel(const DevModel* __restrict__ gmodel, const __grid_c
             const V3 axis = {M.axis[0][i], M.axis[1][i], M.axis[2][i]};
             float sh, ch;
             const bool prismatic = M.jtype[i] == OIGE_JOINT_PRISMATIC;
-            sincosf(prismatic ? 0.f : 0.5f * qv[i], &sh, &ch);
+            sincos_half_angle(prismatic ? 0.f : 0.5f * qv[i], &sh, &ch);
             const Q4 ql = qmul(Q4{M.jquat[0][i], M.jquat[1][i], M.jquat[2][i], M.jquat[3][i]},
                                Q4{ch, sh * axis.x, sh * axis.y, sh * axis.z});
             const Q4 qi = qmul(qp, ql);

@@ -169,7 +169,7 @@ __device__ __forceinline__ void kin_step(const MT& M, int i, float qj, float qdj
     const V3 axis = {M.axis[0][i], M.axis[1][i], M.axis[2][i]};
     const bool prismatic = M.jtype[i] == OIGE_JOINT_PRISMATIC;
     float sh, ch;
-    sincosf(prismatic ? 0.f : 0.5f * qj, &sh, &ch);
+    sincos_half_angle(prismatic ? 0.f : 0.5f * qj, &sh, &ch);
     const Q4 ql = qmul(Q4{M.jquat[0][i], M.jquat[1][i], M.jquat[2][i], M.jquat[3][i]},
                        Q4{ch, sh * axis.x, sh * axis.y, sh * axis.z});
     const Q4 qi = qmul(c.q, ql);

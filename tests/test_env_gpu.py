@@ -378,3 +378,11 @@ def test_whole_step_is_one_launch_from_4096_humanoids(cuda_lib):
     env.step(a)
     assert _lib.launch_count() - n0 == 1
     assert _lib.nonfinite_env_count() == bad0  # (cumulative per process: other tests blow envs up on purpose)
+
+
+def test_graft_entry_smoke_runs(cuda_lib, capsys):
+    """The driver's smoke() (one whole-step launch + the two oracle checks) must keep passing as the step changes shape."""
+    import __graft_entry__ as g
+
+    g.smoke()
+    assert "smoke ok" in capsys.readouterr().out
