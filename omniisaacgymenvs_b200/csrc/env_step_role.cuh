@@ -1049,7 +1049,7 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
                 s_part[(1 * 4 + r) * EPC + e] = part.act;
                 s_part[(2 * 4 + r) * EPC + e] = part.elec;
                 for (int k = 0; k < (S6n + 3) / 4; ++k) {
-                    const int j = lm::owned_index_rt(S6n, r, k, e);
+                    const int j = lm::owned_index_elem_rt(S6n, r, k, e);
                     if (j < S6n) row[12 + 2 * D + j] = lm::clampf(lm::mul(o_sens[e * S6n + j], P.contact_force_scale), clip);
                 }
                 const float4 q4 = *reinterpret_cast<const float4*>(o_quat + 4 * e);

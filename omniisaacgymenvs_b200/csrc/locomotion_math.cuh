@@ -120,6 +120,25 @@ __device__ __forceinline__ int owned_index(int r, int k, int e) {
 __device__ __forceinline__ int owned_index_rt(int len, int r, int k, int e) {
     return (len % 8 == 0) ? 8 * (k >> 1) + ((2 * r + (k & 1) + (e >> 2)) & 7) : r + 4 * k;
 }
+// Same for columns that are only copied / scaled (the sensor block: no reduction, any ownership gives the same bits).
+// LEN % 4 == 0 but not % 8 (the Humanoid's 12 sensor floats): stride 12 reaches 8 banks, lanes e and e + 8 collide
+// (4-way); rotating the column by e >> 3 moves the four lane groups onto the four residues mod 4.
+template <int LEN>
+__device__ __forceinline__ int owned_index_elem(int r, int k, int e) {
+    if constexpr (LEN % 8 != 0 && LEN % 4 == 0) {
+        const int j = r + 4 * k + ((e >> 3) & 3);
+        return j >= LEN ? j - LEN : j;
+    } else {
+        return owned_index<LEN>(r, k, e);
+    }
+}
+__device__ __forceinline__ int owned_index_elem_rt(int len, int r, int k, int e) {
+    if (len % 8 != 0 && len % 4 == 0) {
+        const int j = r + 4 * k + ((e >> 3) & 3);
+        return j >= len ? j - len : j;
+    }
+    return owned_index_rt(len, r, k, e);
+}
 
 // maths.unscale(dof_pos, lo, hi) = (2x - hi - lo) / (hi - lo)  (locomotion.py:233); rcp = RN(1 / (hi - lo))
 __device__ __forceinline__ float unscale(float q, float lo, float hi, float rcp) {

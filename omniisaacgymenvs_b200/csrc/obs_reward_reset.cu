@@ -195,7 +195,7 @@ __global__ void __launch_bounds__(4 * E) obs_reward_reset_kernel(const __grid_co
         s_part[(2 * 4 + r) * E + e] = part.elec;
 #pragma unroll
         for (int k = 0; k < (6 * S + 3) / 4; ++k) {
-            const int j = owned_index<6 * S>(r, k, e);
+            const int j = owned_index_elem<6 * S>(r, k, e);
             if (j < 6 * S) row[12 + 2 * D + j] = mul(s_sens[e * 6 * S + j], P.contact_force_scale);
         }
 
