@@ -1557,6 +1557,20 @@ OigeModel* k2_model_create(const OigeModelDesc* d) {
             rm->oH = rm->oM + 2;                       // one hit word per role (self-collision)
             rm->oL = rm->oH + (has_sc ? best_r : 0);
             rm->group_floats = rm->oL + best_r * maxc * kPu;
+            if (getenv("OIGE_DUMP_ROLES") != nullptr) {  // the trunk and the roles' segment programs (tools/dump_roles.py)
+                fprintf(stderr, "[oige] trunk:");
+                for (int t = 0; t < nt; ++t)
+                    fprintf(stderr, " t%d=link%d(own %s)", t, rm->tlink[t], rm->town[t] ? "handed over" : "role 0");
+                fprintf(stderr, "; %d hand-over slots, group scratch %d floats per lane (max %d)\n", rm->nslots, rm->group_floats,
+                        max_group_floats);
+                for (int r = 0; r < best_r; ++r) {
+                    fprintf(stderr, "[oige] program of role %d:", r);
+                    for (int q = 0; q < rm->nseg[r]; ++q)
+                        fprintf(stderr, " [kind %d links %d..%d flags 0x%x att t%d slot %d]", rm->seg_kind[r][q], rm->seg_first[r][q],
+                                rm->seg_last[r][q], rm->seg_flag[r][q], rm->seg_att[r][q], rm->seg_slot[r][q]);
+                    fprintf(stderr, "\n");
+                }
+            }
             // ---- self-collision tables ----
             rm->has_sc = has_sc ? 1 : 0;
             if (has_sc && fits) {
