@@ -5,7 +5,7 @@ The reference does not contain the robots: it references ``humanoid_instanceable
 which are USD conversions of the public ``nv_humanoid.xml`` / ``nv_ant.xml`` MJCF files of
 IsaacGymEnvs.  The tables below restate those public MJCF models (bodies, hinge joints, capsule /
 sphere geoms) as recalled -- PROVENANCE: not pinned by anything under /root/reference.  What the
-reference DOES pin is cross-checked in tests/test_models.py: DoF counts (21 / 8), the breadth-
+reference DOES pin is cross-checked in tests/test_config_models.py: DoF counts (21 / 8), the breadth-
 first joint order with its body names and gears (tasks/humanoid.py:82-107, tasks/ant.py:80),
 sensor counts (2 / 4, from the observation sizes 87 / 60) and spawn heights (1.34 / 0.5).
 

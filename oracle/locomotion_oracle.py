@@ -2,7 +2,7 @@
 
 A torch-fp32 restatement of the reference's locomotion task arithmetic, operation for
 operation in the reference's order so that every non-transcendental output is bit-identical
-to the verbatim reference functions (pinned by ``tests/test_oracle_vs_reference.py`` here in
+to the verbatim reference functions (pinned by ``tests/test_oracle_golden.py`` here in
 the container, and by the committed fixtures under ``tests/golden/`` everywhere else).
 
 Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s cpu_baseline / ``--impl
