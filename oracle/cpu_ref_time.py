@@ -1,12 +1,12 @@
-"""CPU baseline timings of SURVEY.md section 8(d) / BASELINE.json configs[0] (run in the BUILD container, where
+"""TEST / MEASUREMENT INFRASTRUCTURE ONLY (like the rest of oracle/) -- CPU baseline timings of SURVEY.md section 8(d) / BASELINE.json configs[0] (run in the BUILD container, where
 /root/reference exists -- nothing here runs on the GPU box):
   (i)  the VERBATIM reference torch.jit functions get_observations + get_dof_at_limit_cost + calculate_metrics + is_done
        (tasks/shared/locomotion.py:194-321, tasks/humanoid.py:120-127, tasks/ant.py:92-95), Ant and Humanoid at 4096 envs,
        torch.set_num_threads(1) and all cores, >= 50 iterations after 3 warm-ups;
   (ii) the float64 dynamics oracle (oracle/dynamics_oracle.c) per env-substep, 1 thread and all cores.
-Output: profiles/r2_cpu_reference_timing.txt (stdout)."""
+Output: profiles/r2_cpu_reference_timing.txt (stdout).  Run as `python -m oracle.cpu_ref_time` from the repo root."""
 import os, sys, time, statistics
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)  # repo root
 import numpy as np
 import torch
 from oracle import locomotion_oracle as lo, ref_loader, dynamics as dyn

@@ -3,7 +3,7 @@ algorithmic bytes (24 B read + 36 B written = 60 B/env-step), (2) the whole VecE
 K2 x2 substeps -> obs/reward/done), eager and as a CUDA graph, at the reference's 512 envs and larger counts,
 (3) the CPU oracle (torch fp32 restatement of tasks/cartpole.py + float64 dynamics oracle) on the host cores.
 
-    python tools/cartpole_time.py > gpurun_out/cartpole_time.txt
+    python tests/cartpole_time.py > gpurun_out/cartpole_time.txt
 """
 import contextlib
 import ctypes as C
