@@ -9,9 +9,11 @@ from omniisaacgymenvs_b200.utils.task_util import make_env
 lib = _lib.load()
 robot = sys.argv[1] if len(sys.argv) > 1 else "Humanoid"
 n = int(sys.argv[2]) if len(sys.argv) > 2 else 16384
-physics = len(sys.argv) > 3 and sys.argv[3] == "physics"
+physics = "physics" in sys.argv[3:]
+nosc = "nosc" in sys.argv[3:]  # Humanoid with enable_self_collisions off
 with contextlib.redirect_stdout(io.StringIO()):
-    env, task = make_env(robot, num_envs=n); env.reset()
+    env, task = make_env(robot, num_envs=n, overrides={"task.sim.Humanoid.enable_self_collisions": False} if nosc else None)
+    env.reset()
 dev = torch.device(task.device); v = task.get_robot()
 for _ in range(20):
     env.step(torch.rand(n, task.num_actions, device=dev) * 2 - 1)
