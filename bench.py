@@ -337,11 +337,12 @@ def timed_steps(torch, env, acts, flush, K, device):
 def run_ours(args):
     import torch
 
-    # host-buffer step knobs (read once when the library loads; the device-resident path does not use them): two chunks,
-    # observations stored straight into the pinned host buffer and actions read straight from it -- the best of the
-    # combinations in profiles/r2_e2e_breakdown.txt.  Opt-in because the device copy of obs_buf is then not written.
+    # host-buffer step knobs (read once when the library loads; the device-resident path does not use them): four chunks,
+    # observations, rewards and reset flags stored straight into the pinned host buffers and actions read straight from
+    # them -- the best of the combinations in profiles/r2_e2e_breakdown.txt.  Opt-in because the device copy of obs_buf is
+    # then not written.
     os.environ.setdefault("OIGE_HOST_ZEROCOPY", "3")
-    os.environ.setdefault("OIGE_HOST_CHUNKS", "2")
+    os.environ.setdefault("OIGE_HOST_CHUNKS", "4")
     from omniisaacgymenvs_b200 import _lib
 
     rank = int(os.environ.get("RANK", "0"))

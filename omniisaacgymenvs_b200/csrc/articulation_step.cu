@@ -1137,10 +1137,22 @@ inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) 
 
 // Whole env step in one launch (K2-F with prologue and epilogue).  Returns OIGE_E_MODEL + 1000 ("not applicable") when
 // the model / env count is not served by the role kernel -- the caller then runs the K3 -> K2 -> K1 sequence.
+// Side channel of the host-buffer step (capi.cu): device-mapped pinned host rows for the reward / reset flags of the env
+// range of the NEXT k2_fused_step call of this thread (consumed by it).
+static thread_local float* t_rew_host = nullptr;
+static thread_local long long* t_reset_host = nullptr;
+void k2_set_host_mirror(float* rew_host, long long* reset_host) { t_rew_host = rew_host; t_reset_host = reset_host; }
+bool k2_fused_applicable(const OigeModel* model, int64_t decision_n, bool with_targets) {
+    return k2_uses_role_kernel(model, decision_n) && role_variant_exists(model, with_targets);
+}
+
 int k2_fused_step(const OigeModel* model, const OigeTaskParams* P, const OigeState* st, const OigeTaskBuffers* b,
                   const OigeResetInit* init, const float* actions_in, float clip, uint64_t seed, uint64_t counter,
                   int64_t env_id_offset, int64_t n, int32_t substeps, float dt, cudaStream_t stream, int64_t decision_n,
                   bool bump_counter) {
+    float* const rew_host = t_rew_host;          // (consumed whatever happens below)
+    long long* const reset_host = t_reset_host;
+    t_rew_host = nullptr; t_reset_host = nullptr;
     const int64_t dn = decision_n > 0 ? decision_n : n;
     if (!k2_uses_role_kernel(model, dn) || !role_variant_exists(model, st->dof_pos_targets != nullptr)) return 1000;
     if (P->num_dof != model->num_dof)
@@ -1161,6 +1173,7 @@ int k2_fused_step(const OigeModel* model, const OigeTaskParams* P, const OigeSta
     A.obs = b->obs; A.rew = b->rew; A.pot = b->potentials; A.prev_pot = b->prev_potentials; A.up = b->up_vec;
     A.head = b->heading_vec; A.reset = reinterpret_cast<long long*>(b->reset_buf);
     A.progress = reinterpret_cast<long long*>(b->progress_buf); A.stats = b->episode_stats;
+    if (rew_host != nullptr && reset_host != nullptr) { A.rew_host = rew_host; A.reset_host = reset_host; }
     const void* ptrs[] = {A.pos, A.quat, A.vel, A.q, A.qd, A.sens, A.actions_in, A.actions_out, A.init_pos, A.init_rot,
                           A.init_q, A.obs, A.rew, A.pot, A.prev_pot, A.up, A.head, A.reset, A.progress};
     A.use_bulk = 1;

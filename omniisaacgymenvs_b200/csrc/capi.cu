@@ -68,6 +68,8 @@ int k2_fused_step(const OigeModel*, const OigeTaskParams*, const OigeState*, con
                   const float* actions_in, float clip, uint64_t seed, uint64_t counter, int64_t env_id_offset, int64_t n,
                   int32_t substeps, float dt, cudaStream_t, int64_t decision_n, bool bump_counter);
 void k2_reload_env();
+void k2_set_host_mirror(float* rew_host, long long* reset_host);
+bool k2_fused_applicable(const OigeModel*, int64_t decision_n, bool with_targets);
 uint64_t k2_nonfinite_count();
 OigeModel* k2_model_create(const OigeModelDesc*);
 int dr_apply(const OigeNoiseSpec*, const OigeNoiseSpec*, const OigeNoiseState*, const float*, float*, const int64_t*,
@@ -287,6 +289,20 @@ int oige_env_step_host_f32(const OigeModel* model, const OigeTaskParams* params,
         else if (zmode & 2)
             cudaGetLastError();
     }
+    // ... and, in the same mode, the reward / reset rows when the whole-step kernel serves the call: it stores them into
+    // the pinned buffers itself (besides the device copies the next step needs), and the two D2H copies below go away
+    float* rew_host_dev = nullptr;
+    long long* reset_host_dev = nullptr;
+    if (obs_host_dev && k2_fused_applicable(model, n_envs, state->dof_pos_targets != nullptr)) {
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, rew_host) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer)
+            rew_host_dev = static_cast<float*>(at.devicePointer);
+        else cudaGetLastError();
+        if (cudaPointerGetAttributes(&at, reset_host) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer)
+            reset_host_dev = static_cast<long long*>(at.devicePointer);
+        else cudaGetLastError();
+        if (!rew_host_dev || !reset_host_dev) { rew_host_dev = nullptr; reset_host_dev = nullptr; }
+    }
     const int nchunks = host_chunk_count();
     int64_t per = ((n_envs + nchunks - 1) / nchunks + 31) / 32 * 32;  // tile-aligned chunk size
     if (n_envs < 4096) per = n_envs;                                           // too small to be worth splitting
@@ -332,6 +348,7 @@ int oige_env_step_host_f32(const OigeModel* model, const OigeTaskParams* params,
             if (e != cudaSuccess) return fail((int)e, "H2D actions: %s", cudaGetErrorString(e));
         }
         if (hp->trace) cudaEventRecord(hp->t[used][0], s);
+        if (rew_host_dev) k2_set_host_mirror(rew_host_dev + off, reset_host_dev + off);
         if (int rc = env_step_impl(model, params, &st, &bf, &in, stage, clip_actions, seed, counter,
                                    env_id_offset + off, cnt, substeps, dt, (void*)s, n_envs))
             return rc;
@@ -347,10 +364,12 @@ int oige_env_step_host_f32(const OigeModel* model, const OigeTaskParams* params,
         cudaStreamWaitEvent(user, hp->done[used], 0);  // the caller's stream observes the whole step
     }
     hp->last_used = used;
-    e = cudaMemcpyAsync(rew_host, buf->rew, (size_t)n_envs * sizeof(float), cudaMemcpyDeviceToHost, user);
-    if (e == cudaSuccess)
-        e = cudaMemcpyAsync(reset_host, buf->reset_buf, (size_t)n_envs * sizeof(int64_t), cudaMemcpyDeviceToHost, user);
-    if (e != cudaSuccess) return fail((int)e, "D2H rew/reset: %s", cudaGetErrorString(e));
+    if (!rew_host_dev) {
+        e = cudaMemcpyAsync(rew_host, buf->rew, (size_t)n_envs * sizeof(float), cudaMemcpyDeviceToHost, user);
+        if (e == cudaSuccess)
+            e = cudaMemcpyAsync(reset_host, buf->reset_buf, (size_t)n_envs * sizeof(int64_t), cudaMemcpyDeviceToHost, user);
+        if (e != cudaSuccess) return fail((int)e, "D2H rew/reset: %s", cudaGetErrorString(e));
+    }
     if (buf->reset_counter != nullptr) {
         bump_counter_kernel<<<1, 1, 0, user>>>(reinterpret_cast<unsigned long long*>(buf->reset_counter));
         count_launch();

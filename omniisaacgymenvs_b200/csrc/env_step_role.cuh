@@ -116,6 +116,9 @@ struct FArgs {
     float* obs; float* rew; float* pot; float* prev_pot; float* up; float* head;
     long long* reset; long long* progress;
     double* stats;
+    // host-buffer step, zero-copy mode: reward and reset flags are ALSO stored straight into the caller's pinned host
+    // buffers (device-mapped pointers; null otherwise), so no copy-engine transfer follows the kernel
+    float* rew_host; long long* reset_host;
 };
 
 __device__ unsigned long long g_nonfinite_envs = 0;  // envs parked by the non-finite guard since load (diagnostic)
@@ -1095,6 +1098,7 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
             A.progress[env] = prog;
             A.reset[env] = rst;
             A.rew[env] = total;
+            if (A.rew_host != nullptr) { A.rew_host[env] = total; A.reset_host[env] = rst; }
             A.prev_pot[env] = prev;
             A.pot[env] = o_pot[e];
             st_rew = total;
