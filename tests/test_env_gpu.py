@@ -386,3 +386,37 @@ def test_graft_entry_smoke_runs(cuda_lib, capsys):
 
     g.smoke()
     assert "smoke ok" in capsys.readouterr().out
+
+
+@pytest.mark.parametrize("chunks", ["1", "4"])
+def test_step_host_zero_copy_mode_equals_device_step(cuda_lib, monkeypatch, chunks):
+    """OIGE_HOST_ZEROCOPY=3 (what bench.py's e2e leg runs): the whole-step kernel reads the actions from, and stores
+    observations / rewards / reset flags into, the pinned host buffers itself; results must equal the device-buffer step
+    bit for bit, over several reset waves, eager and as a captured graph."""
+    monkeypatch.setenv("OIGE_HOST_ZEROCOPY", "3")
+    monkeypatch.setenv("OIGE_HOST_CHUNKS", chunks)
+    cuda_lib.oige_reload_env()
+    try:
+        n = 8192 + 96
+        ov = {"task.env.episodeLength": 6}
+        env_a, task_a = make_env("Humanoid", num_envs=n, seed=4, overrides=ov)
+        env_b, task_b = make_env("Humanoid", num_envs=n, seed=4, overrides=ov)
+        env_a.reset(); env_b.reset()
+        ring = [(torch.rand(n, 21) * 2 - 1).pin_memory() for _ in range(2)]
+        obs_h = torch.empty(n, 87).pin_memory(); rew_h = torch.empty(n).pin_memory()
+        rst_h = torch.empty(n, dtype=torch.int64).pin_memory()
+        env_a.enable_cuda_graph_host(ring[0], obs_h, rew_h, rst_h)  # slot 1 stays eager
+        resets = 0
+        for t in range(14):
+            ah = ring[t % 2]
+            ah.copy_(torch.rand(n, 21) * 2 - 1)
+            env_a.step_host(ah, obs_h, rew_h, rst_h)
+            torch.cuda.synchronize()
+            o, r, d, _ = env_b.step(ah.to(task_b.device))
+            assert torch.equal(obs_h, o["obs"].cpu()) and torch.equal(rew_h, r.cpu()) and torch.equal(rst_h, d.cpu()), t
+            resets += int(rst_h.sum())
+        assert resets > n
+        assert torch.equal(task_a.get_robot().dof_pos, task_b.get_robot().dof_pos)
+    finally:
+        monkeypatch.undo()
+        cuda_lib.oige_reload_env()
