@@ -391,6 +391,9 @@ def run_ours(args):
     clocks.__enter__()
     for _ in range(W):
         env.step(torch.rand(n, D, device=device, generator=gen) * 2 - 1)
+    reduce_stats()  # first NCCL collective of the process (lazy connection set-up) happens here, not in the timed region
+    if reducer._side is not None:
+        reducer._side.synchronize()
     barrier()
 
     # ---- timed region: device-resident inputs, per-step event pairs, L2 flushed between steps ----
