@@ -1120,7 +1120,16 @@ int role_dispatch(const OigeModel* model, const OigeTaskParams* P, const FArgs& 
         return role_launch(env_step_role_kernel<6, 3, false, 32, 3, true, false>, 1, 3 * 32, 32, model, P, A, stream);
     }
     if (model->nroles == 4 && model->maxc == 3 && !model->has_sc) {
-        if (tgt) return role_launch(env_step_role_kernel<3, 4, true, 32, 4, false, false>, 2, 4 * 32, 32, model, P, A, stream);
+        // up to three CTAs per SM cover the launch: 168 instead of 128 registers per thread (no spills)
+        // (OIGE_K2_MINB=4 pins the 128-register shape, as it pins K2-T's: the two shapes are different ptxas schedules
+        // and agree to rounding, not bit for bit)
+        const int mb = knobs().minb;
+        const bool roomy = mb ? mb < 4 : (dn + 31) / 32 <= 3ll * sm_count();
+        if (tgt) {
+            if (roomy) return role_launch(env_step_role_kernel<3, 4, true, 32, 3, false, false>, 6, 4 * 32, 32, model, P, A, stream);
+            return role_launch(env_step_role_kernel<3, 4, true, 32, 4, false, false>, 2, 4 * 32, 32, model, P, A, stream);
+        }
+        if (roomy) return role_launch(env_step_role_kernel<3, 4, false, 32, 3, false, false>, 7, 4 * 32, 32, model, P, A, stream);
         return role_launch(env_step_role_kernel<3, 4, false, 32, 4, false, false>, 3, 4 * 32, 32, model, P, A, stream);
     }
     return fail(OIGE_E_MODEL, "env_step_role_kernel: no instantiation for %d roles x %d links%s", model->nroles,

@@ -6,7 +6,7 @@ import torch
 from omniisaacgymenvs_b200.utils.task_util import make_env
 NOSC = len(sys.argv) > 1 and sys.argv[1] == "nosc"
 for robot in (("Humanoid",) if NOSC else ("Humanoid", "Ant")):
-    for n in (1024, 4096, 16384, 65536):
+    for n in [int(x) for x in os.environ.get("STEP_NS", "1024,4096,16384,65536").split(",")]:
         out = [f"{robot} n={n:6d}"]
         for graph in (False, True):
             with contextlib.redirect_stdout(io.StringIO()):
