@@ -98,7 +98,7 @@ class ClockSampler:
     def __init__(self, index: int):
         self.index, self.samples, self._stop, self._t = index, [], threading.Event(), None
         self.sm_max = None
-        self.interval = 0.002  # s between NVML samples (raised around the host-buffer loop: one polling thread per rank)
+        self.interval = 0.001  # s between NVML samples (raised around the host-buffer loop: one polling thread per rank)
         self._nvml = None
         try:
             import pynvml
@@ -444,7 +444,7 @@ def run_ours(args):
         torch.cuda.synchronize(device)  # the caller reads obs/rew/reset every step
     e2e_s = time.perf_counter() - t0  # this rank's own loop; the slowest rank sets the job's rate (max over ranks)
     e2e_value = world * n * K / max_over_ranks(e2e_s, device)
-    clocks.interval = 0.002
+    clocks.interval = 0.001
     h2d = n * D * 4
     d2h = n * task.num_observations * 4 + n * 4 + n * 8
 
