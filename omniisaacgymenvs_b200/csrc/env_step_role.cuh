@@ -957,6 +957,7 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
     }
     if (bad && role == 0 && valid) atomicAdd(&g_nonfinite_envs, 1ull);
     __syncthreads();  // every group is done with its scratch: the output tile below aliases it
+    STAMP(91);
 
     // ================= output tile ============================================================================
     const int S6n = A.S * 6, OBS = A.OBS;
@@ -1016,6 +1017,7 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
         }
     }
     __syncthreads();
+    STAMP(92);
 
     // ================= epilogue: observations, reward, termination (locomotion_math.cuh = K1's arithmetic) ==
     float st_rew = 0.0f, st_done = 0.0f, st_len = 0.0f;
@@ -1081,6 +1083,7 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
             }
         }
         __syncthreads();
+        STAMP(93);
         if (role == 0 && valid) {  // reward + termination: one thread per env, coalesced [N] accesses
             float* row = o_obs + e * OBS;
             float red[3];
@@ -1116,10 +1119,12 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
         }
     }
 
+    STAMP(94);
     // ================= drain ==================================================================================
     if (bulk) {
         fence_async_smem();
         __syncthreads();
+        STAMP(95);
         if (tid == 0) {
             bulk_s2g(A.q + e0 * D, o_q, EPC * D * 4);
             bulk_s2g(A.qd + e0 * D, o_qd, EPC * D * 4);

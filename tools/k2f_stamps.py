@@ -17,7 +17,7 @@ def build():
     print(LIB)
 
 TAGS = {1: "kernel: state in registers", 10: "substep start", 40: "pairs: broad done", 41: "pairs: narrow done", 42: "pairs: hit barrier passed",
-        43: "pairs: contacts done", 44: "pairs: barrier passed", 80: "S2b done / at barrier A", 81: "barrier A passed", 90: "substeps done", 99: "epilogue done"}
+        43: "pairs: contacts done", 44: "pairs: barrier passed", 80: "S2b done / at barrier A", 81: "barrier A passed", 90: "substeps done", 91: "all groups done (syncthreads)", 92: "output tile written", 93: "obs quarters done", 94: "reward / stats done", 95: "fence + sync before the bulk stores", 99: "bulk stores issued"}
 def name(t):
     if t in TAGS: return TAGS[t]
     k, sg = divmod(t, 10)
