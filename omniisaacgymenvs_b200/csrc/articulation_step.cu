@@ -1090,6 +1090,13 @@ int role_launch(K kern, int variant, int nthreads, int epc, const OigeModel* mod
                 const FArgs& A, cudaStream_t stream) {
     static std::atomic<int> configured[8][64];  // [variant][device]: max dynamic smem the kernel was configured for
     const size_t smem = role_smem_bytes(model, epc, A.D, A.S);
+    {   // a group's output tile (32 envs) aliases the group's own scratch
+        const int OBS = 12 + 3 * A.D + 6 * A.S;
+        const size_t group_tile = (size_t)32 * (2 * A.D + 6 * A.S + 13) + (size_t)32 * (A.D + OBS + 6 + 1 + 12) + 128;
+        if (epc > 32 && group_tile > (size_t)model->group_floats * 32)
+            return fail(OIGE_E_MODEL, "env_step_role_kernel: a group's output tile (%zu floats) does not fit in its scratch (%d)",
+                        group_tile, model->group_floats * 32);
+    }
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64) dev = 0;

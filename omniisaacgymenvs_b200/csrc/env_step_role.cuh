@@ -348,7 +348,6 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
     __shared__ __align__(16) RoleModel M;
     __shared__ __align__(8) uint64_t s_bar;
     __shared__ unsigned long long s_counter;
-    __shared__ float s_stat[(EPC / 32) * 3];
     extern __shared__ __align__(128) float dynsm[];
     constexpr int NT = NR * EPC;
     constexpr int GT = NR * 32;  // threads of a group
@@ -956,24 +955,32 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
         rvel = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
     }
     if (bad && role == 0 && valid) atomicAdd(&g_nonfinite_envs, 1ull);
-    __syncthreads();  // every group is done with its scratch: the output tile below aliases it
+    // From here on every GROUP works alone: its output tile (32 envs) aliases its OWN scratch, so a group that is done
+    // with its substeps does not wait for the CTA's slowest group (4.7 k cycles at 16384 Humanoids) -- group barriers
+    // only, one lane per group issues the group's bulk stores.
+    group_barrier(bar_id, GT);  // every role of the group is done with the scratch
     STAMP(91);
 
     // ================= output tile ============================================================================
     const int S6n = A.S * 6, OBS = A.OBS;
-    float* o_q = dynsm;
-    float* o_qd = o_q + EPC * D;
-    float* o_sens = o_qd + EPC * D;
-    float* o_pos = o_sens + EPC * S6n;
-    float* o_quat = o_pos + EPC * 3;
-    float* o_vel = o_quat + EPC * 4;
-    float* o_act = o_vel + EPC * 6;         // epilogue only from here on
-    float* o_obs = o_act + EPC * D;
-    float* o_up = o_obs + EPC * OBS;
-    float* o_head = o_up + EPC * 3;
-    float* o_pot = o_head + EPC * 3;
-    float* s_part = o_pot + EPC;            // [3 reductions][4 quarters][EPC]
-    float* s_lo = s_part + 12 * EPC;        // per-dof constants
+    constexpr int GE = 32;                  // envs of a group
+    const int le = lane;                    // env index inside the group's tile
+    const int gtid = role * 32 + lane;      // thread index inside the group
+    const int gcnt = cnt - grp * GE < 0 ? 0 : (cnt - grp * GE > GE ? GE : cnt - grp * GE);  // envs of this group
+    const long long ge0 = e0 + grp * GE;    // first global env of the group
+    float* o_q = dynsm + (size_t)grp * M.group_floats * 32;
+    float* o_qd = o_q + GE * D;
+    float* o_sens = o_qd + GE * D;
+    float* o_pos = o_sens + GE * S6n;
+    float* o_quat = o_pos + GE * 3;
+    float* o_vel = o_quat + GE * 4;
+    float* o_act = o_vel + GE * 6;          // epilogue only from here on
+    float* o_obs = o_act + GE * D;
+    float* o_up = o_obs + GE * OBS;
+    float* o_head = o_up + GE * 3;
+    float* o_pot = o_head + GE * 3;
+    float* s_part = o_pot + GE;             // [3 reductions][4 quarters][GE]
+    float* s_lo = s_part + 12 * GE;         // per-dof constants
     float* s_hi = s_lo + 32;
     float* s_ratio = s_hi + 32;
     float* s_rcp = s_ratio + 32;
@@ -982,9 +989,9 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
         for (int k = 0; k < MAXC; ++k) {
             if (k < np) {
                 const int d = M.dof[M.plink[role][k]];
-                o_q[e * D + d] = bad ? 0.f : qr[k];
-                o_qd[e * D + d] = bad ? 0.f : qdr[k];
-                o_act[e * D + d] = ar[k];
+                o_q[le * D + d] = bad ? 0.f : qr[k];
+                o_qd[le * D + d] = bad ? 0.f : qdr[k];
+                o_act[le * D + d] = ar[k];
             }
         }
         if (role == 0) {
@@ -992,31 +999,31 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
             for (int t = 1; t < kRT; ++t) {
                 if (t < ntrunk) {
                     const int d = M.dof[M.tlink[t]];
-                    o_q[e * D + d] = bad ? 0.f : tq[t - 1];
-                    o_qd[e * D + d] = bad ? 0.f : tqd[t - 1];
-                    o_act[e * D + d] = ta[t - 1];
+                    o_q[le * D + d] = bad ? 0.f : tq[t - 1];
+                    o_qd[le * D + d] = bad ? 0.f : tqd[t - 1];
+                    o_act[le * D + d] = ta[t - 1];
                 }
             }
-            o_pos[e * 3] = rpos.x; o_pos[e * 3 + 1] = rpos.y; o_pos[e * 3 + 2] = rpos.z;
-            *reinterpret_cast<float4*>(o_quat + e * 4) = make_float4(rquat.w, rquat.x, rquat.y, rquat.z);
-            float* vv = o_vel + e * 6;
+            o_pos[le * 3] = rpos.x; o_pos[le * 3 + 1] = rpos.y; o_pos[le * 3 + 2] = rpos.z;
+            *reinterpret_cast<float4*>(o_quat + le * 4) = make_float4(rquat.w, rquat.x, rquat.y, rquat.z);
+            float* vv = o_vel + le * 6;
             vv[0] = rvel.a[3]; vv[1] = rvel.a[4]; vv[2] = rvel.a[5];
             vv[3] = rvel.a[0]; vv[4] = rvel.a[1]; vv[5] = rvel.a[2];
         }
         if (sw_idx >= 0) {
 #pragma unroll
-            for (int j = 0; j < 6; ++j) o_sens[e * S6n + sw_idx * 6 + j] = bad ? 0.f : sw[j];
+            for (int j = 0; j < 6; ++j) o_sens[le * S6n + sw_idx * 6 + j] = bad ? 0.f : sw[j];
         }
     }
     if (A.epi) {
-        if (tid < 32) {
-            s_lo[tid] = tid < D ? P.dof_limits_lower[tid] : 0.0f;
-            s_hi[tid] = tid < D ? P.dof_limits_upper[tid] : 0.0f;
-            s_ratio[tid] = tid < D ? P.motor_effort_ratio[tid] : 0.0f;
-            s_rcp[tid] = tid < D ? 1.0f / (P.dof_limits_upper[tid] - P.dof_limits_lower[tid]) : 0.0f;
+        if (gtid < 32) {
+            s_lo[gtid] = gtid < D ? P.dof_limits_lower[gtid] : 0.0f;
+            s_hi[gtid] = gtid < D ? P.dof_limits_upper[gtid] : 0.0f;
+            s_ratio[gtid] = gtid < D ? P.motor_effort_ratio[gtid] : 0.0f;
+            s_rcp[gtid] = gtid < D ? 1.0f / (P.dof_limits_upper[gtid] - P.dof_limits_lower[gtid]) : 0.0f;
         }
     }
-    __syncthreads();
+    group_barrier(bar_id, GT);
     STAMP(92);
 
     // ================= epilogue: observations, reward, termination (locomotion_math.cuh = K1's arithmetic) ==
@@ -1029,8 +1036,8 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
         long long prog_in = 0, reset_in = 0;
         if (role == 0 && valid) { prev_pot_in = A.pot[env]; prog_in = A.progress[env]; reset_in = A.reset[env]; }
         if (valid) {
-            float* row = o_obs + e * OBS;
-            // quarter r of env e = K1's thread (e, r).  Quarters are dealt so that role 0, which also evaluates the reward
+            float* row = o_obs + le * OBS;
+            // quarter r of env le = K1's thread (le, r).  Quarters are dealt so that role 0, which also evaluates the reward
             // below, gets the light one (2: heading, potentials) and the last role the two around it (0: roll / up, 3:
             // local velocities); who evaluates a quarter does not change a bit of the result.
 #pragma unroll 1
@@ -1038,11 +1045,11 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
                 lm::Partial part;
                 lm::partial_init(part);
                 for (int k = 0; k < (D + 3) / 4; ++k) {
-                    const int d = lm::owned_index_rt(D, r, k, e);
+                    const int d = lm::owned_index_rt(D, r, k, le);
                     if (d < D) {
-                        const float qs = lm::unscale(o_q[e * D + d], s_lo[d], s_hi[d], s_rcp[d]);
-                        const float dv = lm::mul(o_qd[e * D + d], P.dof_vel_scale);
-                        const float a = o_act[e * D + d];
+                        const float qs = lm::unscale(o_q[le * D + d], s_lo[d], s_hi[d], s_rcp[d]);
+                        const float dv = lm::mul(o_qd[le * D + d], P.dof_vel_scale);
+                        const float a = o_act[le * D + d];
                         row[12 + d] = lm::clampf(qs, clip);
                         row[12 + D + d] = lm::clampf(dv, clip);
                         row[12 + 2 * D + S6n + d] = lm::clampf(a, clip);
@@ -1050,51 +1057,51 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
                     }
                 }
                 lm::partial_finish(P, part);
-                s_part[(0 * 4 + r) * EPC + e] = part.limit;
-                s_part[(1 * 4 + r) * EPC + e] = part.act;
-                s_part[(2 * 4 + r) * EPC + e] = part.elec;
+                s_part[(0 * 4 + r) * GE + le] = part.limit;
+                s_part[(1 * 4 + r) * GE + le] = part.act;
+                s_part[(2 * 4 + r) * GE + le] = part.elec;
                 for (int k = 0; k < (S6n + 3) / 4; ++k) {
-                    const int j = lm::owned_index_elem_rt(S6n, r, k, e);
-                    if (j < S6n) row[12 + 2 * D + j] = lm::clampf(lm::mul(o_sens[e * S6n + j], P.contact_force_scale), clip);
+                    const int j = lm::owned_index_elem_rt(S6n, r, k, le);
+                    if (j < S6n) row[12 + 2 * D + j] = lm::clampf(lm::mul(o_sens[le * S6n + j], P.contact_force_scale), clip);
                 }
-                const float4 q4 = *reinterpret_cast<const float4*>(o_quat + 4 * e);
+                const float4 q4 = *reinterpret_cast<const float4*>(o_quat + 4 * le);
                 const float rot[4] = {q4.x, q4.y, q4.z, q4.w};
                 float tqq[4];
                 lm::torso_quat(P, rot, tqq);
-                const float px = o_pos[3 * e], py = o_pos[3 * e + 1], pz = o_pos[3 * e + 2];
+                const float px = o_pos[3 * le], py = o_pos[3 * le + 1], pz = o_pos[3 * le + 2];
                 // columns 0 (height), 10 (up projection) and 11 (heading projection) stay unclamped until the reward
                 // thread has read them; every other column is clamped by the thread that wrote it
                 if (r == 0) {
-                    lm::root_part0(P, tqq, closed, row, o_up + 3 * e);
+                    lm::root_part0(P, tqq, closed, row, o_up + 3 * le);
                     row[8] = lm::clampf(row[8], clip);
                 } else if (r == 1) {
                     lm::root_part1(P, tqq, px, py, pz, closed, row);
                     row[7] = lm::clampf(row[7], clip);
                     row[9] = lm::clampf(row[9], clip);
                 } else if (r == 2) {
-                    lm::root_part2(P, tqq, px, py, row, o_head + 3 * e, o_pot + e);
+                    lm::root_part2(P, tqq, px, py, row, o_head + 3 * le, o_pot + le);
                 } else {
-                    const float lin3[3] = {o_vel[6 * e], o_vel[6 * e + 1], o_vel[6 * e + 2]};
-                    const float ang3[3] = {o_vel[6 * e + 3], o_vel[6 * e + 4], o_vel[6 * e + 5]};
+                    const float lin3[3] = {o_vel[6 * le], o_vel[6 * le + 1], o_vel[6 * le + 2]};
+                    const float ang3[3] = {o_vel[6 * le + 3], o_vel[6 * le + 4], o_vel[6 * le + 5]};
                     lm::root_part3(P, tqq, pz, lin3, ang3, row);
 #pragma unroll
                     for (int j = 1; j < 7; ++j) row[j] = lm::clampf(row[j], clip);
                 }
             }
         }
-        __syncthreads();
+        group_barrier(bar_id, GT);
         STAMP(93);
         if (role == 0 && valid) {  // reward + termination: one thread per env, coalesced [N] accesses
-            float* row = o_obs + e * OBS;
+            float* row = o_obs + le * OBS;
             float red[3];
 #pragma unroll
             for (int c = 0; c < 3; ++c)
-                red[c] = lm::combine4(s_part[(c * 4 + 0) * EPC + e], s_part[(c * 4 + 1) * EPC + e],
-                                      s_part[(c * 4 + 2) * EPC + e], s_part[(c * 4 + 3) * EPC + e]);
+                red[c] = lm::combine4(s_part[(c * 4 + 0) * GE + le], s_part[(c * 4 + 1) * GE + le],
+                                      s_part[(c * 4 + 2) * GE + le], s_part[(c * 4 + 3) * GE + le]);
             const float prev = prev_pot_in;
             float total;
             long long prog, rst;
-            lm::reward_done(P, row[0], row[10], row[11], o_pot[e], prev, red, prog_in, reset_in, total, prog, rst);
+            lm::reward_done(P, row[0], row[10], row[11], o_pot[le], prev, red, prog_in, reset_in, total, prog, rst);
             row[0] = lm::clampf(row[0], clip);
             row[10] = lm::clampf(row[10], clip);
             row[11] = lm::clampf(row[11], clip);
@@ -1103,70 +1110,61 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
             A.rew[env] = total;
             if (A.rew_host != nullptr) { A.rew_host[env] = total; A.reset_host[env] = rst; }
             A.prev_pot[env] = prev;
-            A.pot[env] = o_pot[e];
+            A.pot[env] = o_pot[le];
             st_rew = total;
             st_done = rst != 0 ? 1.0f : 0.0f;
             st_len = rst != 0 ? (float)prog : 0.0f;
         }
-        if (A.stats != nullptr && role == 0) {  // warp-uniform
+        if (A.stats != nullptr && role == 0) {  // warp-uniform: one striped atomic set per group
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) {
                 st_rew += __shfl_xor_sync(0xffffffffu, st_rew, o);
                 st_done += __shfl_xor_sync(0xffffffffu, st_done, o);
                 st_len += __shfl_xor_sync(0xffffffffu, st_len, o);
             }
-            if (lane == 0) { s_stat[grp * 3 + 0] = st_rew; s_stat[grp * 3 + 1] = st_done; s_stat[grp * 3 + 2] = st_len; }
+            if (lane == 0 && gcnt > 0) {
+                double* slot = A.stats + ((blockIdx.x * (EPC / 32) + grp) % OIGE_STATS_SLOTS) * 4;
+                atomicAdd(slot + 0, (double)st_rew);
+                atomicAdd(slot + 1, (double)st_done);
+                atomicAdd(slot + 2, (double)st_len);
+                atomicAdd(slot + 3, (double)gcnt);
+            }
         }
     }
-
     STAMP(94);
-    // ================= drain ==================================================================================
-    if (bulk) {
+
+    // ================= drain (per group) ======================================================================
+    if (A.use_bulk && gcnt == GE) {
         fence_async_smem();
-        __syncthreads();
+        group_barrier(bar_id, GT);
         STAMP(95);
-        if (tid == 0) {
-            bulk_s2g(A.q + e0 * D, o_q, EPC * D * 4);
-            bulk_s2g(A.qd + e0 * D, o_qd, EPC * D * 4);
-            if (A.sens != nullptr && S6n > 0) bulk_s2g(A.sens + e0 * S6n, o_sens, EPC * S6n * 4);
-            bulk_s2g(A.pos + e0 * 3, o_pos, EPC * 12);
-            bulk_s2g(A.quat + e0 * 4, o_quat, EPC * 16);
-            bulk_s2g(A.vel + e0 * 6, o_vel, EPC * 24);
+        if (gtid == 0) {
+            bulk_s2g(A.q + ge0 * D, o_q, GE * D * 4);
+            bulk_s2g(A.qd + ge0 * D, o_qd, GE * D * 4);
+            if (A.sens != nullptr && S6n > 0) bulk_s2g(A.sens + ge0 * S6n, o_sens, GE * S6n * 4);
+            bulk_s2g(A.pos + ge0 * 3, o_pos, GE * 12);
+            bulk_s2g(A.quat + ge0 * 4, o_quat, GE * 16);
+            bulk_s2g(A.vel + ge0 * 6, o_vel, GE * 24);
             if (A.epi) {
-                bulk_s2g(A.obs + e0 * OBS, o_obs, EPC * OBS * 4);
-                bulk_s2g(A.up + e0 * 3, o_up, EPC * 12);
-                bulk_s2g(A.head + e0 * 3, o_head, EPC * 12);
+                bulk_s2g(A.obs + ge0 * OBS, o_obs, GE * OBS * 4);
+                bulk_s2g(A.up + ge0 * 3, o_up, GE * 12);
+                bulk_s2g(A.head + ge0 * 3, o_head, GE * 12);
             }
             bulk_commit();
+            STAMP(99);
+            bulk_wait_read0();  // smem must stay alive until the TMA engine has read it
         }
     } else {
-        __syncthreads();
-        _Pragma("unroll 1") for (int i = tid; i < cnt * D; i += NT) { A.q[e0 * D + i] = o_q[i]; A.qd[e0 * D + i] = o_qd[i]; }
+        group_barrier(bar_id, GT);
+        _Pragma("unroll 1") for (int i = gtid; i < gcnt * D; i += GT) { A.q[ge0 * D + i] = o_q[i]; A.qd[ge0 * D + i] = o_qd[i]; }
         if (A.sens != nullptr)
-            _Pragma("unroll 1") for (int i = tid; i < cnt * S6n; i += NT) A.sens[e0 * S6n + i] = o_sens[i];
-        _Pragma("unroll 1") for (int i = tid; i < cnt * 3; i += NT) A.pos[e0 * 3 + i] = o_pos[i];
-        _Pragma("unroll 1") for (int i = tid; i < cnt * 4; i += NT) A.quat[e0 * 4 + i] = o_quat[i];
-        _Pragma("unroll 1") for (int i = tid; i < cnt * 6; i += NT) A.vel[e0 * 6 + i] = o_vel[i];
+            _Pragma("unroll 1") for (int i = gtid; i < gcnt * S6n; i += GT) A.sens[ge0 * S6n + i] = o_sens[i];
+        _Pragma("unroll 1") for (int i = gtid; i < gcnt * 3; i += GT) A.pos[ge0 * 3 + i] = o_pos[i];
+        _Pragma("unroll 1") for (int i = gtid; i < gcnt * 4; i += GT) A.quat[ge0 * 4 + i] = o_quat[i];
+        _Pragma("unroll 1") for (int i = gtid; i < gcnt * 6; i += GT) A.vel[ge0 * 6 + i] = o_vel[i];
         if (A.epi) {
-            _Pragma("unroll 1") for (int i = tid; i < cnt * OBS; i += NT) A.obs[e0 * OBS + i] = o_obs[i];
-            _Pragma("unroll 1") for (int i = tid; i < cnt * 3; i += NT) { A.up[e0 * 3 + i] = o_up[i]; A.head[e0 * 3 + i] = o_head[i]; }
+            _Pragma("unroll 1") for (int i = gtid; i < gcnt * OBS; i += GT) A.obs[ge0 * OBS + i] = o_obs[i];
+            _Pragma("unroll 1") for (int i = gtid; i < gcnt * 3; i += GT) { A.up[ge0 * 3 + i] = o_up[i]; A.head[ge0 * 3 + i] = o_head[i]; }
         }
-    }
-    STAMP(99);
-    if (tid == 0) {
-        if (A.epi && A.stats != nullptr) {
-            double r = 0.0, d = 0.0, l = 0.0;
-            for (int w = 0; w < EPC / 32; ++w) {
-                r += (double)s_stat[w * 3 + 0];
-                d += (double)s_stat[w * 3 + 1];
-                l += (double)s_stat[w * 3 + 2];
-            }
-            double* slot = A.stats + (blockIdx.x % OIGE_STATS_SLOTS) * 4;
-            atomicAdd(slot + 0, r);
-            atomicAdd(slot + 1, d);
-            atomicAdd(slot + 2, l);
-            atomicAdd(slot + 3, (double)cnt);
-        }
-        if (bulk) bulk_wait_read0();  // smem must stay alive until the TMA engine has read it
     }
 }
