@@ -273,6 +273,34 @@ int oige_env_step_host_f32(const OigeModel* model, const OigeTaskParams* params,
                            float clip_actions, uint64_t seed, uint64_t counter, int64_t env_id_offset,
                            int64_t n_envs, int32_t substeps, float dt, void* stream);
 
+/* ---- the host-buffer step for callers that cannot provide device scratch ----
+ * No counterpart in the reference (its .to(device) copies allocate through torch every step,
+ * envs/vec_env_rlgames.py:57): this exists for the users of THIS library's host-buffer step.
+ * oige_env_step_host_f32 wants `actions_dev_staging`, an [N,D] device buffer that is pure scratch.  The callers of the
+ * host-buffer step are the ones least able to supply it: a policy loop that lives in host memory behind a ctypes /
+ * cgo binding has no CUDA runtime of its own to allocate with, and inside a torch process a raw cudaMalloc from the
+ * step loop bypasses the caching allocator (it can fail once that pool holds the HBM, and it stalls the device).
+ * This variant keeps the staging rows in a fixed array inside the library image and allocates nothing: no cudaMalloc /
+ * cudaFree, no stream or event creation, no torch.  Same arguments as oige_env_step_host_f32 minus the staging
+ * pointer; same results, bit for bit, as oige_env_step_host_f32 / oige_env_step_f32.
+ *   limit      n_envs * params->num_dof <= OIGE_STATIC_STAGING_FLOATS (2 Mi floats = 8 MiB: 99,864 Humanoids, 262,144
+ *              Ants, 65,536 envs of a 32-DoF robot); beyond it the call returns OIGE_E_RANGE and does nothing.
+ *   footprint  every GPU that loads the library holds those 8 MiB until the process exits.
+ *   sharing    one array per GPU, used by every call: calls whose GPU work may overlap (other streams, other host
+ *              threads, several envs on one GPU) race on it -- keep them ordered on the device.  The array keeps the
+ *              previous call's rows; none of it needs clearing, the rows a call reads are the rows its own H2D wrote.
+ *   first call on each GPU it looks up the array's device address (with that GPU current) and caches it; make that
+ *              call -- n_envs = 0 suffices -- before beginning any stream capture.
+ * Copies and kernel run back to back on `stream` (no library-owned chunk streams); the caller synchronises `stream`
+ * before reading the host outputs. */
+#define OIGE_STATIC_STAGING_FLOATS (2 * 1024 * 1024)
+#define OIGE_STATIC_STAGING_BYTES (4 * OIGE_STATIC_STAGING_FLOATS)
+int oige_env_step_host_static_f32(const OigeModel* model, const OigeTaskParams* params, const OigeState* state,
+                                  const OigeTaskBuffers* buf, const OigeResetInit* init,
+                                  const float* actions_host, float* obs_host, float* rew_host, int64_t* reset_host,
+                                  float clip_actions, uint64_t seed, uint64_t counter, int64_t env_id_offset,
+                                  int64_t n_envs, int32_t substeps, float dt, void* stream);
+
 /* ================= Cartpole (tasks/cartpole.py) =================
  * Same three-kernel step as the locomotion tasks with the task-specific passes swapped:
  *   reset + efforts (pre_physics_step, cartpole.py:101-130)  ->  K2 on the 3-link welded-base tree

@@ -17,6 +17,7 @@ MAX_LINKS = 32
 MAX_SPHERES = 48
 MAX_SENSORS = 4
 MAX_PAIRS = 96
+STATIC_STAGING_FLOATS = 2 * 1024 * 1024  # OIGE_STATIC_STAGING_FLOATS: action floats one oige_env_step_host_static_f32 call may stage
 STATS_SLOTS = 2048
 ABI_VERSION = 3
 LIMIT_COST_HUMANOID = 0
@@ -133,7 +134,7 @@ EXPORTED_SYMBOLS = [
     "oige_obs_reward_reset_f32", "oige_obs_reward_reset_tile_f32",
     "oige_reset_masked_f32", "oige_reset_idx_f32",
     "oige_model_create", "oige_model_destroy", "oige_articulation_step_f32",
-    "oige_env_step_f32", "oige_env_step_host_f32",
+    "oige_env_step_f32", "oige_env_step_host_f32", "oige_env_step_host_static_f32",
     "oige_cartpole_obs_reward_reset_f32", "oige_cartpole_reset_masked_f32", "oige_cartpole_reset_idx_f32",
     "oige_cartpole_env_step_f32",
     "oige_anymal_obs_reward_reset_f32", "oige_anymal_reset_masked_f32", "oige_anymal_reset_idx_f32",
@@ -177,6 +178,10 @@ def load() -> C.CDLL:
     lib.oige_env_step_host_f32.argtypes = [vp, P(OigeTaskParams), P(OigeState), P(OigeTaskBuffers),
                                            P(OigeResetInit), vp, vp, vp, vp, vp, f32, u64, u64, i64, i64, i32,
                                            f32, vp]
+    lib.oige_env_step_host_static_f32.argtypes = [vp, P(OigeTaskParams), P(OigeState), P(OigeTaskBuffers),
+                                                  P(OigeResetInit), vp, vp, vp, vp, f32, u64, u64, i64, i64, i32,
+                                                  f32, vp]
+    lib.oige_env_step_host_static_f32.restype = C.c_int
     CP, CB = P(OigeCartpoleParams), P(OigeCartpoleBuffers)
     lib.oige_cartpole_obs_reward_reset_f32.argtypes = [CP, P(OigeState), CB, i64, vp]
     lib.oige_cartpole_reset_masked_f32.argtypes = [CP, P(OigeState), CB, vp, f32, vp, u64, u64, i64, i64, vp]

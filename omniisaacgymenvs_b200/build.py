@@ -31,6 +31,7 @@ SOURCES = [
     ("domain_randomization.cu", ["-fmad=false"]),
     ("articulation_step.cu", []),
     ("capi.cu", []),
+    ("env_step_host_static.cu", []),
 ]
 
 
