@@ -6,6 +6,8 @@ Keeps the reference attribute names (``obs_buf``, ``rew_buf``, ``reset_buf``, ``
 USD cloning / collision filtering / viewport set-up of the reference has no counterpart here:
 environments are rows of the state tensors and never interact.
 """
+import warnings
+
 import numpy as np
 import torch
 
@@ -100,13 +102,24 @@ class RLTask(BaseTask):
         return self._reset_counter_dev
 
     def _invalidate_graphs(self) -> None:
-        """Buffers were re-bound: graphs captured with the old pointers must not be replayed."""
+        """Buffers were re-bound: graphs captured with the old pointers must not be replayed.  Goes through the env's
+        own disable_* calls, which also hand the Randomizer back its host-side step counter -- the eager step does
+        not advance the device word the captured graphs used, so noise drawn from it would repeat every step."""
         env = getattr(self, "_env", None)
-        if env is not None:
-            if getattr(env, "_graph", None) is not None:
-                env._graph = None
-            if getattr(env, "_host_graphs", None):
-                env._host_graphs = {}
+        if env is None:
+            return
+        dropped = False
+        if getattr(env, "_graph", None) is not None:
+            env.disable_cuda_graph()
+            dropped = True
+        if getattr(env, "_host_graphs", None):
+            env.disable_cuda_graph_host()
+            dropped = True
+        if dropped and not getattr(self, "_warned_graph_drop", False):
+            self._warned_graph_drop = True
+            warnings.warn(f"{self.name}: a task buffer was re-assigned while CUDA-graph mode was on; the captured graphs "
+                          "were dropped and the env steps eagerly (about 3x the launch overhead) until "
+                          "enable_cuda_graph() / enable_cuda_graph_host() is called again", RuntimeWarning, stacklevel=3)
 
     def cleanup(self) -> None:
         """Allocates the RL buffers (rl_task.py:98-107)."""

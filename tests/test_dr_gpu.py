@@ -215,6 +215,42 @@ def test_env_step_with_noise_eager_equals_graph(cuda_lib, task_name):
     assert float(oe["obs"].abs().max()) <= float(task_e.clip_obs)
 
 
+def test_rebinding_a_buffer_in_graph_mode_drops_the_graph_and_keeps_the_noise_moving(cuda_lib):
+    """A caller re-assigns `task.obs_buf` while the step is captured (the reference's reset() re-creates buffers): the
+    graphs are dropped with ONE warning, the Randomizer goes back to the host-side step counter, and the eager steps
+    that follow draw the same fresh noise an always-eager env draws -- not the same draw every step from the device
+    counter nobody advances any more."""
+    n = 256
+    env_e, task_e = _env("Ant", n)
+    env_g, task_g = _env("Ant", n)
+    env_g.enable_cuda_graph()
+    gen = torch.Generator(device=DEV).manual_seed(9)
+
+    def both(t):
+        a = torch.rand(n, task_e.num_actions, device=DEV, generator=gen) * 2 - 1
+        oe, re_, de, _ = env_e.step(a)
+        og, rg, dg, _ = env_g.step(a)
+        assert torch.equal(oe["obs"], og["obs"]) and torch.equal(re_, rg) and torch.equal(de, dg), t
+        return og["obs"].clone()
+
+    for t in range(3):
+        both(t)
+    assert env_g._graph is not None
+    for task in (task_e, task_g):
+        task.obs_buf = task.obs_buf.clone()
+    task_e.get_observations()
+    with pytest.warns(RuntimeWarning, match="captured graphs were dropped"):
+        task_g.get_observations()  # the first hook after the re-assignment notices it
+    assert env_g._graph is None and task_g._dr_randomizer._counter_dev is None
+    seen = [both(t) for t in range(3, 8)]
+    assert all(not torch.equal(seen[i], seen[i + 1]) for i in range(len(seen) - 1))
+    import warnings as _w
+    with _w.catch_warnings():
+        _w.simplefilter("error")  # warned once, not on every later hook
+        task_g.obs_buf = task_g.obs_buf.clone()
+        task_g.get_observations()
+
+
 def test_env_noise_changes_observations_by_the_configured_amount(cuda_lib):
     """Only observation noise active: the physics is identical to the noise-free env, the returned observations
     differ from it by correlated + uncorrelated gaussians of the configured sigmas."""
