@@ -58,6 +58,10 @@ struct OigeModel {
 namespace oige {
 namespace {
 
+// envs parked by the non-finite guard of ANY articulation kernel (K2-W, K2-T, K2-F) since load, on this device
+// (oige_nonfinite_env_count; diagnostic)
+__device__ unsigned long long g_nonfinite_envs = 0;
+
 #ifndef TPE_MINBLOCKS
 #define TPE_MINBLOCKS 4
 #endif
@@ -117,10 +121,15 @@ __device__ __forceinline__ float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y 
 
 struct Q4 { float w, x, y, z; };
 // sin / cos of a joint HALF angle.  Joint limits keep |x| below ~1.4 rad (the knee: 160 deg / 2), where two short Taylor
-// chains (x^13, x^12: truncation < 2e-8 at |x| = 1.75, i.e. below half an ulp of the result) replace sincosf's range
-// reduction -- it heads the dependency chain of every link's kinematics.  Anything larger takes sincosf.
+// chains (x^13, x^12) replace sincosf's range reduction -- it heads the dependency chain of every link's kinematics.
+// Accuracy is ABSOLUTE (what the components of a unit quaternion need), not relative to the result: up to the 1.45 rad
+// cut-over |error| <= 1.03e-7 (sine) / 8.7e-8 (cosine), i.e. < 2 ulp of 1.0 against 0.5 ulp for a correctly rounded
+// value, nearly all of it Horner rounding (the first dropped terms are x^15/15! = 2e-10 and x^14/14! = 2.1e-9 there).
+// Near pi/2 the cosine is small and the same absolute error is many ulps OF THE RESULT; past 1.45 the dropped cosine
+// term grows to 2.9e-8 at 1.75 and the total passes 1.3e-7, so anything beyond 1.45 (unlimited test joints) takes
+// sincosf.  tests/test_oracle_math.py sweeps the restated chains against float64 sin / cos.
 __device__ __forceinline__ void sincos_half_angle(float x, float* s, float* c) {
-    if (fabsf(x) > 1.75f) {
+    if (fabsf(x) > 1.45f) {
         sincosf(x, s, c);
         return;
     }
@@ -706,6 +715,7 @@ articulation_step_kernel(const DevModel* __restrict__ gmodel, const __grid_const
     const unsigned bad_lanes = __ballot_sync(0xffffffffu, bad);
     const unsigned env_lanes = active ? (((L >= 32 ? 0u : (1u << L)) - 1u) << ebase) : 0u;
     if (bad_lanes & env_lanes) {  // any lane of THIS env
+        if (is_root) atomicAdd(&g_nonfinite_envs, 1ull);  // one lane per env
         q = 0.f; qd = 0.f;
         if (!fixed_base) {  // a welded base stays where it is; only the joints are zeroed
             rpos = {0.f, 0.f, -1.f};
@@ -997,6 +1007,7 @@ articulation_step_tpe_kernel(const DevModel* __restrict__ gmodel, const __grid_c
         rvel = {{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
     }
     if (bad) {
+        atomicAdd(&g_nonfinite_envs, 1ull);
         if (A.sens != nullptr)
             for (int k = 0; k < M.num_sensors * 6; ++k) A.sens[env * M.num_sensors * 6 + k] = 0.f;
     }
@@ -1226,7 +1237,6 @@ int k2_step(const OigeModel* model, const OigeTaskParams* P, const OigeState* st
         const void* ptrs[] = {F.pos, F.quat, F.vel, F.q, F.qd, F.actions, F.sens};
         for (const void* p : ptrs)
             if (p != nullptr && !al16(p)) F.use_bulk = 0;
-        if (F.sens == nullptr && F.S > 0) F.use_bulk = F.use_bulk;  // sensors are optional for a physics-only call
         return role_dispatch(model, P, F, stream, dn);
     }
     if (model->has_sc)

@@ -121,7 +121,7 @@ struct FArgs {
     float* rew_host; long long* reset_host;
 };
 
-__device__ unsigned long long g_nonfinite_envs = 0;  // envs parked by the non-finite guard since load (diagnostic)
+// g_nonfinite_envs (envs parked by the non-finite guard since load) is defined in articulation_step.cu: K2-W / K2-T count too
 
 // Phase timing (diagnostic build only, -DOIGE_STAMPS -> tools/k2f_stamps.py): (tag, clock64) pairs of group 0 of CTA 0.
 #ifdef OIGE_STAMPS

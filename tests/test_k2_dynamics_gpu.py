@@ -266,7 +266,11 @@ def test_non_finite_state_is_parked_for_reset(cuda_lib):
     st = dh.random_state(model, 64, 6)
     st["qd"][3, 2] = np.nan
     st["vel"][7, 0] = np.inf
+    from omniisaacgymenvs_b200 import _lib
+
+    parked0 = _lib.nonfinite_env_count()
     g = dh.run_gpu(cuda_lib, model, spec, st, 2, DT)
+    assert _lib.nonfinite_env_count() == parked0 + 2, "every articulation kernel counts the envs it parks"
     for k in g:
         assert np.isfinite(g[k]).all(), k
     assert g["pos"][3, 2] < spec.termination_height and g["pos"][7, 2] < spec.termination_height

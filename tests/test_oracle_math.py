@@ -94,3 +94,37 @@ def test_unscale_clamp_rand():
     torch.manual_seed(0)
     r = im.torch_rand_float(-0.2, 0.2, (1000, 3), "cpu")
     assert float(r.min()) >= -0.2 and float(r.max()) <= 0.2
+
+
+def test_half_angle_polynomials_absolute_error_up_to_the_cut_over():
+    """csrc/articulation_step.cu `sincos_half_angle`: the two Taylor chains K2 evaluates instead of sincosf for
+    |x| <= 1.45 rad, restated here with the same coefficients and the same fused multiply-adds (float64 product + sum,
+    rounded once to float32).  The bound that matters for a unit quaternion is ABSOLUTE: <= 1.1e-7 (< 2 ulp of 1.0)
+    inside the cut-over; between 1.45 and the old cut-over (1.75 rad) the error passes 1.3e-7, which is why the
+    cut-over was lowered -- there the kernel calls sincosf."""
+    f32 = np.float32
+
+    def fma(a, b, c):
+        return (a.astype(np.float64) * b.astype(np.float64) + np.asarray(c, np.float64)).astype(f32)
+
+    def chains(x):
+        x2 = (x * x).astype(f32)
+        ps = fma(x2, f32(1.6059044e-10), f32(-2.5052108e-8))
+        for c in (2.7557319e-6, -1.9841270e-4, 8.3333333e-3, -1.6666667e-1):
+            ps = fma(ps, x2, f32(c))
+        s = fma((ps * x2).astype(f32), x, x)
+        pc = fma(x2, f32(2.0876757e-9), f32(-2.7557319e-7))
+        for c in (2.4801587e-5, -1.3888889e-3, 4.1666667e-2, -0.5):
+            pc = fma(pc, x2, f32(c))
+        return s, fma(pc, x2, f32(1.0))
+
+    x = np.linspace(0.0, 1.45, 200001).astype(f32)
+    x = np.concatenate([x, -x])
+    s, c = chains(x)
+    xd = x.astype(np.float64)
+    assert np.abs(s - np.sin(xd)).max() <= 1.1e-7 and np.abs(c - np.cos(xd)).max() <= 1.1e-7
+    assert np.abs(s.astype(np.float64) ** 2 + c.astype(np.float64) ** 2 - 1.0).max() <= 2.5e-7
+    far = np.linspace(1.45, 1.75, 20001).astype(f32)
+    fs, fc = chains(far)
+    fd = far.astype(np.float64)
+    assert max(np.abs(fs - np.sin(fd)).max(), np.abs(fc - np.cos(fd)).max()) > 1.3e-7
