@@ -252,9 +252,17 @@ int oige_articulation_step_f32(const OigeModel* model, const OigeTaskParams* par
  * +-clip_actions into buf->actions, masked reset_idx of the flagged envs (tasks/shared/locomotion.py:103-145),
  * `substeps` articulation substeps, progress += 1 / observations / reward / done (tasks/base/rl_task.py:242,
  * locomotion.py:190-321).  No host synchronisation.  ONE launch (K2-F, env_step_role_kernel: prologue + substeps +
- * epilogue in the role-split articulation kernel) whenever that kernel serves the model and env count -- Humanoid
- * from 4096 envs, Ant from 1024; three launches (K3 -> K2-W / K2-T -> K1) otherwise.  Both paths produce the same
- * bits as calling the three entry points above one after the other. */
+ * epilogue in the role-split articulation kernel) whenever that kernel serves the model and env count; three launches
+ * (K3 -> K2-W / K2-T -> K1) otherwise.  The rule (k2_uses_role_kernel, csrc/articulation_step.cu):
+ *   - a model WITH collision pairs (the stock Humanoid) takes K2-F at EVERY env count -- only K2-F integrates
+ *     self-collision -- and a forced OIGE_K2_MODE=warp|thread then fails with OIGE_E_MODEL instead of dropping the pairs;
+ *   - without pairs, a three-role tree (Humanoid shape) takes K2-F from 4096 envs up; a four-role tree (Ant, Anymal) from
+ *     1024 envs up to two waves (2 * 4 * 32 * SM count = 37,888 envs on a B200), beyond which the three launches with the
+ *     thread-per-env kernel are faster for such small trees (OIGE_K2_MODE=role keeps K2-F);
+ *   - a tree the role split cannot cut (trunk not a path, more than 4 chains ...) always takes the three launches.
+ * Both paths produce the same bits as calling the three entry points above one after the other.
+ * buf->reset_counter, when not NULL, MUST be the two-word form {counter, ticket = 0} described at OigeTaskBuffers: K2-F
+ * does an atomic on word 1, so a one-word scalar from an older caller is written out of bounds. */
 int oige_env_step_f32(const OigeModel* model, const OigeTaskParams* params, const OigeState* state,
                       const OigeTaskBuffers* buf, const OigeResetInit* init, const float* actions_in,
                       float clip_actions, uint64_t seed, uint64_t counter, int64_t env_id_offset,
