@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define OIGE_ABI_VERSION 3
+#define OIGE_ABI_VERSION 4
 #define OIGE_MAX_DOF 32      /* one lane per link in the articulation kernel */
 #define OIGE_MAX_LINKS 32
 #define OIGE_MAX_SPHERES 48  /* collision spheres per robot */
@@ -113,12 +113,20 @@ typedef struct OigeTaskBuffers {
     float* up_vec;           /* [N,3] out */
     float* heading_vec;      /* [N,3] out */
     float* actions;          /* [N,D] the task's stored (clamped) actions */
-    double* episode_stats;   /* [OIGE_STATS_SLOTS,4] accumulators or NULL: sum(rew), #done, sum(len at done), #env-steps */
+    double* episode_stats;   /* [OIGE_STATS_SLOTS,4] accumulators or NULL: sum(rew) (see episode_return), #done,
+                                sum(len at done), #env-steps */
     uint64_t* reset_counter; /* NULL, or TWO device words {counter, 0}: oige_env_step_f32 then takes the Philox reset
                                 counter from word 0 (instead of its `counter` argument) and increments it at the end of
                                 the step, so that the step can be captured once in a CUDA graph and replayed; word 1 is
                                 scratch of the single-launch step (its CTAs take a ticket there: the last one to finish
                                 advances the counter) and must be zero between steps */
+    /* ---- ABI 4 ---- */
+    float* episode_return;   /* NULL, or [N] in/out running return of each env's CURRENT episode: every pass adds the
+                                step's reward, and an env whose episode ends in this pass (reset_buf set) contributes its
+                                return to episode_stats[.][0] and starts again from 0.  episode_stats[.][0] is then the
+                                sum of the RETURNS OF FINISHED EPISODES (what the reference's observer averages,
+                                utils/rlgames/rlgames_utils.py:51-62) instead of the sum of every env-step's reward.
+                                The caller zeroes the rows of envs it resets by hand (reset_idx). */
 } OigeTaskBuffers;
 
 /* Per-env initial state captured at post_reset (locomotion.py:148-150). */

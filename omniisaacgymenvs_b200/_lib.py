@@ -19,7 +19,7 @@ MAX_SENSORS = 4
 MAX_PAIRS = 96
 STATIC_STAGING_FLOATS = 2 * 1024 * 1024  # OIGE_STATIC_STAGING_FLOATS: action floats one oige_env_step_host_static_f32 call may stage
 STATS_SLOTS = 2048
-ABI_VERSION = 3
+ABI_VERSION = 4
 LIMIT_COST_HUMANOID = 0
 LIMIT_COST_ANT = 1
 
@@ -52,7 +52,8 @@ class OigeState(C.Structure):
 
 class OigeTaskBuffers(C.Structure):
     _fields_ = [("obs", vp), ("rew", vp), ("reset_buf", vp), ("progress_buf", vp), ("potentials", vp),
-                ("prev_potentials", vp), ("up_vec", vp), ("heading_vec", vp), ("actions", vp), ("episode_stats", vp), ("reset_counter", vp)]
+                ("prev_potentials", vp), ("up_vec", vp), ("heading_vec", vp), ("actions", vp), ("episode_stats", vp), ("reset_counter", vp),
+                ("episode_return", vp)]
 
 
 class OigeResetInit(C.Structure):

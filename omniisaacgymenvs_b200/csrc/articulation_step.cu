@@ -1200,6 +1200,7 @@ int k2_fused_step(const OigeModel* model, const OigeTaskParams* P, const OigeSta
     A.obs = b->obs; A.rew = b->rew; A.pot = b->potentials; A.prev_pot = b->prev_potentials; A.up = b->up_vec;
     A.head = b->heading_vec; A.reset = reinterpret_cast<long long*>(b->reset_buf);
     A.progress = reinterpret_cast<long long*>(b->progress_buf); A.stats = b->episode_stats;
+    A.ep_ret = b->episode_stats != nullptr ? b->episode_return : nullptr;
     if (rew_host != nullptr && reset_host != nullptr) { A.rew_host = rew_host; A.reset_host = reset_host; }
     const void* ptrs[] = {A.pos, A.quat, A.vel, A.q, A.qd, A.sens, A.actions_in, A.actions_out, A.init_pos, A.init_rot,
                           A.init_q, A.obs, A.rew, A.pot, A.prev_pot, A.up, A.head, A.reset, A.progress};

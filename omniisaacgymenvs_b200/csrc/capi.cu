@@ -334,6 +334,7 @@ int oige_env_step_host_f32(const OigeModel* model, const OigeTaskParams* params,
         OigeTaskBuffers bf = *buf;
         bf.obs += off * OBS; bf.rew += off; bf.reset_buf += off; bf.progress_buf += off; bf.potentials += off;
         bf.prev_potentials += off; bf.up_vec += off * 3; bf.heading_vec += off * 3; bf.actions += off * D;
+        if (bf.episode_return) bf.episode_return += off;
         if (obs_host_dev) bf.obs = obs_host_dev + off * OBS;
         // chunks share one counter: the host-provided one, or -- when buf->reset_counter is set (the call is being
         // captured in a CUDA graph) -- the device scalar, which K3 only reads; it is bumped once after the last chunk

@@ -116,6 +116,7 @@ struct FArgs {
     float* obs; float* rew; float* pot; float* prev_pot; float* up; float* head;
     long long* reset; long long* progress;
     double* stats;
+    float* ep_ret;   // [N] running return of the current episode (OigeTaskBuffers.episode_return) or null
     // host-buffer step, zero-copy mode: reward and reset flags are ALSO stored straight into the caller's pinned host
     // buffers (device-mapped pointers; null otherwise), so no copy-engine transfer follows the kernel
     float* rew_host; long long* reset_host;
@@ -1114,6 +1115,11 @@ env_step_role_kernel(const RoleModel* __restrict__ gmodel, const __grid_constant
             st_rew = total;
             st_done = rst != 0 ? 1.0f : 0.0f;
             st_len = rst != 0 ? (float)prog : 0.0f;
+            if (A.ep_ret != nullptr) {  // episodic return: published (and started over) in the step that ends the episode
+                const float ret = A.ep_ret[env] + total;
+                A.ep_ret[env] = rst != 0 ? 0.0f : ret;
+                st_rew = rst != 0 ? ret : 0.0f;
+            }
         }
         if (A.stats != nullptr && role == 0) {  // warp-uniform: one striped atomic set per group
 #pragma unroll

@@ -57,6 +57,7 @@ struct K1Args {
     long long* reset;
     long long* progress;
     double* stats;  // [OIGE_STATS_SLOTS][4] or null
+    float* ep_ret;  // [N] running return of the current episode (OigeTaskBuffers.episode_return) or null
     unsigned long long* step_counter;  // device-side reset counter to bump (whole-step calls only) or null
     long long n;
     int use_bulk;
@@ -237,6 +238,11 @@ __global__ void __launch_bounds__(4 * E) obs_reward_reset_kernel(const __grid_co
         st_rew = total;
         st_done = rst != 0 ? 1.0f : 0.0f;
         st_len = rst != 0 ? (float)prog : 0.0f;
+        if (A.ep_ret != nullptr) {  // episodic return: published (and started over) in the pass that ends the episode
+            const float ret = A.ep_ret[e0 + e] + total;
+            A.ep_ret[e0 + e] = rst != 0 ? 0.0f : ret;
+            st_rew = rst != 0 ? ret : 0.0f;
+        }
     }
     if (A.stats != nullptr && r == 0) {  // warp-uniform condition
 #pragma unroll
@@ -341,6 +347,7 @@ int k1_dispatch(const OigeTaskParams* P, const OigeState* st, const OigeTaskBuff
     A.reset = reinterpret_cast<long long*>(b->reset_buf);
     A.progress = reinterpret_cast<long long*>(b->progress_buf);
     A.stats = b->episode_stats;
+    A.ep_ret = b->episode_stats != nullptr ? b->episode_return : nullptr;
     A.step_counter = bump_counter ? reinterpret_cast<unsigned long long*>(b->reset_counter) : nullptr;
     A.n = n;
     const void* ptrs[] = {A.pos, A.quat, A.vel, A.q, A.qd, A.sens, A.act, A.pot, A.prev_pot,

@@ -112,14 +112,15 @@ class LocomotionTask(RLTask):
         self._buffers = _lib.OigeTaskBuffers(
             self.obs_buf.data_ptr(), self.rew_buf.data_ptr(), self.reset_buf.data_ptr(), self.progress_buf.data_ptr(),
             self.potentials.data_ptr(), self.prev_potentials.data_ptr(), self.up_vec.data_ptr(),
-            self.heading_vec.data_ptr(), self.actions.data_ptr(), self.episode_stats.data_ptr(), None)
+            self.heading_vec.data_ptr(), self.actions.data_ptr(), self.episode_stats.data_ptr(), None,
+            self.episode_return.data_ptr())
         # CUDA-graph twin: the Philox reset counter lives on the device and is bumped by the step itself
         self._ensure_reset_counter()
         self._buffers_graph = _lib.OigeTaskBuffers(
             self.obs_buf.data_ptr(), self.rew_buf.data_ptr(), self.reset_buf.data_ptr(), self.progress_buf.data_ptr(),
             self.potentials.data_ptr(), self.prev_potentials.data_ptr(), self.up_vec.data_ptr(),
             self.heading_vec.data_ptr(), self.actions.data_ptr(), self.episode_stats.data_ptr(),
-            self._reset_counter_dev.data_ptr())
+            self._reset_counter_dev.data_ptr(), self.episode_return.data_ptr())
         # staging twins for the individually-callable get_observations / calculate_metrics / is_done
         self._staged_rew = torch.zeros_like(self.rew_buf)
         self._staged_reset = torch.zeros_like(self.reset_buf)
@@ -218,6 +219,13 @@ class LocomotionTask(RLTask):
                                     C.byref(self._reset_init), env_ids.data_ptr(), k, rp, rv, self._reset_seed,
                                     self._reset_counter, self.env_id_offset, self._stream())
         _lib.check(rc, "oige_reset_idx_f32")
+        self.episode_return[env_ids] = 0.0  # a hand-reset env starts a new episode: its partial return is dropped
+
+    def reset(self):
+        """rl_task.py:218-221, plus: the partial returns of the episodes cut short here are not published."""
+        super().reset()
+        if hasattr(self, "episode_return"):
+            self.episode_return.zero_()
 
     def post_reset(self):
         """locomotion.py:147-171."""
@@ -238,8 +246,10 @@ class LocomotionTask(RLTask):
         self.potentials = torch.tensor([-1000.0 / self.dt], dtype=torch.float32, device=dev).repeat(n)
         self.prev_potentials = self.potentials.clone()
         self.actions = torch.zeros((n, self.num_actions), device=dev)
-        # episode statistics accumulated by K1 (sum rew, #done, sum len at done, #env-steps), striped
+        # episode statistics accumulated by K1 / K2-F (sum of the returns of finished episodes, #done, sum len at done,
+        # #env-steps), striped; episode_return is each env's running return, published when its episode ends
         self.episode_stats = torch.zeros((_lib.STATS_SLOTS, 4), device=dev, dtype=torch.float64)
+        self.episode_return = torch.zeros(n, device=dev, dtype=torch.float32)
         # landing buffer of poll_episode_extras, pinned HERE (cudaHostAlloc synchronises the device and takes
         # milliseconds: not something to do lazily inside a step)
         self._ep_host = torch.zeros(4, dtype=torch.float64).pin_memory()
@@ -309,7 +319,9 @@ class LocomotionTask(RLTask):
         """Puts the episode statistics where the reference's observer looks (``infos["episode"]``,
         utils/rlgames/rlgames_utils.py:51-62,67-91) WITHOUT a per-step sync: every ``every`` steps the striped
         accumulators are summed on the device and copied to pinned host memory asynchronously; the copy enqueued
-        earlier is published as the window's mean return / mean length / episode count once its event has completed
+        earlier is published as the window's mean return (sum of the returns of the episodes that FINISHED in the window,
+        each accumulated per env in ``episode_return`` by the kernel, over their count) / mean length / episode count
+        once its event has completed
         (polled with ``query()``, never waited for: a host that runs ahead of the device just tries again later).  ``extras["episode"]`` is present only in the step that publishes a window (the observer
         appends whatever it finds, so a stale entry would be counted again)."""
         self.extras.pop("episode", None)

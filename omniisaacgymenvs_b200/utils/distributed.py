@@ -63,7 +63,10 @@ class EpisodeStatsReducer:
         if self._side is not None:
             torch.cuda.current_stream(self.device).wait_stream(self._side)
         s = self.total.tolist()
+        # s[0]: sum of the returns of FINISHED episodes when the task passes OigeTaskBuffers.episode_return (the
+        # locomotion tasks do), else the sum of every env-step's reward (Cartpole / Anymal passes)
         return {"sum_reward": s[0], "episodes_finished": s[1],
+                "mean_episode_return": (s[0] / s[1]) if s[1] else None,
                 "mean_episode_length": (s[2] / s[1]) if s[1] else None, "env_steps": s[3]}
 
 

@@ -21,7 +21,7 @@ def test_library_builds_and_loads():
     assert os.path.exists(path)
     lib = ctypes.CDLL(path)
     lib.oige_abi_version.restype = ctypes.c_int
-    assert lib.oige_abi_version() == _lib.ABI_VERSION == 3
+    assert lib.oige_abi_version() == _lib.ABI_VERSION == 4
 
 
 def test_every_declared_symbol_is_exported():
@@ -38,7 +38,7 @@ def test_struct_layouts_match_header_sizes():
     # sizes computed by hand from the header: catches ctypes / C drift without running a kernel
     assert ctypes.sizeof(_lib.OigeTaskParams) == 8 * 4 + 16 * 4 + 4 * 16 + 4 * 32 * 4
     assert ctypes.sizeof(_lib.OigeState) == 7 * 8
-    assert ctypes.sizeof(_lib.OigeTaskBuffers) == 11 * 8
+    assert ctypes.sizeof(_lib.OigeTaskBuffers) == 12 * 8  # ABI 4: episode_return
     assert ctypes.sizeof(_lib.OigeResetInit) == 3 * 8
     assert ctypes.sizeof(_lib.OigeCartpoleParams) == 8 * 4
     assert ctypes.sizeof(_lib.OigeCartpoleBuffers) == 7 * 8

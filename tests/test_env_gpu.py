@@ -148,10 +148,19 @@ def test_resets_happen_and_episode_stats_accumulate(cuda_lib):
     env.reset()
     task.read_episode_stats()
     total_done = 0
+    # episodic return, accumulated here the way the reference's observer would see it per env (rlgames_utils.py:51-62)
+    running = task.episode_return.double().clone()  # the reset step's reward already belongs to the first episode
+    finished = 0.0
     for _ in range(50):
-        _, _, done, _ = env.step(torch.rand(n, 21, device=task.device) * 2 - 1)
+        _, rew, done, _ = env.step(torch.rand(n, 21, device=task.device) * 2 - 1)
         total_done += int(done.sum())
+        running += rew.double()
+        finished += float(running[done != 0].sum())
+        running[done != 0] = 0.0
     st = task.read_episode_stats()
+    # slot 0 is the sum of the RETURNS OF FINISHED EPISODES (per-env accumulator in the kernel), not of every reward
+    assert abs(float(st[0]) - finished) <= 1e-4 * abs(finished) + 1e-2
+    assert torch.allclose(task.episode_return.double(), running, rtol=1e-5, atol=1e-3)
     assert total_done > n  # every env times out at least twice in 50 steps of 20-step episodes
     assert int(st[1]) == total_done and int(st[3]) == 50 * n
     assert 1.0 <= float(st[2]) / float(st[1]) <= 20.0
